@@ -1,0 +1,126 @@
+// ba_device.h — device-side data layout and kernel launchers of the B200 bundle adjuster.
+//
+// Layout in HBM (one handle = one problem or one batch of independent problems):
+//   observations  sorted by (point, pose): obs_cam int32[No], obs_uv float2[No]      12 B/obs
+//                 (the owning point is implied by the CSR pt_ptr int32[Np+1])
+//   points        double[2][Np][3]  (current / candidate, per-problem `cur` selects)
+//   poses         double[2][Nc][7]  quaternion xyzw + t; cam_rt double[2][Nc][12] = R|t
+//   per-obs rec   double[No][12] = {x/z, y/z, 1/z, w, G~(2x3), v~(2)}  written by linearize,
+//                 gathered by schur_blocks and re-read by update (96 B, 32 B-sector aligned)
+//   per-point     double[Np][9] = {L^-1 (6, lower), L^-1 b_l (3)}                     72 B
+//   pair list     int2[Npairs] sorted by S block: the scatter-free gather order
+//   S             packed lower-triangular 6x6 blocks per problem, double[nblocks][36]
+#ifndef VISO_BA_DEVICE_H
+#define VISO_BA_DEVICE_H
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace visoba {
+
+constexpr int kRecDoubles = 12;   // per-observation record
+constexpr int kPtInfoDoubles = 9; // per-point record
+constexpr int kItemPart = 42;     // 36 block entries + 6 rhs entries per work item
+constexpr int kChunkPoints = 1024;
+constexpr int kSmallMaxN = 162; // dense per-problem solve in shared memory up to 27 free poses
+
+struct LmState { // one per problem, lives in device memory; g2o OptimizationAlgorithmLevenberg state
+    double lambda;
+    double nu;
+    double chi;         // robustified cost of the current state
+    double chi_start;   // cost at the start of the current outer iteration
+    double chi_initial; // cost before the first iteration
+    double rho;
+    double dp_sq;       // |delta_pose|^2 of the last solve (damping part of computeScale)
+    int32_t cur;        // which of the two state buffers is current
+    int32_t it;         // outer iterations finished
+    int32_t q;          // trials spent in the current outer iteration
+    int32_t trials;     // trials total
+    int32_t active;     // 0 once finished or terminated
+    int32_t terminated;
+    int32_t ok2;        // last solve succeeded (S + lambda I was positive definite)
+    int32_t accepted;   // a step was accepted in the current outer iteration
+    int32_t target_it;  // outer iterations requested
+    int32_t max_trials;
+};
+
+struct IterStat { // mirrors viso_ba_iter_stats
+    double cost_before, cost_after, lambda;
+    int32_t trials, accepted;
+};
+
+struct DevProblem {
+    // sizes
+    int32_t n_cams, n_points, n_problems;
+    int32_t pt_begin, pt_end; // this rank's point range (sharding); whole range otherwise
+    int64_t n_obs;
+    int64_t n_pairs;
+    int32_t n_items, n_diag_items, n_blocks, n_chunks;
+    // camera model / robust kernel
+    double fx, fy, cx, cy, huber_delta;
+    // topology
+    const int32_t* pt_ptr;
+    const int32_t* pt_prob;
+    const int32_t* obs_cam;
+    const float2* obs_uv;
+    const int32_t* cam_free;   // free index inside the problem or -1
+    const int32_t* cam_prob;
+    const int32_t* prob_cam0;  // [B+1]
+    const int32_t* prob_tri0;  // [B+1] first S block of the problem
+    const int32_t* prob_nfree; // [B]
+    const int2* pairs;
+    const int4* items;         // {pair_begin, pair_end, block, is_diag}
+    const int32_t* diag_items; // indices of the items of diagonal blocks
+    const int32_t* block_item_ptr; // [n_blocks+1]
+    const int32_t* block_cam;  // [n_blocks] global cam of the block row if diagonal else -1
+    const int4* chunks;        // {problem, pt_begin, pt_end, 0}
+    const int32_t* prob_chunk_ptr; // [B+1]
+    // state
+    double* pts[2];
+    double* pose[2];
+    double* cam_rt[2];
+    LmState* lm;
+    IterStat* iter_stats; // [target_it] (problem 0 only) or null
+    // workspace
+    double* rec;
+    double* ptinfo;
+    double* cost_pt;   // robust cost of the current state per point
+    double* cost_new_pt;
+    double* scale_pt;
+    double* item_part;
+    double* S_blk;     // [n_blocks][36] followed by bs
+    double* bs;        // [n_cams][6]  (zero rows for fixed poses)
+    double* dp;        // [n_cams][6]
+    double* chunk_part;// [n_chunks][2]
+    double* prob_sums; // [B][2]  (sharded: what gets all-reduced)
+    unsigned long long* maxdiag_bits; // [B]
+    int32_t* n_active; // [1]
+    double lambda_scale; // 1 on the rank that adds lambda to diag(S) (rank 0), else 0
+};
+
+struct LargeSolve { // dense path for one problem with n > kSmallMaxN
+    int32_t n;      // 6 * free poses
+    int32_t ld;     // leading dimension (doubles) of A, row-major, rows 0..n (row n = rhs)
+    double* A;
+    double* Dd;     // factorised diagonal blocks, [ceil(n/32)][32][32] (A's own are stale)
+    double* x;      // [n]
+    int32_t* fail;  // [1]
+};
+
+// launchers (all asynchronous on `st`); each returns the number of kernels it launched
+int launch_state_init(const DevProblem& P, int iterations, int max_trials, double lambda_init,
+                      cudaStream_t st);
+int launch_cam_rt(const DevProblem& P, int which, cudaStream_t st); // R|t of all poses of buffer
+int launch_linearize(const DevProblem& P, int init_pass, double lambda_override, cudaStream_t st);
+int launch_schur_blocks(const DevProblem& P, int diag_only, cudaStream_t st);
+int launch_block_finalize(const DevProblem& P, int init_pass, double lambda_override, cudaStream_t st);
+int launch_reduce(const DevProblem& P, int which, cudaStream_t st); // 0/2: cost_pt (2: even if inactive), 1: cost_new+scale
+int launch_lm_init(const DevProblem& P, double tau, double lambda_init, cudaStream_t st);
+int launch_solve_small(const DevProblem& P, int max_n, cudaStream_t st);
+int launch_solve_large(const DevProblem& P, const LargeSolve& L, cudaStream_t st);
+int launch_update(const DevProblem& P, cudaStream_t st);
+int launch_decide(const DevProblem& P, cudaStream_t st);
+int launch_eval_cost(const DevProblem& P, cudaStream_t st); // cost of current state -> cost_pt
+
+} // namespace visoba
+#endif

@@ -1,0 +1,1042 @@
+// ba_kernels.cu — hand-written sm_100a kernels of the viso bundle-adjustment hot path.
+//
+// Reference semantics restated on the device (citations relative to /root/reference):
+//   projection          include/keyframe.h:82-89          Pc = R Pw + t, u = fx x/z + cx
+//   2x6 pose Jacobian   src/viso.cpp:640-658 (dPixeldXi)  columns (v, w), left perturbation
+//   2x3 point Jacobian  first three columns of dPixeldXi times R (absent in the reference)
+//   pose update         include/bundle_adjuster.h:51-55   T <- exp(d) T
+//   point update        include/bundle_adjuster.h:34-38   P <- P + d
+//   6/3 block Schur     include/bundle_adjuster.h:108,:128 (g2o BlockSolver<6,3>, points marginalised)
+//   dense pose solve    include/bundle_adjuster.h:113-114 (g2o LinearSolverDense)
+//   LM                  include/bundle_adjuster.h:116-117 (g2o OptimizationAlgorithmLevenberg)
+//
+// No tensor cores: the blocks are 6x6 / 3x3 fp64.  Everything is scatter-free: per-point
+// quantities are owned by one thread, camera blocks are GATHERED through a pair list that
+// is sorted by destination block, and every cross-thread sum is a fixed-shape tree, so the
+// result is bit-reproducible and independent of the order edges were added in.
+#include "ba_device.h"
+
+#include <float.h>
+#include <math.h>
+
+namespace visoba {
+
+// ------------------------------------------------------------------------------------------
+// small helpers
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ double huber_rho(double s, double delta, double& w)
+{ // g2o RobustKernelHuber::robustify (rho[0], rho[1]); delta <= 0 -> plain L2
+    w = 1.0;
+    if (delta <= 0.0) return s;
+    const double dsqr = delta * delta;
+    if (s <= dsqr) return s;
+    const double sq = sqrt(s);
+    w = delta / sq;
+    return 2.0 * sq * delta - dsqr;
+}
+
+__device__ __forceinline__ void quat_to_R(const double* q, double* R)
+{
+    const double x = q[0], y = q[1], z = q[2], w = q[3];
+    R[0] = 1.0 - 2.0 * (y * y + z * z);
+    R[1] = 2.0 * (x * y - z * w);
+    R[2] = 2.0 * (x * z + y * w);
+    R[3] = 2.0 * (x * y + z * w);
+    R[4] = 1.0 - 2.0 * (x * x + z * z);
+    R[5] = 2.0 * (y * z - x * w);
+    R[6] = 2.0 * (x * z - y * w);
+    R[7] = 2.0 * (y * z + x * w);
+    R[8] = 1.0 - 2.0 * (x * x + y * y);
+}
+
+// Sophus SE3d::exp(xi) * T, xi = (v, w); writes the new pose (q xyzw, t)
+__device__ void pose_oplus(const double* xi, const double* pose, double* out)
+{
+    const double wx = xi[3], wy = xi[4], wz = xi[5];
+    const double th2 = wx * wx + wy * wy + wz * wz;
+    double im, re, a, b;
+    if (th2 < 1e-10) {
+        const double th4 = th2 * th2;
+        im = 0.5 - th2 / 48.0 + th4 / 3840.0;
+        re = 1.0 - th2 / 8.0 + th4 / 384.0;
+        a = 0.5 - th2 / 24.0 + th4 / 720.0;
+        b = 1.0 / 6.0 - th2 / 120.0 + th4 / 5040.0;
+    } else {
+        const double th = sqrt(th2);
+        double sh, ch, s1, c1;
+        sincos(0.5 * th, &sh, &ch);
+        sincos(th, &s1, &c1);
+        im = sh / th;
+        re = ch;
+        a = (1.0 - c1) / th2;
+        b = (th - s1) / (th2 * th);
+    }
+    const double dq[4] = { im * wx, im * wy, im * wz, re };
+    const double vx = xi[0], vy = xi[1], vz = xi[2];
+    const double c1x = wy * vz - wz * vy, c1y = wz * vx - wx * vz, c1z = wx * vy - wy * vx;
+    const double c2x = wy * c1z - wz * c1y, c2y = wz * c1x - wx * c1z, c2z = wx * c1y - wy * c1x;
+    const double dt0 = vx + a * c1x + b * c2x;
+    const double dt1 = vy + a * c1y + b * c2y;
+    const double dt2 = vz + a * c1z + b * c2z;
+    double dR[9];
+    quat_to_R(dq, dR);
+    const double bx = pose[0], by = pose[1], bz = pose[2], bw = pose[3];
+    const double qx = dq[3] * bx + dq[0] * bw + dq[1] * bz - dq[2] * by;
+    const double qy = dq[3] * by - dq[0] * bz + dq[1] * bw + dq[2] * bx;
+    const double qz = dq[3] * bz + dq[0] * by - dq[1] * bx + dq[2] * bw;
+    const double qw = dq[3] * bw - dq[0] * bx - dq[1] * by - dq[2] * bz;
+    const double n = 1.0 / sqrt(qx * qx + qy * qy + qz * qz + qw * qw);
+    out[0] = qx * n;
+    out[1] = qy * n;
+    out[2] = qz * n;
+    out[3] = qw * n;
+    const double tx = pose[4], ty = pose[5], tz = pose[6];
+    out[4] = dR[0] * tx + dR[1] * ty + dR[2] * tz + dt0;
+    out[5] = dR[3] * tx + dR[4] * ty + dR[5] * tz + dt1;
+    out[6] = dR[6] * tx + dR[7] * ty + dR[8] * tz + dt2;
+}
+
+__device__ __forceinline__ void write_cam_rt(const double* pose, double* rt)
+{
+    double R[9];
+    quat_to_R(pose, R);
+#pragma unroll
+    for (int i = 0; i < 9; ++i) rt[i] = R[i];
+    rt[9] = pose[4];
+    rt[10] = pose[5];
+    rt[11] = pose[6];
+}
+
+// ------------------------------------------------------------------------------------------
+// state init / R|t cache
+// ------------------------------------------------------------------------------------------
+__global__ void k_state_init(DevProblem P, int iterations, int max_trials, double lambda_init)
+{
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b == 0) *P.n_active = P.n_problems;
+    if (b >= P.n_problems) return;
+    LmState& s = P.lm[b];
+    s.lambda = lambda_init;
+    s.nu = 2.0;
+    s.chi = 0.0;
+    s.chi_start = 0.0;
+    s.chi_initial = 0.0;
+    s.rho = 0.0;
+    s.dp_sq = 0.0;
+    s.it = 0;
+    s.q = 0;
+    s.trials = 0;
+    s.active = iterations > 0 ? 1 : 0;
+    s.terminated = 0;
+    s.ok2 = 1;
+    s.accepted = 0;
+    s.target_it = iterations;
+    s.max_trials = max_trials;
+    P.maxdiag_bits[b] = 0ull;
+    if (iterations <= 0 && b == 0) *P.n_active = 0;
+}
+
+__global__ void k_cam_rt(DevProblem P, int which)
+{
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= P.n_cams) return;
+    write_cam_rt(P.pose[which] + 7 * (size_t)c, P.cam_rt[which] + 12 * (size_t)c);
+}
+
+// ------------------------------------------------------------------------------------------
+// K1 linearize: one thread per point.
+//   pass 1  H_ll = sum w Jl^T Jl, b_l = -sum w Jl^T r, robust cost of the point
+//   3x3     L L^T = H_ll + lambda I, L^-1, zb = L^-1 b_l          -> ptinfo (72 B)
+//   pass 2  per observation record {x/z, y/z, 1/z, w, G~ = F w Jl L^-T, v~ = F (w r + G zb)}
+// The record is all the camera-block gather (K2) and the back substitution (K4) need:
+//   S_IJ  -= Jp_a^T G_a G_b^T Jp_b,  S_II += w Jp_a^T Jp_a,  bs_I -= Jp_a^T v_a
+// with Jp = F J~(x/z, y/z, 1/z) rebuilt from three doubles (viso.cpp:653-655).
+// ------------------------------------------------------------------------------------------
+struct ObsGeom {
+    double xn, yn, iz, ru, rv, w, rho;
+    double jl0[3], jl1[3]; // rows of the 2x3 point Jacobian (with fx, fy)
+};
+
+__device__ __forceinline__ void obs_geometry(const DevProblem& P, const double* __restrict__ rt,
+    double X, double Y, double Z, float2 uv, ObsGeom& g)
+{
+    const double x = rt[0] * X + rt[1] * Y + rt[2] * Z + rt[9];
+    const double y = rt[3] * X + rt[4] * Y + rt[5] * Z + rt[10];
+    const double z = rt[6] * X + rt[7] * Y + rt[8] * Z + rt[11];
+    g.iz = 1.0 / z;
+    g.xn = x * g.iz;
+    g.yn = y * g.iz;
+    g.ru = P.fx * g.xn + P.cx - (double)uv.x;
+    g.rv = P.fy * g.yn + P.cy - (double)uv.y;
+    g.rho = huber_rho(g.ru * g.ru + g.rv * g.rv, P.huber_delta, g.w);
+    const double a0 = P.fx * g.iz, a2 = -P.fx * g.xn * g.iz;
+    const double b1 = P.fy * g.iz, b2 = -P.fy * g.yn * g.iz;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        g.jl0[k] = a0 * rt[k] + a2 * rt[6 + k];
+        g.jl1[k] = b1 * rt[3 + k] + b2 * rt[6 + k];
+    }
+}
+
+__global__ void __launch_bounds__(128) k_linearize(DevProblem P, int init_pass, double lambda_override)
+{
+    const int p = P.pt_begin + blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= P.pt_end) return;
+    const int prob = P.pt_prob[p];
+    const LmState& st = P.lm[prob];
+    if (!st.active && lambda_override < 0.0) return;
+    const int cur = st.cur;
+    const double lambda = init_pass ? 0.0 : (lambda_override >= 0.0 ? lambda_override : st.lambda);
+    const double* __restrict__ pt = P.pts[cur] + 3 * (size_t)p;
+    const double X = pt[0], Y = pt[1], Z = pt[2];
+    const double* __restrict__ cam_rt = P.cam_rt[cur];
+    const int s0 = P.pt_ptr[p], s1 = P.pt_ptr[p + 1];
+
+    double h00 = 0, h10 = 0, h11 = 0, h20 = 0, h21 = 0, h22 = 0, b0 = 0, b1 = 0, b2 = 0, cost = 0;
+    for (int s = s0; s < s1; ++s) {
+        const int cam = __ldg(P.obs_cam + s);
+        const float2 uv = __ldg(P.obs_uv + s);
+        ObsGeom g;
+        obs_geometry(P, cam_rt + 12 * (size_t)cam, X, Y, Z, uv, g);
+        cost += g.rho;
+        h00 += g.w * (g.jl0[0] * g.jl0[0] + g.jl1[0] * g.jl1[0]);
+        h10 += g.w * (g.jl0[1] * g.jl0[0] + g.jl1[1] * g.jl1[0]);
+        h11 += g.w * (g.jl0[1] * g.jl0[1] + g.jl1[1] * g.jl1[1]);
+        h20 += g.w * (g.jl0[2] * g.jl0[0] + g.jl1[2] * g.jl1[0]);
+        h21 += g.w * (g.jl0[2] * g.jl0[1] + g.jl1[2] * g.jl1[1]);
+        h22 += g.w * (g.jl0[2] * g.jl0[2] + g.jl1[2] * g.jl1[2]);
+        b0 -= g.w * (g.jl0[0] * g.ru + g.jl1[0] * g.rv);
+        b1 -= g.w * (g.jl0[1] * g.ru + g.jl1[1] * g.rv);
+        b2 -= g.w * (g.jl0[2] * g.ru + g.jl1[2] * g.rv);
+    }
+    P.cost_pt[p] = cost;
+    double i00 = 0, i10 = 0, i11 = 0, i20 = 0, i21 = 0, i22 = 0, z0 = 0, z1 = 0, z2 = 0;
+    if (init_pass) {
+        // g2o computeLambdaInit: the point part of max diag(H); max is order-free -> deterministic
+        const double m = fmax(h00, fmax(h11, h22));
+        if (m > 0.0) atomicMax(P.maxdiag_bits + prob, (unsigned long long)__double_as_longlong(m));
+    } else {
+        h00 += lambda;
+        h11 += lambda;
+        h22 += lambda;
+        const double l00 = sqrt(h00);
+        i00 = 1.0 / l00;
+        const double l10 = h10 * i00, l20 = h20 * i00;
+        const double l11 = sqrt(h11 - l10 * l10);
+        i11 = 1.0 / l11;
+        const double l21 = (h21 - l20 * l10) * i11;
+        const double l22 = sqrt(h22 - l20 * l20 - l21 * l21);
+        i22 = 1.0 / l22;
+        i10 = -l10 * i00 * i11;
+        i21 = -l21 * i11 * i22;
+        i20 = -(l20 * i00 + l21 * i10) * i22;
+        z0 = i00 * b0;
+        z1 = i10 * b0 + i11 * b1;
+        z2 = i20 * b0 + i21 * b1 + i22 * b2;
+    }
+    double* info = P.ptinfo + kPtInfoDoubles * (size_t)p;
+    info[0] = i00, info[1] = i10, info[2] = i11, info[3] = i20, info[4] = i21, info[5] = i22;
+    info[6] = z0, info[7] = z1, info[8] = z2;
+
+    for (int s = s0; s < s1; ++s) {
+        const int cam = __ldg(P.obs_cam + s);
+        const float2 uv = __ldg(P.obs_uv + s);
+        ObsGeom g;
+        obs_geometry(P, cam_rt + 12 * (size_t)cam, X, Y, Z, uv, g);
+        // G = w Jl L^-T   (L^-T)[m][k] = Linv[k][m], k >= m
+        const double g00 = g.w * (g.jl0[0] * i00);
+        const double g01 = g.w * (g.jl0[0] * i10 + g.jl0[1] * i11);
+        const double g02 = g.w * (g.jl0[0] * i20 + g.jl0[1] * i21 + g.jl0[2] * i22);
+        const double g10 = g.w * (g.jl1[0] * i00);
+        const double g11 = g.w * (g.jl1[0] * i10 + g.jl1[1] * i11);
+        const double g12 = g.w * (g.jl1[0] * i20 + g.jl1[1] * i21 + g.jl1[2] * i22);
+        const double v0 = g.w * g.ru + g00 * z0 + g01 * z1 + g02 * z2;
+        const double v1 = g.w * g.rv + g10 * z0 + g11 * z1 + g12 * z2;
+        double2* r = reinterpret_cast<double2*>(P.rec + kRecDoubles * (size_t)s);
+        r[0] = make_double2(g.xn, g.yn);
+        r[1] = make_double2(g.iz, g.w);
+        r[2] = make_double2(P.fx * g00, P.fx * g01);
+        r[3] = make_double2(P.fx * g02, P.fy * g10);
+        r[4] = make_double2(P.fy * g11, P.fy * g12);
+        r[5] = make_double2(P.fx * v0, P.fy * v1);
+    }
+}
+
+// cost of the current state only (viso_ba_eval_cost): same pass 1 without the rest
+__global__ void __launch_bounds__(128) k_eval_cost(DevProblem P)
+{
+    const int p = P.pt_begin + blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= P.pt_end) return;
+    const int cur = P.lm[P.pt_prob[p]].cur;
+    const double* __restrict__ pt = P.pts[cur] + 3 * (size_t)p;
+    const double X = pt[0], Y = pt[1], Z = pt[2];
+    const double* __restrict__ cam_rt = P.cam_rt[cur];
+    double cost = 0;
+    for (int s = P.pt_ptr[p]; s < P.pt_ptr[p + 1]; ++s) {
+        ObsGeom g;
+        obs_geometry(P, cam_rt + 12 * (size_t)__ldg(P.obs_cam + s), X, Y, Z, __ldg(P.obs_uv + s), g);
+        cost += g.rho;
+    }
+    P.cost_pt[p] = cost;
+}
+
+// ------------------------------------------------------------------------------------------
+// K2 schur_blocks: one warp per work item (a slice of the pair list of one S block).
+// Each lane gathers two 96-byte records per pair, forms  X = J~_a^T M J~_b  (6x6) with
+// M = -G~_a G~_b^T (+ diag(w fx^2, w fy^2) when a == b) and keeps 36 + 6 fp64 accumulators in
+// registers.  The warp then folds them with a recursive-halving butterfly (31 shuffles for
+// 32 values instead of 160) and lane e writes entry e of the item's partial block.
+// ------------------------------------------------------------------------------------------
+template <int N>
+__device__ __forceinline__ void butterfly_reduce(double (&v)[N], int lane)
+{ // N = 32: afterwards lane l holds the warp total of v[l] in v[0]
+#pragma unroll
+    for (int off = 16, cnt = N / 2; off >= 1; off >>= 1, cnt >>= 1) {
+        const bool upper = (lane & off) != 0;
+#pragma unroll
+        for (int i = 0; i < cnt; ++i) {
+            const double send = upper ? v[i] : v[i + cnt];
+            const double keep = upper ? v[i + cnt] : v[i];
+            v[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+        }
+    }
+}
+
+__device__ __forceinline__ void jtilde(double xn, double yn, double iz, double (&r0)[6], double (&r1)[6])
+{ // viso.cpp:653-655 without the fx / fy factors
+    r0[0] = iz, r0[1] = 0.0, r0[2] = -xn * iz, r0[3] = -xn * yn, r0[4] = 1.0 + xn * xn, r0[5] = -yn;
+    r1[0] = 0.0, r1[1] = iz, r1[2] = -yn * iz, r1[3] = -(1.0 + yn * yn), r1[4] = xn * yn, r1[5] = xn;
+}
+
+__global__ void __launch_bounds__(128) k_schur_blocks(DevProblem P, int diag_only)
+{
+    const int lane = threadIdx.x & 31;
+    const int widx = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    int item;
+    if (diag_only) {
+        if (widx >= P.n_diag_items) return;
+        item = P.diag_items[widx];
+    } else {
+        if (widx >= P.n_items) return;
+        item = widx;
+    }
+    const int4 it = P.items[item];
+    const int prob = it.w >> 1;
+    const bool is_diag = (it.w & 1) != 0;
+    if (!P.lm[prob].active) return;
+    const double fx2 = P.fx * P.fx, fy2 = P.fy * P.fy;
+
+    double acc[32];
+    double acc2[16]; // entries 32..35 of the block, then 6 rhs entries, padded to 16
+#pragma unroll
+    for (int i = 0; i < 32; ++i) acc[i] = 0.0;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) acc2[i] = 0.0;
+
+    for (int q = it.x + lane; q < it.y; q += 32) {
+        const int2 pr = __ldg(P.pairs + q);
+        const double2* __restrict__ ra = reinterpret_cast<const double2*>(P.rec + kRecDoubles * (size_t)pr.x);
+        const double2* __restrict__ rb = reinterpret_cast<const double2*>(P.rec + kRecDoubles * (size_t)pr.y);
+        const double2 a0 = ra[0], a1 = ra[1], a2 = ra[2], a3 = ra[3], a4 = ra[4];
+        const double2 b0 = rb[0], b1 = rb[1], b2 = rb[2], b3 = rb[3], b4 = rb[4];
+        double ja0[6], ja1[6], jb0[6], jb1[6];
+        jtilde(a0.x, a0.y, a1.x, ja0, ja1);
+        jtilde(b0.x, b0.y, b1.x, jb0, jb1);
+        // M = -G~_a G~_b^T
+        double m00 = -(a2.x * b2.x + a2.y * b2.y + a3.x * b3.x);
+        double m01 = -(a2.x * b3.y + a2.y * b4.x + a3.x * b4.y);
+        double m10 = -(a3.y * b2.x + a4.x * b2.y + a4.y * b3.x);
+        double m11 = -(a3.y * b3.y + a4.x * b4.x + a4.y * b4.y);
+        const bool same = pr.x == pr.y;
+        if (same) {
+            m00 += a1.y * fx2;
+            m11 += a1.y * fy2;
+        }
+        double t0[6], t1[6];
+#pragma unroll
+        for (int c = 0; c < 6; ++c) {
+            t0[c] = m00 * jb0[c] + m01 * jb1[c];
+            t1[c] = m10 * jb0[c] + m11 * jb1[c];
+        }
+        double x[36];
+#pragma unroll
+        for (int r = 0; r < 6; ++r)
+#pragma unroll
+            for (int c = 0; c < 6; ++c) x[6 * r + c] = ja0[r] * t0[c] + ja1[r] * t1[c];
+        if (is_diag && !same) { // duplicate (point, pose) edges: both (a,b) and (b,a) land here
+#pragma unroll
+            for (int r = 0; r < 6; ++r)
+#pragma unroll
+                for (int c = r; c < 6; ++c) {
+                    const double sdiag = x[6 * r + c] + x[6 * c + r];
+                    x[6 * r + c] = sdiag;
+                    x[6 * c + r] = sdiag;
+                }
+        }
+#pragma unroll
+        for (int i = 0; i < 32; ++i) acc[i] += x[i];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) acc2[i] += x[32 + i];
+        if (same) {
+            const double2 a5 = ra[5];
+#pragma unroll
+            for (int r = 0; r < 6; ++r) acc2[4 + r] += ja0[r] * a5.x + ja1[r] * a5.y;
+        }
+    }
+    butterfly_reduce<32>(acc, lane);
+    // second group: 16 padded values; fold the two half-warps first, then butterfly over 16 lanes
+#pragma unroll
+    for (int i = 0; i < 16; ++i) acc2[i] += __shfl_xor_sync(0xffffffffu, acc2[i], 16);
+#pragma unroll
+    for (int off = 8, cnt = 8; off >= 1; off >>= 1, cnt >>= 1) {
+        const bool upper = (lane & off) != 0;
+#pragma unroll
+        for (int i = 0; i < cnt; ++i) {
+            const double send = upper ? acc2[i] : acc2[i + cnt];
+            const double keep = upper ? acc2[i + cnt] : acc2[i];
+            acc2[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+        }
+    }
+    double* out = P.item_part + kItemPart * (size_t)item;
+    out[lane] = acc[0];
+    if (lane < 10) out[32 + lane] = acc2[0];
+}
+
+// K2b: one warp per S block sums the item partials in list order, adds lambda on the
+// diagonal (g2o setLambda) and writes S_blk / bs.  bs sign: g2o solves H x = b, b = -J^T r.
+__global__ void __launch_bounds__(128) k_block_finalize(DevProblem P, int init_pass, double lambda_override)
+{
+    const int lane = threadIdx.x & 31;
+    const int blk = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (blk >= P.n_blocks) return;
+    const int cam = P.block_cam[blk];
+    if (init_pass && cam < 0) return;
+    const int i0 = P.block_item_ptr[blk], i1 = P.block_item_ptr[blk + 1];
+    int prob = 0;
+    if (cam >= 0) prob = P.cam_prob[cam];
+    else if (i0 < i1) prob = P.items[i0].w >> 1;
+    else { // block with no co-visible point: keep it zero
+        for (int e = lane; e < 36; e += 32) P.S_blk[36 * (size_t)blk + e] = 0.0;
+        return;
+    }
+    const LmState& st = P.lm[prob];
+    if (!st.active && lambda_override < 0.0) return;
+    const double lambda = init_pass ? 0.0 : (lambda_override >= 0.0 ? lambda_override : st.lambda);
+    for (int e = lane; e < kItemPart; e += 32) {
+        if (e >= 36 && cam < 0) break;
+        double s = 0.0;
+        for (int i = i0; i < i1; ++i) s += P.item_part[kItemPart * (size_t)i + e];
+        if (e < 36) {
+            if (cam >= 0 && (e % 7) == 0) s += lambda * P.lambda_scale;
+            P.S_blk[36 * (size_t)blk + e] = s;
+        } else {
+            P.bs[6 * (size_t)cam + (e - 36)] = -s;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// deterministic sums: chunk partials (fixed tree inside a CTA), then one thread per problem
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_chunk_reduce(DevProblem P, int which)
+{
+    __shared__ double sh[2][256];
+    const int4 ch = P.chunks[blockIdx.x];
+    if (!P.lm[ch.x].active && which != 2) return;
+    double a = 0.0, b = 0.0;
+    const double* src0 = which == 1 ? P.cost_new_pt : P.cost_pt;
+    for (int p = ch.y + threadIdx.x; p < ch.z; p += 256) {
+        a += src0[p];
+        if (which == 1) b += P.scale_pt[p];
+    }
+    sh[0][threadIdx.x] = a;
+    sh[1][threadIdx.x] = b;
+    __syncthreads();
+    for (int s = 128; s > 0; s >>= 1) {
+        if (threadIdx.x < s) {
+            sh[0][threadIdx.x] += sh[0][threadIdx.x + s];
+            sh[1][threadIdx.x] += sh[1][threadIdx.x + s];
+        }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        P.chunk_part[2 * (size_t)blockIdx.x] = sh[0][0];
+        P.chunk_part[2 * (size_t)blockIdx.x + 1] = sh[1][0];
+    }
+}
+
+__global__ void k_prob_sums(DevProblem P, int which)
+{
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= P.n_problems) return;
+    if (!P.lm[b].active && which != 2) return;
+    double s0 = 0.0, s1 = 0.0;
+    for (int c = P.prob_chunk_ptr[b]; c < P.prob_chunk_ptr[b + 1]; ++c) {
+        s0 += P.chunk_part[2 * (size_t)c];
+        s1 += P.chunk_part[2 * (size_t)c + 1];
+    }
+    P.prob_sums[2 * (size_t)b] = s0;
+    P.prob_sums[2 * (size_t)b + 1] = s1;
+}
+
+// g2o computeLambdaInit + first computeActiveErrors: lambda_0 = tau * max diag(H), chi_0
+__global__ void k_lm_init(DevProblem P, double tau, double lambda_init)
+{
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= P.n_problems) return;
+    LmState& s = P.lm[b];
+    double m = __longlong_as_double((long long)P.maxdiag_bits[b]);
+    const int tri0 = P.prob_tri0[b];
+    const int nf = P.prob_nfree[b];
+    for (int I = 0; I < nf; ++I) {
+        const double* blk = P.S_blk + 36 * (size_t)(tri0 + I * (I + 1) / 2 + I);
+        for (int r = 0; r < 6; ++r) m = fmax(m, fabs(blk[7 * r]));
+    }
+    s.chi = P.prob_sums[2 * (size_t)b];
+    s.chi_initial = s.chi;
+    s.chi_start = s.chi;
+    if (!(lambda_init > 0.0)) s.lambda = tau * m;
+    s.nu = 2.0;
+}
+
+// ------------------------------------------------------------------------------------------
+// K3 (small): one CTA per problem.  S (+ rhs as an extra row, so that the forward
+// substitution falls out of the factorisation) is assembled densely in shared memory,
+// factorised by a right-looking Cholesky, back-substituted by one warp, and the candidate
+// poses  T' = exp(d) T  are written straight away.
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_solve_small(DevProblem P)
+{
+    extern __shared__ double sm[];
+    __shared__ int s_fail;
+    const int b = blockIdx.x;
+    LmState& st = P.lm[b];
+    if (!st.active) return;
+    const int nf = P.prob_nfree[b];
+    const int n = 6 * nf;
+    const int ld = (n + 1) | 1;
+    const int tid = threadIdx.x, nt = blockDim.x;
+    const int cam0 = P.prob_cam0[b], cam1 = P.prob_cam0[b + 1];
+    const int tri0 = P.prob_tri0[b];
+    const int cur = st.cur;
+    if (tid == 0) s_fail = 0;
+    // assemble the lower triangle
+    const int nblk = nf * (nf + 1) / 2;
+    for (int idx = tid; idx < nblk * 36; idx += nt) {
+        const int blk = idx / 36, e = idx - 36 * blk;
+        int I = (int)((sqrt(8.0 * (double)blk + 1.0) - 1.0) * 0.5);
+        while ((I + 1) * (I + 2) / 2 <= blk) ++I;
+        while (I * (I + 1) / 2 > blk) --I;
+        const int J = blk - I * (I + 1) / 2;
+        const int r = e / 6, c = e - 6 * r;
+        sm[(6 * I + r) * ld + 6 * J + c] = P.S_blk[36 * (size_t)(tri0 + blk) + e];
+    }
+    for (int c = cam0 + tid; c < cam1; c += nt) {
+        const int f = P.cam_free[c];
+        if (f >= 0)
+            for (int r = 0; r < 6; ++r) sm[n * ld + 6 * f + r] = P.bs[6 * (size_t)c + r];
+    }
+    __syncthreads();
+    const int warp = tid >> 5, lane = tid & 31, nw = nt >> 5;
+    for (int j = 0; j < n; ++j) {
+        if (tid == 0) {
+            const double d = sm[j * ld + j];
+            if (!(d > 0.0) || !isfinite(d)) s_fail = 1;
+            sm[j * ld + j] = sqrt(d);
+        }
+        __syncthreads();
+        if (s_fail) break;
+        const double inv = 1.0 / sm[j * ld + j];
+        for (int i = j + 1 + tid; i <= n; i += nt) sm[i * ld + j] *= inv;
+        __syncthreads();
+        for (int i = j + 1 + warp; i <= n; i += nw) {
+            const double lij = sm[i * ld + j];
+            const int kmax = i < n ? i : n - 1;
+            for (int k = j + 1 + lane; k <= kmax; k += 32) sm[i * ld + k] -= lij * sm[k * ld + j];
+        }
+        __syncthreads();
+    }
+    const int fail = s_fail;
+    // backward substitution  L^T x = y  (y sits in row n), one warp, row-contiguous reads
+    if (warp == 0 && !fail) {
+        double* y = sm + n * ld;
+        for (int j = n - 1; j >= 0; --j) {
+            const double xj = y[j] / sm[j * ld + j];
+            __syncwarp();
+            if (lane == 0) y[j] = xj;
+            for (int i = lane; i < j; i += 32) y[i] -= sm[j * ld + i] * xj;
+            __syncwarp();
+        }
+    }
+    __syncthreads();
+    // scatter the step, build candidate poses
+    const int cand = cur ^ 1;
+    for (int c = cam0 + tid; c < cam1; c += nt) {
+        const int f = P.cam_free[c];
+        double d[6];
+        for (int r = 0; r < 6; ++r) d[r] = (f >= 0 && !fail) ? sm[n * ld + 6 * f + r] : 0.0;
+        for (int r = 0; r < 6; ++r) P.dp[6 * (size_t)c + r] = d[r];
+        const double* pc = P.pose[cur] + 7 * (size_t)c;
+        double* pn = P.pose[cand] + 7 * (size_t)c;
+        if (f >= 0 && !fail) pose_oplus(d, pc, pn);
+        else
+            for (int r = 0; r < 7; ++r) pn[r] = pc[r];
+        write_cam_rt(pn, P.cam_rt[cand] + 12 * (size_t)c);
+    }
+    if (tid == 0) {
+        double ss = 0.0;
+        if (!fail)
+            for (int i = 0; i < n; ++i) ss += sm[n * ld + i] * sm[n * ld + i];
+        st.dp_sq = ss;
+        st.ok2 = fail ? 0 : 1;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// K3 (large, one problem): dense lower matrix in global memory, rhs as row n.
+// Blocked right-looking Cholesky with NB = 32: panel kernel (diagonal block factorised
+// redundantly by every CTA + triangular solve of its rows), trailing-update kernel.
+// ------------------------------------------------------------------------------------------
+constexpr int kNB = 32;
+
+__global__ void __launch_bounds__(256) k_dense_assemble(DevProblem P, LargeSolve L)
+{ // one warp per S block (problem 0)
+    const int lane = threadIdx.x & 31;
+    const int blk = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int nf = P.prob_nfree[0];
+    const int nblk = nf * (nf + 1) / 2;
+    if (blk == 0 && lane == 0) *L.fail = 0;
+    if (blk < nblk) {
+        int I = (int)((sqrt(8.0 * (double)blk + 1.0) - 1.0) * 0.5);
+        while ((I + 1) * (I + 2) / 2 <= blk) ++I;
+        while (I * (I + 1) / 2 > blk) --I;
+        const int J = blk - I * (I + 1) / 2;
+        for (int e = lane; e < 36; e += 32) {
+            const int r = e / 6, c = e - 6 * r;
+            L.A[(size_t)(6 * I + r) * L.ld + 6 * J + c] = P.S_blk[36 * (size_t)blk + e];
+        }
+    } else if (blk < nblk + P.n_cams) {
+        const int c = blk - nblk;
+        const int f = P.cam_free[c];
+        if (f >= 0 && lane < 6) L.A[(size_t)L.n * L.ld + 6 * f + lane] = P.bs[6 * (size_t)c + lane];
+    }
+}
+
+__global__ void __launch_bounds__(128) k_chol_panel(LargeSolve L, int j0)
+{
+    __shared__ double D[kNB][kNB + 1];
+    __shared__ int s_fail;
+    const int tid = threadIdx.x;
+    const int nb = min(kNB, L.n - j0);
+    if (tid == 0) s_fail = 0;
+    for (int idx = tid; idx < nb * nb; idx += blockDim.x) {
+        const int r = idx / nb, c = idx - r * nb;
+        D[r][c] = c <= r ? L.A[(size_t)(j0 + r) * L.ld + j0 + c] : 0.0;
+    }
+    __syncthreads();
+    for (int j = 0; j < nb; ++j) {
+        if (tid == 0) {
+            const double d = D[j][j];
+            if (!(d > 0.0) || !isfinite(d)) s_fail = 1;
+            D[j][j] = sqrt(d);
+        }
+        __syncthreads();
+        if (s_fail) break;
+        if (tid > j && tid < nb) D[tid][j] /= D[j][j];
+        __syncthreads();
+        for (int idx = tid; idx < nb * nb; idx += blockDim.x) {
+            const int r = idx / nb, c = idx - r * nb;
+            if (c > j && r >= c) D[r][c] -= D[r][j] * D[c][j];
+        }
+        __syncthreads();
+    }
+    if (s_fail) {
+        if (blockIdx.x == 0 && tid == 0) *L.fail = 1;
+        return;
+    }
+    if (blockIdx.x == 0) { // not into A: the other CTAs may still be reading the unfactorised block
+        double* dd = L.Dd + (size_t)(j0 / kNB) * kNB * kNB;
+        for (int idx = tid; idx < nb * nb; idx += blockDim.x) {
+            const int r = idx / nb, c = idx - r * nb;
+            dd[r * kNB + c] = D[r][c];
+        }
+    }
+    // rows below the diagonal block (including the rhs row n): X L^T = A  ->  one thread per row
+    const int row = j0 + nb + blockIdx.x * blockDim.x + tid;
+    if (row > L.n) return;
+    double* a = L.A + (size_t)row * L.ld + j0;
+    double x[kNB];
+#pragma unroll
+    for (int c = 0; c < kNB; ++c) x[c] = c < nb ? a[c] : 0.0;
+#pragma unroll
+    for (int c = 0; c < kNB; ++c) {
+        if (c < nb) {
+            double s = x[c];
+#pragma unroll
+            for (int k = 0; k < kNB; ++k)
+                if (k < c) s -= x[k] * D[c][k];
+            x[c] = s / D[c][c];
+        }
+    }
+#pragma unroll
+    for (int c = 0; c < kNB; ++c)
+        if (c < nb) a[c] = x[c];
+}
+
+// trailing update: A[i][l] -= sum_k P[i][k] P[l][k] over 64x64 tiles of the lower triangle
+__global__ void __launch_bounds__(256) k_chol_trail(LargeSolve L, int j0, int nb)
+{
+    __shared__ double Pi[64][kNB + 1];
+    __shared__ double Pl[64][kNB + 1];
+    if (*L.fail) return;
+    // decode the tile (ti >= tl) from the linear block index
+    const int t = blockIdx.x;
+    int ti = (int)((sqrt(8.0 * (double)t + 1.0) - 1.0) * 0.5);
+    while ((ti + 1) * (ti + 2) / 2 <= t) ++ti;
+    while (ti * (ti + 1) / 2 > t) --ti;
+    const int tl = t - ti * (ti + 1) / 2;
+    const int base = j0 + nb;
+    const int i0 = base + 64 * ti, l0 = base + 64 * tl;
+    const int tid = threadIdx.x;
+    for (int idx = tid; idx < 64 * kNB; idx += 256) {
+        const int r = idx / kNB, c = idx - r * kNB;
+        Pi[r][c] = (i0 + r <= L.n && c < nb) ? L.A[(size_t)(i0 + r) * L.ld + j0 + c] : 0.0;
+        Pl[r][c] = (l0 + r < L.n && c < nb) ? L.A[(size_t)(l0 + r) * L.ld + j0 + c] : 0.0;
+    }
+    __syncthreads();
+    const int tr = tid / 16, tc = tid % 16; // 16 x 16 threads, 4 x 4 each
+    double acc[4][4] = {};
+#pragma unroll 8
+    for (int k = 0; k < kNB; ++k) {
+        double a[4], b[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) a[i] = Pi[tr + 16 * i][k];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) b[i] = Pl[tc + 16 * i][k];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) acc[i][j] += a[i] * b[j];
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int r = i0 + tr + 16 * i, c = l0 + tc + 16 * j;
+            if (r <= L.n && c < L.n && c <= r) L.A[(size_t)r * L.ld + c] -= acc[i][j];
+        }
+}
+
+// L^T x = y with one CTA: y (row n) is staged in shared memory, rows of L are read contiguously
+__global__ void __launch_bounds__(1024) k_back_substitute(LargeSolve L)
+{
+    extern __shared__ double y[];
+    __shared__ double xb[kNB];
+    const int tid = threadIdx.x;
+    const int n = L.n;
+    if (*L.fail) return;
+    for (int i = tid; i < n; i += blockDim.x) y[i] = L.A[(size_t)n * L.ld + i];
+    __syncthreads();
+    for (int jb = ((n - 1) / kNB) * kNB; jb >= 0; jb -= kNB) {
+        const int nb = min(kNB, n - jb);
+        if (tid < 32) { // solve the nb x nb diagonal block with one warp
+            const double* dd = L.Dd + (size_t)(jb / kNB) * kNB * kNB;
+            for (int j = nb - 1; j >= 0; --j) {
+                const double xj = y[jb + j] / dd[j * kNB + j];
+                __syncwarp();
+                if (tid == 0) xb[j] = xj, y[jb + j] = xj;
+                if (tid < j) y[jb + tid] -= dd[j * kNB + tid] * xj;
+                __syncwarp();
+            }
+        }
+        __syncthreads();
+        for (int i = tid; i < jb; i += blockDim.x) {
+            double s = 0.0;
+            for (int j = 0; j < nb; ++j) s += L.A[(size_t)(jb + j) * L.ld + i] * xb[j];
+            y[i] -= s;
+        }
+        __syncthreads();
+    }
+    for (int i = tid; i < n; i += blockDim.x) L.x[i] = y[i];
+}
+
+__global__ void __launch_bounds__(256) k_large_finish(DevProblem P, LargeSolve L)
+{
+    __shared__ double sh[256];
+    LmState& st = P.lm[0];
+    if (!st.active) return;
+    const int fail = *L.fail;
+    const int cur = st.cur, cand = cur ^ 1;
+    const int tid = threadIdx.x;
+    for (int c = tid; c < P.n_cams; c += blockDim.x) {
+        const int f = P.cam_free[c];
+        double d[6];
+        for (int r = 0; r < 6; ++r) d[r] = (f >= 0 && !fail) ? L.x[6 * f + r] : 0.0;
+        for (int r = 0; r < 6; ++r) P.dp[6 * (size_t)c + r] = d[r];
+        const double* pc = P.pose[cur] + 7 * (size_t)c;
+        double* pn = P.pose[cand] + 7 * (size_t)c;
+        if (f >= 0 && !fail) pose_oplus(d, pc, pn);
+        else
+            for (int r = 0; r < 7; ++r) pn[r] = pc[r];
+        write_cam_rt(pn, P.cam_rt[cand] + 12 * (size_t)c);
+    }
+    double ss = 0.0;
+    if (!fail)
+        for (int i = tid; i < L.n; i += blockDim.x) ss += L.x[i] * L.x[i];
+    sh[tid] = ss;
+    __syncthreads();
+    for (int s = 128; s > 0; s >>= 1) {
+        if (tid < s) sh[tid] += sh[tid + s];
+        __syncthreads();
+    }
+    if (tid == 0) {
+        st.dp_sq = sh[0];
+        st.ok2 = fail ? 0 : 1;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// K4 update: one thread per point.  Back substitution through the stored records,
+//   d_l = L^-T (zb - sum_a G_a^T Jp_a d_p),   P' = P + d_l,
+// the point's share of g2o's computeScale  sum_j x_j (lambda x_j + b_j), and the robust
+// cost of the candidate state (K5 fused: the new point never leaves registers).
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) k_update(DevProblem P)
+{
+    const int p = P.pt_begin + blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= P.pt_end) return;
+    const int prob = P.pt_prob[p];
+    const LmState& st = P.lm[prob];
+    if (!st.active) return;
+    const int cur = st.cur, cand = cur ^ 1;
+    const double lambda = st.lambda;
+    const double* info = P.ptinfo + kPtInfoDoubles * (size_t)p;
+    const double i00 = info[0], i10 = info[1], i11 = info[2], i20 = info[3], i21 = info[4], i22 = info[5];
+    const double z0 = info[6], z1 = info[7], z2 = info[8];
+    double y0 = z0, y1 = z1, y2 = z2, sc = 0.0;
+    const int s0 = P.pt_ptr[p], s1 = P.pt_ptr[p + 1];
+    for (int s = s0; s < s1; ++s) {
+        const int cam = __ldg(P.obs_cam + s);
+        const double2* __restrict__ r = reinterpret_cast<const double2*>(P.rec + kRecDoubles * (size_t)s);
+        const double2 r0 = r[0], r1 = r[1], r2 = r[2], r3 = r[3], r4 = r[4], r5 = r[5];
+        const double* __restrict__ d = P.dp + 6 * (size_t)cam;
+        double ja0[6], ja1[6];
+        jtilde(r0.x, r0.y, r1.x, ja0, ja1);
+        double t0 = 0.0, t1 = 0.0;
+#pragma unroll
+        for (int k = 0; k < 6; ++k) {
+            const double dk = d[k];
+            t0 += ja0[k] * dk;
+            t1 += ja1[k] * dk;
+        }
+        // G~ = (r2.x r2.y r3.x ; r3.y r4.x r4.y)
+        y0 -= r2.x * t0 + r3.y * t1;
+        y1 -= r2.y * t0 + r4.x * t1;
+        y2 -= r3.x * t0 + r4.y * t1;
+        // pose part of computeScale: d_p . b_p = -sum t~ . (F w r),  F w r = v~ - G~ zb
+        const double wr0 = r5.x - (r2.x * z0 + r2.y * z1 + r3.x * z2);
+        const double wr1 = r5.y - (r3.y * z0 + r4.x * z1 + r4.y * z2);
+        sc -= t0 * wr0 + t1 * wr1;
+    }
+    const double d0 = i00 * y0 + i10 * y1 + i20 * y2;
+    const double d1 = i11 * y1 + i21 * y2;
+    const double d2 = i22 * y2;
+    sc += y0 * z0 + y1 * z1 + y2 * z2 + lambda * (d0 * d0 + d1 * d1 + d2 * d2);
+    const double* pt = P.pts[cur] + 3 * (size_t)p;
+    const double X = pt[0] + d0, Y = pt[1] + d1, Z = pt[2] + d2;
+    double* pn = P.pts[cand] + 3 * (size_t)p;
+    pn[0] = X, pn[1] = Y, pn[2] = Z;
+    const double* __restrict__ cam_rt = P.cam_rt[cand];
+    double cost = 0.0;
+    for (int s = s0; s < s1; ++s) {
+        const double* __restrict__ rt = cam_rt + 12 * (size_t)__ldg(P.obs_cam + s);
+        const float2 uv = __ldg(P.obs_uv + s);
+        const double x = rt[0] * X + rt[1] * Y + rt[2] * Z + rt[9];
+        const double y = rt[3] * X + rt[4] * Y + rt[5] * Z + rt[10];
+        const double z = rt[6] * X + rt[7] * Y + rt[8] * Z + rt[11];
+        const double iz = 1.0 / z;
+        const double ru = P.fx * (x * iz) + P.cx - (double)uv.x;
+        const double rv = P.fy * (y * iz) + P.cy - (double)uv.y;
+        double w;
+        cost += huber_rho(ru * ru + rv * rv, P.huber_delta, w);
+    }
+    P.cost_new_pt[p] = cost;
+    P.scale_pt[p] = sc;
+}
+
+// ------------------------------------------------------------------------------------------
+// LM decision, one thread per problem: g2o OptimizationAlgorithmLevenberg::solve, the part
+// after the candidate has been evaluated.  Accepting flips `cur`; rejecting leaves the state.
+// ------------------------------------------------------------------------------------------
+__global__ void k_decide(DevProblem P)
+{
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= P.n_problems) return;
+    LmState& s = P.lm[b];
+    if (!s.active) return;
+    if (s.q == 0) {
+        s.chi_start = s.chi;
+        s.accepted = 0;
+    }
+    double chi_new = P.prob_sums[2 * (size_t)b];
+    if (!s.ok2) chi_new = DBL_MAX;
+    const double scale = P.prob_sums[2 * (size_t)b + 1] + s.lambda * s.dp_sq + 1e-3;
+    const double rho = (s.chi - chi_new) / scale;
+    s.rho = rho;
+    bool lambda_bad = false;
+    if (rho > 0.0 && isfinite(chi_new)) {
+        double alpha = 1.0 - (2.0 * rho - 1.0) * (2.0 * rho - 1.0) * (2.0 * rho - 1.0);
+        alpha = fmin(alpha, 2.0 / 3.0);
+        s.lambda *= fmax(1.0 / 3.0, alpha);
+        s.nu = 2.0;
+        s.chi = chi_new;
+        s.cur ^= 1;
+        s.accepted = 1;
+    } else {
+        s.lambda *= s.nu;
+        s.nu *= 2.0;
+        if (!isfinite(s.lambda)) lambda_bad = true;
+    }
+    s.q += 1;
+    s.trials += 1;
+    if (!lambda_bad && rho < 0.0 && s.q < s.max_trials) return; // another trial, same iteration
+    if (P.iter_stats && b == 0) {
+        IterStat& r = P.iter_stats[s.it];
+        r.cost_before = s.chi_start;
+        r.cost_after = s.chi;
+        r.lambda = s.lambda;
+        r.trials = s.q;
+        r.accepted = s.accepted;
+    }
+    const bool term = (s.q == s.max_trials) || rho == 0.0 || lambda_bad;
+    s.it += 1;
+    s.q = 0;
+    if (term) s.terminated = 1;
+    if (term || s.it >= s.target_it) {
+        s.active = 0;
+        atomicSub(P.n_active, 1);
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// launchers
+// ------------------------------------------------------------------------------------------
+static inline int cdiv(long long a, long long b) { return (int)((a + b - 1) / b); }
+
+int launch_state_init(const DevProblem& P, int iterations, int max_trials, double lambda_init, cudaStream_t st)
+{
+    k_state_init<<<cdiv(P.n_problems, 128), 128, 0, st>>>(P, iterations, max_trials, lambda_init);
+    return 1;
+}
+
+int launch_cam_rt(const DevProblem& P, int which, cudaStream_t st)
+{
+    k_cam_rt<<<cdiv(P.n_cams, 128), 128, 0, st>>>(P, which);
+    return 1;
+}
+
+int launch_linearize(const DevProblem& P, int init_pass, double lambda_override, cudaStream_t st)
+{
+    const int np = P.pt_end - P.pt_begin;
+    if (np <= 0) return 0;
+    k_linearize<<<cdiv(np, 128), 128, 0, st>>>(P, init_pass, lambda_override);
+    return 1;
+}
+
+int launch_eval_cost(const DevProblem& P, cudaStream_t st)
+{
+    const int np = P.pt_end - P.pt_begin;
+    if (np <= 0) return 0;
+    k_eval_cost<<<cdiv(np, 128), 128, 0, st>>>(P);
+    return 1;
+}
+
+int launch_schur_blocks(const DevProblem& P, int diag_only, cudaStream_t st)
+{
+    const long long warps = diag_only ? P.n_diag_items : P.n_items;
+    if (warps <= 0) return 0;
+    k_schur_blocks<<<cdiv(warps * 32, 128), 128, 0, st>>>(P, diag_only);
+    return 1;
+}
+
+int launch_block_finalize(const DevProblem& P, int init_pass, double lambda_override, cudaStream_t st)
+{
+    if (P.n_blocks <= 0) return 0;
+    k_block_finalize<<<cdiv((long long)P.n_blocks * 32, 128), 128, 0, st>>>(P, init_pass, lambda_override);
+    return 1;
+}
+
+int launch_reduce(const DevProblem& P, int which, cudaStream_t st)
+{
+    int n = 0;
+    if (P.n_chunks > 0) {
+        k_chunk_reduce<<<P.n_chunks, 256, 0, st>>>(P, which);
+        ++n;
+    }
+    k_prob_sums<<<cdiv(P.n_problems, 128), 128, 0, st>>>(P, which);
+    return n + 1;
+}
+
+int launch_lm_init(const DevProblem& P, double tau, double lambda_init, cudaStream_t st)
+{
+    k_lm_init<<<cdiv(P.n_problems, 128), 128, 0, st>>>(P, tau, lambda_init);
+    return 1;
+}
+
+int launch_solve_small(const DevProblem& P, int max_n, cudaStream_t st)
+{
+    const int ld = (max_n + 1) | 1;
+    const size_t smem = sizeof(double) * (size_t)(max_n + 1) * (size_t)ld;
+    static size_t configured = 0;
+    if (smem > 48 * 1024 && smem > configured) {
+        cudaFuncSetAttribute(k_solve_small, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        configured = smem;
+    }
+    k_solve_small<<<P.n_problems, 256, smem, st>>>(P);
+    return 1;
+}
+
+int launch_solve_large(const DevProblem& P, const LargeSolve& L, cudaStream_t st)
+{
+    int launches = 0;
+    const int nf = L.n / 6;
+    const long long warps = (long long)nf * (nf + 1) / 2 + P.n_cams;
+    k_dense_assemble<<<cdiv(warps * 32, 256), 256, 0, st>>>(P, L);
+    ++launches;
+    for (int j0 = 0; j0 < L.n; j0 += kNB) {
+        const int nb = L.n - j0 < kNB ? L.n - j0 : kNB;
+        const int rows_below = L.n + 1 - (j0 + nb); // includes the rhs row
+        k_chol_panel<<<rows_below > 0 ? cdiv(rows_below, 128) : 1, 128, 0, st>>>(L, j0);
+        ++launches;
+        if (rows_below > 0) {
+            const int tiles = cdiv(rows_below, 64);
+            k_chol_trail<<<tiles * (tiles + 1) / 2, 256, 0, st>>>(L, j0, nb);
+            ++launches;
+        }
+    }
+    static bool configured = false;
+    const size_t smem = sizeof(double) * (size_t)L.n;
+    if (!configured) {
+        cudaFuncSetAttribute(k_back_substitute, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        configured = true;
+    }
+    k_back_substitute<<<1, 1024, smem, st>>>(L);
+    k_large_finish<<<1, 256, 0, st>>>(P, L);
+    return launches + 2;
+}
+
+int launch_update(const DevProblem& P, cudaStream_t st)
+{
+    const int np = P.pt_end - P.pt_begin;
+    if (np <= 0) return 0;
+    k_update<<<cdiv(np, 128), 128, 0, st>>>(P);
+    return 1;
+}
+
+int launch_decide(const DevProblem& P, cudaStream_t st)
+{
+    k_decide<<<cdiv(P.n_problems, 128), 128, 0, st>>>(P);
+    return 1;
+}
+
+} // namespace visoba
