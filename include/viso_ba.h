@@ -61,6 +61,9 @@ typedef struct {
     double lm_lambda_init; /* > 0 overrides tau rule                                    */
     int32_t lm_max_trials; /* g2o maxTrialsAfterFailure, default 10                     */
     int32_t verbose;       /* reference: optimizer_.setVerbose(true) (:120); default 0  */
+    int32_t fix_first_pose;/* gauge: fix the first pose of every problem (viso keeps frame 0
+                              at identity, keyframe.h:34-35); default 1                  */
+    int32_t use_cuda_graph;/* replay one captured LM trial instead of re-launching; default 1 */
 } viso_ba_config;
 
 /* per outer LM iteration (single-problem handles) */

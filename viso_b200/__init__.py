@@ -1,0 +1,9 @@
+"""viso_b200 — B200-native bundle-adjustment backend behind viso's `bundle_adjuster.h` surface.
+
+Only what the hot path needs lives here: csrc/ (CUDA kernels + the C ABI of
+include/viso_ba.h) and api.py (ctypes binding + the Python mirror of the reference class).
+"""
+from .api import (  # noqa: F401
+    BundleAdjuster, Config, IterStats, KernelTime, Summary, SynthSpec, VisoBaError, LIB_PATH, SYMBOLS,
+    batch_problems, default_config, load_library, nccl_unique_id, synth_config, synth_preset, synth_problem,
+)

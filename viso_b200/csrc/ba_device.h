@@ -110,7 +110,8 @@ struct LargeSolve { // dense path for one problem with n > kSmallMaxN
 // launchers (all asynchronous on `st`); each returns the number of kernels it launched
 int launch_state_init(const DevProblem& P, int iterations, int max_trials, double lambda_init,
                       cudaStream_t st);
-int launch_cam_rt(const DevProblem& P, int which, cudaStream_t st); // R|t of all poses of buffer
+int launch_cam_rt(const DevProblem& P, int which, cudaStream_t st); // R|t of all poses of buffer `which` (< 0: each problem's current)
+int launch_gather_current(const DevProblem& P, double* poses_out, double* pts_out, cudaStream_t st);
 int launch_linearize(const DevProblem& P, int init_pass, double lambda_override, cudaStream_t st);
 int launch_schur_blocks(const DevProblem& P, int diag_only, cudaStream_t st);
 int launch_block_finalize(const DevProblem& P, int init_pass, double lambda_override, cudaStream_t st);

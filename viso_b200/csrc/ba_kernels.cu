@@ -140,7 +140,23 @@ __global__ void k_cam_rt(DevProblem P, int which)
 {
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= P.n_cams) return;
+    if (which < 0) which = P.lm[P.cam_prob[c]].cur; // the current buffer of the camera's problem
     write_cam_rt(P.pose[which] + 7 * (size_t)c, P.cam_rt[which] + 12 * (size_t)c);
+}
+
+// read-back: current poses / points of every problem into one contiguous buffer each
+__global__ void k_gather_current(DevProblem P, double* __restrict__ poses_out, double* __restrict__ pts_out)
+{
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long long n_pose = 7ll * P.n_cams, n_pt = 3ll * P.n_points;
+    if (i < n_pose) {
+        const int c = (int)(i / 7);
+        poses_out[i] = P.pose[P.lm[P.cam_prob[c]].cur][i];
+    } else if (i < n_pose + n_pt) {
+        const long long j = i - n_pose;
+        const int p = (int)(j / 3);
+        pts_out[j] = P.pts[P.lm[P.pt_prob[p]].cur][j];
+    }
 }
 
 // ------------------------------------------------------------------------------------------
@@ -932,6 +948,14 @@ int launch_state_init(const DevProblem& P, int iterations, int max_trials, doubl
 int launch_cam_rt(const DevProblem& P, int which, cudaStream_t st)
 {
     k_cam_rt<<<cdiv(P.n_cams, 128), 128, 0, st>>>(P, which);
+    return 1;
+}
+
+int launch_gather_current(const DevProblem& P, double* poses_out, double* pts_out, cudaStream_t st)
+{
+    const long long n = 7ll * P.n_cams + 3ll * P.n_points;
+    if (n <= 0) return 0;
+    k_gather_current<<<cdiv(n, 256), 256, 0, st>>>(P, poses_out, pts_out);
     return 1;
 }
 

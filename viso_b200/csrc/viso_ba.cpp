@@ -1,0 +1,1255 @@
+// viso_ba.cpp — host side of the C ABI declared in include/viso_ba.h.
+//
+// Replaces the header-only g2o wrapper of the reference (include/bundle_adjuster.h:108-187):
+// the pools the reference pre-allocates in its constructor (:122-166) become one device arena
+// that is kept across Clear()/SetProblem(); graph construction (addVertex/addEdge) becomes the
+// structure build in upload(); optimizer_.optimize() — never reached in the reference —
+// becomes the LM driver in run_lm().  No CPU compute path exists here: every numeric result
+// comes from the kernels in ba_kernels.cu (there is deliberately no fallback).
+#include "../../include/viso_ba.h"
+#include "ba_device.h"
+
+#include <cuda_runtime.h>
+#include <dlfcn.h>
+
+#include <algorithm>
+#include <chrono>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <new>
+#include <string>
+#include <vector>
+
+using namespace visoba;
+
+namespace {
+
+// ------------------------------------------------------------------------------------------
+// NCCL through dlopen: the library must load (and every single-GPU path must work) on a box
+// without NCCL; only viso_ba_shard_init needs it.
+// ------------------------------------------------------------------------------------------
+struct Id128 { // ncclUniqueId, passed by value
+    char b[128];
+};
+struct NcclApi {
+    void* lib = nullptr;
+    int (*GetUniqueId)(void*) = nullptr;
+    int (*CommInitRank)(void**, int, Id128, int) = nullptr;
+    int (*AllReduce)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+    int (*Broadcast)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+    int (*GroupStart)() = nullptr;
+    int (*GroupEnd)() = nullptr;
+    int (*CommDestroy)(void*) = nullptr;
+    const char* (*GetErrorString)(int) = nullptr;
+};
+constexpr int kNcclDouble = 8; // ncclFloat64
+constexpr int kNcclSum = 0, kNcclMax = 2;
+
+NcclApi* nccl_api()
+{
+    static NcclApi api;
+    static bool tried = false;
+    if (tried) return api.lib ? &api : nullptr;
+    tried = true;
+    const char* names[] = { "libnccl.so.2", "libnccl.so" };
+    for (const char* n : names) {
+        api.lib = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+        if (api.lib) break;
+    }
+    if (!api.lib) return nullptr;
+#define VISO_SYM(field, name)                                                   \
+    *(void**)(&api.field) = dlsym(api.lib, name);                               \
+    if (!api.field) {                                                           \
+        api.lib = nullptr;                                                      \
+        return nullptr;                                                         \
+    }
+    VISO_SYM(GetUniqueId, "ncclGetUniqueId")
+    VISO_SYM(CommInitRank, "ncclCommInitRank")
+    VISO_SYM(AllReduce, "ncclAllReduce")
+    VISO_SYM(Broadcast, "ncclBroadcast")
+    VISO_SYM(GroupStart, "ncclGroupStart")
+    VISO_SYM(GroupEnd, "ncclGroupEnd")
+    VISO_SYM(CommDestroy, "ncclCommDestroy")
+    VISO_SYM(GetErrorString, "ncclGetErrorString")
+#undef VISO_SYM
+    return &api;
+}
+
+// ------------------------------------------------------------------------------------------
+// device arena: one allocation, bump-pointer sub-allocation, kept while it is large enough
+// (the reference's "allocate the pools once in the constructor", bundle_adjuster.h:122-166)
+// ------------------------------------------------------------------------------------------
+struct Arena {
+    char* base = nullptr;
+    size_t cap = 0, used = 0;
+    template <typename T> T* take(size_t count)
+    {
+        const size_t bytes = (count * sizeof(T) + 255) & ~(size_t)255;
+        T* p = reinterpret_cast<T*>(base ? base + used : nullptr);
+        used += bytes;
+        return p;
+    }
+};
+
+struct KernelAcc {
+    int64_t launches = 0;
+    double ms = 0.0;
+};
+
+struct PendingEvent {
+    std::string name;
+    cudaEvent_t a, b;
+    int n;
+};
+
+double now_ms()
+{
+    using namespace std::chrono;
+    return duration<double, std::milli>(steady_clock::now().time_since_epoch()).count();
+}
+
+} // namespace
+
+struct viso_ba {
+    viso_ba_config cfg;
+    std::string err;
+    // ---- host staging (what AddPoint / AddPose / AddEdge append to) ----
+    std::vector<double> poses, points;
+    std::vector<int32_t> e_pose, e_point;
+    std::vector<float> e_uv;
+    std::vector<int8_t> fixed; // -1 default policy, 0 free, 1 fixed
+    std::vector<int64_t> pose_off, point_off, edge_off; // batched: B+1 entries, else empty
+    int64_t n_problems = 1;
+    // ---- device ----
+    bool cuda_ok = false;
+    bool uploaded = false;
+    cudaStream_t own_stream = nullptr, stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    Arena arena;
+    DevProblem P;
+    LargeSolve L;
+    bool use_large = false;
+    int max_n = 0; // largest reduced system over the problems
+    double *d_pose_init = nullptr, *d_pts_init = nullptr, *d_pose_out = nullptr, *d_pts_out = nullptr;
+    double* d_allreduce = nullptr; // S_blk | bs   (contiguous)
+    size_t allreduce_count = 0;
+    // pinned host mirrors
+    void* pin = nullptr;
+    size_t pin_cap = 0;
+    std::vector<LmState> lm_host;
+    float setup_ms = 0.f;
+    // ---- sharding ----
+    int rank = 0, n_ranks = 1;
+    void* comm = nullptr;
+    std::vector<int32_t> shard_pt; // n_ranks+1 point boundaries
+    // ---- accounting ----
+    int64_t launches = 0;
+    bool timing = false;
+    std::map<std::string, KernelAcc> ktimes;
+    std::vector<PendingEvent> pending;
+    // ---- CUDA graph of one LM trial ----
+    cudaGraphExec_t trial_graph = nullptr;
+    int trial_graph_launches = 0;
+
+    viso_ba() { std::memset(&P, 0, sizeof(P)), std::memset(&L, 0, sizeof(L)); }
+};
+
+namespace {
+
+int32_t fail(viso_ba* h, int32_t code, const char* fmt, ...)
+{
+    if (h) {
+        char buf[512];
+        va_list ap;
+        va_start(ap, fmt);
+        vsnprintf(buf, sizeof(buf), fmt, ap);
+        va_end(ap);
+        h->err = buf;
+        if (h->cfg.verbose) fprintf(stderr, "[viso_ba] %s\n", buf);
+    }
+    return code;
+}
+
+#define CU(call)                                                                                \
+    do {                                                                                        \
+        cudaError_t e_ = (call);                                                                \
+        if (e_ != cudaSuccess)                                                                  \
+            return fail(h, VISO_BA_ERR_CUDA, "%s: %s (%s:%d)", #call, cudaGetErrorString(e_),   \
+                __FILE__, __LINE__);                                                            \
+    } while (0)
+
+#define NC(call)                                                                                \
+    do {                                                                                        \
+        int e_ = (call);                                                                        \
+        if (e_ != 0)                                                                            \
+            return fail(h, VISO_BA_ERR_NCCL, "%s: %s", #call, nccl_api()->GetErrorString(e_));  \
+    } while (0)
+
+void drop_graph(viso_ba* h)
+{
+    if (h->trial_graph) {
+        cudaGraphExecDestroy(h->trial_graph);
+        h->trial_graph = nullptr;
+    }
+}
+
+int32_t ensure_cuda(viso_ba* h)
+{
+    if (h->cuda_ok) {
+        CU(cudaSetDevice(h->cfg.device));
+        return VISO_BA_OK;
+    }
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n <= 0)
+        return fail(h, VISO_BA_ERR_CUDA, "no CUDA device usable (%s); this backend has no CPU fallback",
+            e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
+    if (h->cfg.device < 0 || h->cfg.device >= n)
+        return fail(h, VISO_BA_ERR_CUDA, "device %d out of range (%d devices)", h->cfg.device, n);
+    CU(cudaSetDevice(h->cfg.device));
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, h->cfg.device));
+    if (prop.major != 10)
+        return fail(h, VISO_BA_ERR_CUDA, "device %d is sm_%d%d; the kernels are built for sm_100a only",
+            h->cfg.device, prop.major, prop.minor);
+    CU(cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking));
+    if (!h->stream) h->stream = h->own_stream;
+    CU(cudaEventCreate(&h->ev0));
+    CU(cudaEventCreate(&h->ev1));
+    h->cuda_ok = true;
+    return VISO_BA_OK;
+}
+
+// run one launcher, count its kernels and (optionally) time it with CUDA events
+template <typename F> inline void run_k(viso_ba* h, const char* name, F&& f)
+{
+    if (h->timing) {
+        PendingEvent pe;
+        pe.name = name;
+        cudaEventCreate(&pe.a);
+        cudaEventCreate(&pe.b);
+        cudaEventRecord(pe.a, h->stream);
+        pe.n = f();
+        cudaEventRecord(pe.b, h->stream);
+        h->launches += pe.n;
+        h->pending.push_back(pe);
+    } else {
+        h->launches += f();
+    }
+}
+
+void resolve_timing(viso_ba* h)
+{
+    for (auto& pe : h->pending) {
+        float ms = 0.f;
+        cudaEventSynchronize(pe.b);
+        cudaEventElapsedTime(&ms, pe.a, pe.b);
+        KernelAcc& k = h->ktimes[pe.name];
+        k.launches += pe.n;
+        k.ms += ms;
+        cudaEventDestroy(pe.a);
+        cudaEventDestroy(pe.b);
+    }
+    h->pending.clear();
+}
+
+} // namespace
+
+// ==========================================================================================
+// C ABI: lifetime, staging
+// ==========================================================================================
+extern "C" int32_t viso_ba_version(void) { return VISO_BA_VERSION; }
+
+extern "C" const char* viso_ba_status_string(int32_t s)
+{
+    switch (s) {
+    case VISO_BA_OK: return "ok";
+    case VISO_BA_ERR_CAPACITY: return "capacity exceeded";
+    case VISO_BA_ERR_INDEX: return "index out of range";
+    case VISO_BA_ERR_CUDA: return "CUDA error";
+    case VISO_BA_ERR_NCCL: return "NCCL error";
+    case VISO_BA_ERR_NONFINITE: return "non-finite input";
+    case VISO_BA_ERR_ARG: return "bad argument";
+    case VISO_BA_ERR_STATE: return "invalid state";
+    case VISO_BA_ERR_UNSUPPORTED: return "unsupported";
+    default: return "unknown status";
+    }
+}
+
+extern "C" void viso_ba_default_config(viso_ba_config* c)
+{
+    if (!c) return;
+    std::memset(c, 0, sizeof(*c));
+    c->struct_size = (int32_t)sizeof(*c);
+    c->device = 0;
+    c->max_points = 1000; // bundle_adjuster.h:182-184
+    c->max_poses = 1000;
+    c->max_edges = 1000;
+    c->fx = 517.3; // src/main.cpp:14-17
+    c->fy = 516.5;
+    c->cx = 325.1;
+    c->cy = 249.7;
+    c->huber_delta = 0.0; // the reference sets no robust kernel (bundle_adjuster.h:160)
+    c->lm_tau = 1e-5;
+    c->lm_lambda_init = 0.0;
+    c->lm_max_trials = 10;
+    c->verbose = 0;
+    c->fix_first_pose = 1;
+    c->use_cuda_graph = 1;
+}
+
+extern "C" int32_t viso_ba_create(const viso_ba_config* cfg, viso_ba** out)
+{
+    if (!out) return VISO_BA_ERR_ARG;
+    *out = nullptr;
+    viso_ba_config c;
+    viso_ba_default_config(&c);
+    if (cfg) {
+        if (cfg->struct_size != (int32_t)sizeof(viso_ba_config)) return VISO_BA_ERR_ARG;
+        c = *cfg;
+    }
+    if (c.max_points < 0 || c.max_poses < 0 || c.max_edges < 0) return VISO_BA_ERR_ARG;
+    if (c.max_points > 0x7fffffff || c.max_poses > 0x7fffffff || c.max_edges > 0x7fffffff)
+        return VISO_BA_ERR_UNSUPPORTED;
+    if (c.lm_max_trials < 1) c.lm_max_trials = 1;
+    viso_ba* h = new (std::nothrow) viso_ba();
+    if (!h) return VISO_BA_ERR_CAPACITY;
+    h->cfg = c;
+    // CUDA is initialised lazily (first upload) so that staging-only use and the
+    // "library loads and exports its symbols" check need no GPU.
+    *out = h;
+    return VISO_BA_OK;
+}
+
+extern "C" void viso_ba_destroy(viso_ba* h)
+{
+    if (!h) return;
+    if (h->cuda_ok) {
+        cudaSetDevice(h->cfg.device);
+        cudaStreamSynchronize(h->stream);
+        drop_graph(h);
+        resolve_timing(h);
+        if (h->comm && nccl_api()) nccl_api()->CommDestroy(h->comm);
+        if (h->arena.base) cudaFree(h->arena.base);
+        if (h->pin) cudaFreeHost(h->pin);
+        if (h->ev0) cudaEventDestroy(h->ev0);
+        if (h->ev1) cudaEventDestroy(h->ev1);
+        if (h->own_stream) cudaStreamDestroy(h->own_stream);
+    }
+    delete h;
+}
+
+extern "C" const char* viso_ba_last_error(const viso_ba* h) { return h ? h->err.c_str() : "null handle"; }
+
+extern "C" int32_t viso_ba_clear(viso_ba* h)
+{
+    if (!h) return VISO_BA_ERR_ARG;
+    h->poses.clear(), h->points.clear(), h->e_pose.clear(), h->e_point.clear(), h->e_uv.clear();
+    h->fixed.clear();
+    h->pose_off.clear(), h->point_off.clear(), h->edge_off.clear();
+    h->n_problems = 1;
+    h->uploaded = false;
+    drop_graph(h);
+    return VISO_BA_OK;
+}
+
+extern "C" int64_t viso_ba_add_point(viso_ba* h, const double xyz[3])
+{
+    if (!h || !xyz) return -(int64_t)VISO_BA_ERR_ARG;
+    if (!h->pose_off.empty()) return -(int64_t)fail(h, VISO_BA_ERR_STATE, "handle holds a batched problem; clear it first");
+    const int64_t n = (int64_t)h->points.size() / 3;
+    if (n >= h->cfg.max_points) return -(int64_t)fail(h, VISO_BA_ERR_CAPACITY, "point pool full (%lld)", (long long)h->cfg.max_points);
+    for (int i = 0; i < 3; ++i)
+        if (!std::isfinite(xyz[i])) return -(int64_t)fail(h, VISO_BA_ERR_NONFINITE, "point %lld is not finite", (long long)n);
+    h->points.insert(h->points.end(), xyz, xyz + 3);
+    h->uploaded = false;
+    return n;
+}
+
+extern "C" int64_t viso_ba_add_pose(viso_ba* h, const double q[7])
+{
+    if (!h || !q) return -(int64_t)VISO_BA_ERR_ARG;
+    if (!h->pose_off.empty()) return -(int64_t)fail(h, VISO_BA_ERR_STATE, "handle holds a batched problem; clear it first");
+    const int64_t n = (int64_t)h->poses.size() / 7;
+    if (n >= h->cfg.max_poses) return -(int64_t)fail(h, VISO_BA_ERR_CAPACITY, "pose pool full (%lld)", (long long)h->cfg.max_poses);
+    for (int i = 0; i < 7; ++i)
+        if (!std::isfinite(q[i])) return -(int64_t)fail(h, VISO_BA_ERR_NONFINITE, "pose %lld is not finite", (long long)n);
+    const double nn = q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3];
+    if (!(nn > 1e-12)) return -(int64_t)fail(h, VISO_BA_ERR_ARG, "pose %lld has a zero quaternion", (long long)n);
+    h->poses.insert(h->poses.end(), q, q + 7);
+    h->fixed.push_back(-1);
+    h->uploaded = false;
+    return n;
+}
+
+extern "C" int32_t viso_ba_add_edge(viso_ba* h, int64_t point, int64_t pose, float u, float v)
+{
+    if (!h) return VISO_BA_ERR_ARG;
+    if (!h->pose_off.empty()) return fail(h, VISO_BA_ERR_STATE, "handle holds a batched problem; clear it first");
+    if ((int64_t)h->e_pose.size() >= h->cfg.max_edges) return fail(h, VISO_BA_ERR_CAPACITY, "edge pool full (%lld)", (long long)h->cfg.max_edges);
+    if (point < 0 || point >= (int64_t)h->points.size() / 3) return fail(h, VISO_BA_ERR_INDEX, "edge refers to point %lld", (long long)point);
+    if (pose < 0 || pose >= (int64_t)h->poses.size() / 7) return fail(h, VISO_BA_ERR_INDEX, "edge refers to pose %lld", (long long)pose);
+    if (!std::isfinite(u) || !std::isfinite(v)) return fail(h, VISO_BA_ERR_NONFINITE, "edge measurement is not finite");
+    h->e_pose.push_back((int32_t)pose);
+    h->e_point.push_back((int32_t)point);
+    h->e_uv.push_back(u);
+    h->e_uv.push_back(v);
+    h->uploaded = false;
+    return VISO_BA_OK;
+}
+
+namespace {
+int32_t check_finite(viso_ba* h, const double* a, size_t n, const char* what)
+{
+    for (size_t i = 0; i < n; ++i)
+        if (!std::isfinite(a[i])) return fail(h, VISO_BA_ERR_NONFINITE, "%s[%zu] is not finite", what, i);
+    return VISO_BA_OK;
+}
+} // namespace
+
+extern "C" int32_t viso_ba_set_problem_batched(viso_ba* h, int64_t B, const int64_t* pose_off,
+    const int64_t* point_off, const int64_t* edge_off, const double* poses7, const double* points3,
+    const int32_t* edge_pose, const int32_t* edge_point, const float* edge_uv)
+{
+    if (!h || B < 1 || !pose_off || !point_off || !edge_off) return VISO_BA_ERR_ARG;
+    const int64_t Nc = pose_off[B], Np = point_off[B], Ne = edge_off[B];
+    if (pose_off[0] != 0 || point_off[0] != 0 || edge_off[0] != 0) return fail(h, VISO_BA_ERR_ARG, "offset arrays must start at 0");
+    if (Nc < 0 || Np < 0 || Ne < 0) return fail(h, VISO_BA_ERR_ARG, "negative sizes");
+    if ((Nc && !poses7) || (Np && !points3) || (Ne && (!edge_pose || !edge_point || !edge_uv))) return fail(h, VISO_BA_ERR_ARG, "null array");
+    if (Nc > h->cfg.max_poses || Np > h->cfg.max_points || Ne > h->cfg.max_edges)
+        return fail(h, VISO_BA_ERR_CAPACITY, "problem (%lld poses, %lld points, %lld edges) exceeds the pools (%lld, %lld, %lld)",
+            (long long)Nc, (long long)Np, (long long)Ne, (long long)h->cfg.max_poses, (long long)h->cfg.max_points, (long long)h->cfg.max_edges);
+    for (int64_t b = 0; b < B; ++b) {
+        if (pose_off[b + 1] < pose_off[b] || point_off[b + 1] < point_off[b] || edge_off[b + 1] < edge_off[b])
+            return fail(h, VISO_BA_ERR_ARG, "offsets of problem %lld decrease", (long long)b);
+        const int64_t nc = pose_off[b + 1] - pose_off[b], np = point_off[b + 1] - point_off[b];
+        for (int64_t e = edge_off[b]; e < edge_off[b + 1]; ++e) {
+            if (edge_pose[e] < 0 || edge_pose[e] >= nc) return fail(h, VISO_BA_ERR_INDEX, "edge %lld refers to pose %d", (long long)e, edge_pose[e]);
+            if (edge_point[e] < 0 || edge_point[e] >= np) return fail(h, VISO_BA_ERR_INDEX, "edge %lld refers to point %d", (long long)e, edge_point[e]);
+        }
+    }
+    int32_t rc;
+    if ((rc = check_finite(h, poses7, (size_t)Nc * 7, "poses"))) return rc;
+    if ((rc = check_finite(h, points3, (size_t)Np * 3, "points"))) return rc;
+    for (int64_t e = 0; e < 2 * Ne; ++e)
+        if (!std::isfinite(edge_uv[e])) return fail(h, VISO_BA_ERR_NONFINITE, "edge_uv[%lld] is not finite", (long long)e);
+    for (int64_t c = 0; c < Nc; ++c) {
+        const double* q = poses7 + 7 * c;
+        if (!(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3] > 1e-12)) return fail(h, VISO_BA_ERR_ARG, "pose %lld has a zero quaternion", (long long)c);
+    }
+    viso_ba_clear(h);
+    h->poses.assign(poses7, poses7 + 7 * Nc);
+    h->points.assign(points3, points3 + 3 * Np);
+    h->e_uv.assign(edge_uv, edge_uv + 2 * Ne);
+    h->e_pose.resize((size_t)Ne);
+    h->e_point.resize((size_t)Ne);
+    for (int64_t b = 0; b < B; ++b) // store GLOBAL indices
+        for (int64_t e = edge_off[b]; e < edge_off[b + 1]; ++e) {
+            h->e_pose[(size_t)e] = (int32_t)(edge_pose[e] + pose_off[b]);
+            h->e_point[(size_t)e] = (int32_t)(edge_point[e] + point_off[b]);
+        }
+    h->fixed.assign((size_t)Nc, -1);
+    h->n_problems = B;
+    if (B > 1) {
+        h->pose_off.assign(pose_off, pose_off + B + 1);
+        h->point_off.assign(point_off, point_off + B + 1);
+        h->edge_off.assign(edge_off, edge_off + B + 1);
+    }
+    return VISO_BA_OK;
+}
+
+extern "C" int32_t viso_ba_set_problem(viso_ba* h, int64_t n_poses, const double* poses7, int64_t n_points,
+    const double* points3, int64_t n_edges, const int32_t* edge_pose, const int32_t* edge_point, const float* edge_uv)
+{
+    const int64_t po[2] = { 0, n_poses }, pt[2] = { 0, n_points }, eo[2] = { 0, n_edges };
+    return viso_ba_set_problem_batched(h, 1, po, pt, eo, poses7, points3, edge_pose, edge_point, edge_uv);
+}
+
+extern "C" int32_t viso_ba_set_pose_fixed(viso_ba* h, int64_t pose, int32_t fixed)
+{
+    if (!h) return VISO_BA_ERR_ARG;
+    if (pose < 0 || pose >= (int64_t)h->fixed.size()) return fail(h, VISO_BA_ERR_INDEX, "no pose %lld", (long long)pose);
+    h->fixed[(size_t)pose] = fixed ? 1 : 0;
+    h->uploaded = false;
+    return VISO_BA_OK;
+}
+
+extern "C" int32_t viso_ba_set_intrinsics(viso_ba* h, double fx, double fy, double cx, double cy)
+{
+    if (!h) return VISO_BA_ERR_ARG;
+    if (!(fx > 0.0) || !(fy > 0.0) || !std::isfinite(fx) || !std::isfinite(fy) || !std::isfinite(cx) || !std::isfinite(cy))
+        return fail(h, VISO_BA_ERR_ARG, "bad intrinsics");
+    h->cfg.fx = fx, h->cfg.fy = fy, h->cfg.cx = cx, h->cfg.cy = cy;
+    h->P.fx = fx, h->P.fy = fy, h->P.cx = cx, h->P.cy = cy;
+    drop_graph(h);
+    return VISO_BA_OK;
+}
+
+extern "C" int32_t viso_ba_set_huber_delta(viso_ba* h, double delta)
+{
+    if (!h) return VISO_BA_ERR_ARG;
+    if (std::isnan(delta)) return fail(h, VISO_BA_ERR_ARG, "bad huber delta");
+    h->cfg.huber_delta = delta;
+    h->P.huber_delta = delta;
+    drop_graph(h);
+    return VISO_BA_OK;
+}
+
+extern "C" int32_t viso_ba_set_stream(viso_ba* h, void* s)
+{
+    if (!h) return VISO_BA_ERR_ARG;
+    int32_t rc = ensure_cuda(h);
+    if (rc) return rc;
+    h->stream = s ? (cudaStream_t)s : h->own_stream;
+    drop_graph(h);
+    return VISO_BA_OK;
+}
+
+extern "C" int64_t viso_ba_num_points(const viso_ba* h) { return h ? (int64_t)h->points.size() / 3 : -1; }
+extern "C" int64_t viso_ba_num_poses(const viso_ba* h) { return h ? (int64_t)h->poses.size() / 7 : -1; }
+extern "C" int64_t viso_ba_num_edges(const viso_ba* h) { return h ? (int64_t)h->e_pose.size() : -1; }
+extern "C" int64_t viso_ba_num_problems(const viso_ba* h) { return h ? h->n_problems : -1; }
+extern "C" int64_t viso_ba_kernel_launches(const viso_ba* h) { return h ? h->launches : -1; }
+
+// ==========================================================================================
+// structure build: what g2o does in addVertex/addEdge/initializeOptimization
+// (bundle_adjuster.h:122-166) — sort the edges by (point, pose), index the block structure
+// of the reduced camera system and list, for every S block, the observation pairs feeding it.
+// ==========================================================================================
+namespace {
+
+struct Built {
+    std::vector<int32_t> pt_ptr, pt_prob, obs_cam, cam_free, cam_prob, prob_cam0, prob_tri0, prob_nfree;
+    std::vector<float> obs_uv;
+    std::vector<int32_t> pairs;      // 2 per pair
+    std::vector<int32_t> items;      // 4 per item
+    std::vector<int32_t> diag_items, block_item_ptr, block_cam;
+    std::vector<int32_t> chunks;     // 4 per chunk
+    std::vector<int32_t> prob_chunk_ptr;
+    int64_t n_pairs = 0;
+    int32_t n_blocks = 0, max_n = 0;
+};
+
+int32_t build_structure(viso_ba* h, Built& b)
+{
+    const int64_t Nc = (int64_t)h->poses.size() / 7, Np = (int64_t)h->points.size() / 3;
+    const int64_t Ne = (int64_t)h->e_pose.size();
+    const int64_t B = h->n_problems;
+    // ---- problems, gauge, free indices, block offsets ----
+    b.cam_prob.assign((size_t)Nc, 0);
+    b.pt_prob.assign((size_t)Np, 0);
+    b.prob_cam0.assign((size_t)B + 1, 0);
+    std::vector<int64_t> pt0((size_t)B + 1, 0);
+    if (B > 1) {
+        for (int64_t p = 0; p <= B; ++p) b.prob_cam0[(size_t)p] = (int32_t)h->pose_off[(size_t)p], pt0[(size_t)p] = h->point_off[(size_t)p];
+        for (int64_t p = 0; p < B; ++p) {
+            for (int64_t c = h->pose_off[(size_t)p]; c < h->pose_off[(size_t)p + 1]; ++c) b.cam_prob[(size_t)c] = (int32_t)p;
+            for (int64_t q = h->point_off[(size_t)p]; q < h->point_off[(size_t)p + 1]; ++q) b.pt_prob[(size_t)q] = (int32_t)p;
+        }
+    } else {
+        b.prob_cam0[1] = (int32_t)Nc;
+        pt0[1] = Np;
+    }
+    b.cam_free.assign((size_t)Nc, -1);
+    b.prob_nfree.assign((size_t)B, 0);
+    b.prob_tri0.assign((size_t)B + 1, 0);
+    int64_t tri = 0;
+    b.max_n = 0;
+    for (int64_t p = 0; p < B; ++p) {
+        int32_t nf = 0;
+        for (int32_t c = b.prob_cam0[(size_t)p]; c < b.prob_cam0[(size_t)p + 1]; ++c) {
+            int8_t f = h->fixed[(size_t)c];
+            if (f < 0) f = (h->cfg.fix_first_pose && c == b.prob_cam0[(size_t)p]) ? 1 : 0;
+            b.cam_free[(size_t)c] = f ? -1 : nf++;
+        }
+        b.prob_nfree[(size_t)p] = nf;
+        b.prob_tri0[(size_t)p] = (int32_t)tri;
+        tri += (int64_t)nf * (nf + 1) / 2;
+        b.max_n = std::max(b.max_n, 6 * nf);
+        if (tri > 0x7fffffff / 36) return fail(h, VISO_BA_ERR_UNSUPPORTED, "reduced camera system too large (%lld blocks)", (long long)tri);
+    }
+    b.prob_tri0[(size_t)B] = (int32_t)tri;
+    b.n_blocks = (int32_t)tri;
+
+    // ---- stable counting sort by point, then by pose inside each point ----
+    b.pt_ptr.assign((size_t)Np + 1, 0);
+    for (int64_t e = 0; e < Ne; ++e) b.pt_ptr[(size_t)h->e_point[(size_t)e] + 1]++;
+    for (int64_t p = 0; p < Np; ++p) b.pt_ptr[(size_t)p + 1] += b.pt_ptr[(size_t)p];
+    b.obs_cam.resize((size_t)Ne);
+    b.obs_uv.resize((size_t)Ne * 2);
+    {
+        std::vector<int32_t> cur(b.pt_ptr.begin(), b.pt_ptr.end() - 1);
+        for (int64_t e = 0; e < Ne; ++e) {
+            const int32_t s = cur[(size_t)h->e_point[(size_t)e]]++;
+            b.obs_cam[(size_t)s] = h->e_pose[(size_t)e];
+            b.obs_uv[2 * (size_t)s] = h->e_uv[2 * (size_t)e];
+            b.obs_uv[2 * (size_t)s + 1] = h->e_uv[2 * (size_t)e + 1];
+        }
+    }
+    for (int64_t p = 0; p < Np; ++p) { // insertion sort: tracks are short
+        const int32_t s0 = b.pt_ptr[(size_t)p], s1 = b.pt_ptr[(size_t)p + 1];
+        for (int32_t i = s0 + 1; i < s1; ++i) {
+            const int32_t c = b.obs_cam[(size_t)i];
+            const float u = b.obs_uv[2 * (size_t)i], v = b.obs_uv[2 * (size_t)i + 1];
+            int32_t j = i - 1;
+            while (j >= s0 && b.obs_cam[(size_t)j] > c) {
+                b.obs_cam[(size_t)j + 1] = b.obs_cam[(size_t)j];
+                b.obs_uv[2 * (size_t)j + 2] = b.obs_uv[2 * (size_t)j];
+                b.obs_uv[2 * (size_t)j + 3] = b.obs_uv[2 * (size_t)j + 1];
+                --j;
+            }
+            b.obs_cam[(size_t)j + 1] = c;
+            b.obs_uv[2 * (size_t)j + 2] = u;
+            b.obs_uv[2 * (size_t)j + 3] = v;
+        }
+    }
+
+    // ---- this rank's point range (sharding: contiguous points, balanced on edge count) ----
+    h->shard_pt.assign((size_t)h->n_ranks + 1, (int32_t)Np);
+    h->shard_pt[0] = 0;
+    for (int r = 1; r < h->n_ranks; ++r) {
+        const int64_t target = Ne * r / h->n_ranks;
+        const auto it = std::lower_bound(b.pt_ptr.begin(), b.pt_ptr.end(), (int32_t)target);
+        h->shard_pt[(size_t)r] = (int32_t)std::min<int64_t>(Np, it - b.pt_ptr.begin());
+    }
+    const int32_t pt_begin = h->shard_pt[(size_t)h->rank], pt_end = h->shard_pt[(size_t)h->rank + 1];
+
+    // ---- pair list sorted by S block (two passes: count, fill) ----
+    std::vector<int64_t> blk_ptr((size_t)b.n_blocks + 1, 0);
+    auto for_pairs = [&](auto&& emit) {
+        for (int32_t p = pt_begin; p < pt_end; ++p) {
+            const int32_t tri0 = b.prob_tri0[(size_t)b.pt_prob[(size_t)p]];
+            const int32_t s0 = b.pt_ptr[(size_t)p], s1 = b.pt_ptr[(size_t)p + 1];
+            for (int32_t a = s0; a < s1; ++a) {
+                const int32_t fa = b.cam_free[(size_t)b.obs_cam[(size_t)a]];
+                if (fa < 0) continue;
+                for (int32_t c = s0; c <= a; ++c) { // sorted by pose: fc <= fa
+                    const int32_t fc = b.cam_free[(size_t)b.obs_cam[(size_t)c]];
+                    if (fc < 0) continue;
+                    emit(tri0 + fa * (fa + 1) / 2 + fc, a, c);
+                }
+            }
+        }
+    };
+    for_pairs([&](int32_t blk, int32_t, int32_t) { blk_ptr[(size_t)blk + 1]++; });
+    for (int32_t k = 0; k < b.n_blocks; ++k) blk_ptr[(size_t)k + 1] += blk_ptr[(size_t)k];
+    b.n_pairs = blk_ptr[(size_t)b.n_blocks];
+    if (b.n_pairs > 0x7fffffff) return fail(h, VISO_BA_ERR_UNSUPPORTED, "pair list too long (%lld)", (long long)b.n_pairs);
+    b.pairs.resize((size_t)b.n_pairs * 2);
+    {
+        std::vector<int64_t> cur(blk_ptr.begin(), blk_ptr.end() - 1);
+        for_pairs([&](int32_t blk, int32_t a, int32_t c) {
+            const int64_t q = cur[(size_t)blk]++;
+            b.pairs[2 * (size_t)q] = a;
+            b.pairs[2 * (size_t)q + 1] = c;
+        });
+    }
+
+    // ---- work items: slices of one block's pairs, one warp each ----
+    int64_t item_pairs = (b.n_pairs / 16384 + 31) / 32 * 32;
+    item_pairs = std::max<int64_t>(64, std::min<int64_t>(512, item_pairs));
+    b.block_item_ptr.assign((size_t)b.n_blocks + 1, 0);
+    b.block_cam.assign((size_t)b.n_blocks, -1);
+    for (int64_t p = 0; p < B; ++p)
+        for (int32_t c = b.prob_cam0[(size_t)p]; c < b.prob_cam0[(size_t)p + 1]; ++c) {
+            const int32_t f = b.cam_free[(size_t)c];
+            if (f >= 0) b.block_cam[(size_t)(b.prob_tri0[(size_t)p] + f * (f + 1) / 2 + f)] = c;
+        }
+    {
+        int32_t prob = 0;
+        for (int32_t k = 0; k < b.n_blocks; ++k) {
+            while (k >= b.prob_tri0[(size_t)prob + 1]) ++prob;
+            const int32_t is_diag = b.block_cam[(size_t)k] >= 0 ? 1 : 0;
+            for (int64_t q = blk_ptr[(size_t)k]; q < blk_ptr[(size_t)k + 1]; q += item_pairs) {
+                const int64_t q1 = std::min(q + item_pairs, blk_ptr[(size_t)k + 1]);
+                if (is_diag) b.diag_items.push_back((int32_t)(b.items.size() / 4));
+                b.items.push_back((int32_t)q);
+                b.items.push_back((int32_t)q1);
+                b.items.push_back(k);
+                b.items.push_back((prob << 1) | is_diag);
+            }
+            b.block_item_ptr[(size_t)k + 1] = (int32_t)(b.items.size() / 4);
+        }
+    }
+
+    // ---- chunks of points for the deterministic per-problem sums ----
+    b.prob_chunk_ptr.assign((size_t)B + 1, 0);
+    for (int64_t p = 0; p < B; ++p) {
+        const int32_t lo = std::max<int64_t>(pt0[(size_t)p], pt_begin), hi = (int32_t)std::min<int64_t>(pt0[(size_t)p + 1], pt_end);
+        for (int32_t q = lo; q < hi; q += kChunkPoints) {
+            b.chunks.push_back((int32_t)p);
+            b.chunks.push_back(q);
+            b.chunks.push_back(std::min(q + kChunkPoints, hi));
+            b.chunks.push_back(0);
+        }
+        b.prob_chunk_ptr[(size_t)p + 1] = (int32_t)(b.chunks.size() / 4);
+    }
+    return VISO_BA_OK;
+}
+
+template <typename T> int32_t h2d(viso_ba* h, T* dst, const std::vector<T>& src)
+{
+    if (src.empty()) return VISO_BA_OK;
+    CU(cudaMemcpyAsync(dst, src.data(), src.size() * sizeof(T), cudaMemcpyHostToDevice, h->stream));
+    return VISO_BA_OK;
+}
+
+} // namespace
+
+// ==========================================================================================
+// upload: H2D + device layout
+// ==========================================================================================
+namespace {
+
+struct DevPtrs { // everything carved out of the arena, in one place so that the dry run and the
+                 // real pass cannot diverge
+    int32_t *pt_ptr, *pt_prob, *obs_cam, *cam_free, *cam_prob, *prob_cam0, *prob_tri0, *prob_nfree;
+    float2* obs_uv;
+    int2* pairs;
+    int4 *items, *chunks;
+    int32_t *diag_items, *block_item_ptr, *block_cam, *prob_chunk_ptr;
+    double *pts[2], *pose[2], *cam_rt[2], *pose_init, *pts_init, *pose_out, *pts_out;
+    LmState* lm;
+    IterStat* iter_stats;
+    double *rec, *ptinfo, *cost_pt, *cost_new_pt, *scale_pt, *item_part, *S_blk, *bs, *dp, *chunk_part, *prob_sums;
+    unsigned long long* maxdiag_bits;
+    int32_t* n_active;
+    double *LA, *LDd, *Lx;
+    int32_t* Lfail;
+};
+
+constexpr int kMaxIterStats = 4096;
+
+void carve(Arena& A, DevPtrs& d, int64_t Nc, int64_t Np, int64_t Ne, int64_t B, const Built& b, bool large, int ldL)
+{
+    A.used = 0;
+    d.pt_ptr = A.take<int32_t>((size_t)Np + 1);
+    d.pt_prob = A.take<int32_t>((size_t)Np);
+    d.obs_cam = A.take<int32_t>((size_t)Ne);
+    d.obs_uv = A.take<float2>((size_t)Ne);
+    d.cam_free = A.take<int32_t>((size_t)Nc);
+    d.cam_prob = A.take<int32_t>((size_t)Nc);
+    d.prob_cam0 = A.take<int32_t>((size_t)B + 1);
+    d.prob_tri0 = A.take<int32_t>((size_t)B + 1);
+    d.prob_nfree = A.take<int32_t>((size_t)B);
+    d.pairs = A.take<int2>((size_t)b.n_pairs);
+    d.items = A.take<int4>(b.items.size() / 4);
+    d.diag_items = A.take<int32_t>(b.diag_items.size());
+    d.block_item_ptr = A.take<int32_t>((size_t)b.n_blocks + 1);
+    d.block_cam = A.take<int32_t>((size_t)b.n_blocks);
+    d.chunks = A.take<int4>(b.chunks.size() / 4);
+    d.prob_chunk_ptr = A.take<int32_t>((size_t)B + 1);
+    for (int k = 0; k < 2; ++k) {
+        d.pts[k] = A.take<double>((size_t)Np * 3);
+        d.pose[k] = A.take<double>((size_t)Nc * 7);
+        d.cam_rt[k] = A.take<double>((size_t)Nc * 12);
+    }
+    d.pose_init = A.take<double>((size_t)Nc * 7);
+    d.pts_init = A.take<double>((size_t)Np * 3);
+    d.pose_out = A.take<double>((size_t)Nc * 7);
+    d.pts_out = A.take<double>((size_t)Np * 3);
+    d.lm = A.take<LmState>((size_t)B);
+    d.iter_stats = A.take<IterStat>(kMaxIterStats);
+    d.rec = A.take<double>((size_t)Ne * kRecDoubles);
+    d.ptinfo = A.take<double>((size_t)Np * kPtInfoDoubles);
+    d.cost_pt = A.take<double>((size_t)Np);
+    d.cost_new_pt = A.take<double>((size_t)Np);
+    d.scale_pt = A.take<double>((size_t)Np);
+    d.item_part = A.take<double>(b.items.size() / 4 * kItemPart);
+    // S_blk | bs | prob_sums must stay contiguous: they are what a sharded handle all-reduces
+    d.S_blk = A.take<double>((size_t)b.n_blocks * 36 + (size_t)Nc * 6 + (size_t)B * 2);
+    d.bs = d.S_blk + (size_t)b.n_blocks * 36;
+    d.prob_sums = d.bs + (size_t)Nc * 6;
+    d.dp = A.take<double>((size_t)Nc * 6);
+    d.chunk_part = A.take<double>(b.chunks.size() / 4 * 2);
+    d.maxdiag_bits = A.take<unsigned long long>((size_t)B);
+    d.n_active = A.take<int32_t>(1);
+    if (large) {
+        const size_t n = (size_t)b.max_n;
+        d.LA = A.take<double>((n + 1) * (size_t)ldL);
+        d.LDd = A.take<double>(((n + 31) / 32) * 32 * 32);
+        d.Lx = A.take<double>(n);
+        d.Lfail = A.take<int32_t>(1);
+    } else {
+        d.LA = d.LDd = d.Lx = nullptr;
+        d.Lfail = nullptr;
+    }
+}
+
+} // namespace
+
+extern "C" int32_t viso_ba_upload(viso_ba* h)
+{
+    if (!h) return VISO_BA_ERR_ARG;
+    if (h->uploaded) return VISO_BA_OK;
+    int32_t rc = ensure_cuda(h);
+    if (rc) return rc;
+    const double t0 = now_ms();
+    const int64_t Nc = (int64_t)h->poses.size() / 7, Np = (int64_t)h->points.size() / 3;
+    const int64_t Ne = (int64_t)h->e_pose.size(), B = h->n_problems;
+    if (Nc < 1 || Np < 1) return fail(h, VISO_BA_ERR_STATE, "nothing to optimise: %lld poses, %lld points", (long long)Nc, (long long)Np);
+    drop_graph(h);
+    Built b;
+    if ((rc = build_structure(h, b))) return rc;
+    h->max_n = b.max_n;
+    h->use_large = b.max_n > kSmallMaxN;
+    if (h->use_large && B > 1)
+        return fail(h, VISO_BA_ERR_UNSUPPORTED, "batched problems need <= %d free poses each (got a reduced system of %d)", kSmallMaxN / 6, b.max_n);
+    if (h->n_ranks > 1 && B > 1) return fail(h, VISO_BA_ERR_UNSUPPORTED, "batched problems are not sharded: run replicas instead");
+    const int ldL = (b.max_n + 8) & ~7;
+
+    DevPtrs d;
+    Arena dry;
+    carve(dry, d, Nc, Np, Ne, B, b, h->use_large, ldL);
+    if (dry.used > h->arena.cap) {
+        if (h->arena.base) {
+            CU(cudaStreamSynchronize(h->stream));
+            CU(cudaFree(h->arena.base));
+            h->arena.base = nullptr, h->arena.cap = 0;
+        }
+        const size_t want = dry.used + dry.used / 8; // head-room so that a slightly larger window re-uses it
+        CU(cudaMalloc((void**)&h->arena.base, want));
+        h->arena.cap = want;
+    }
+    carve(h->arena, d, Nc, Np, Ne, B, b, h->use_large, ldL);
+
+    // topology
+    if ((rc = h2d(h, d.pt_ptr, b.pt_ptr))) return rc;
+    if ((rc = h2d(h, d.pt_prob, b.pt_prob))) return rc;
+    if ((rc = h2d(h, d.obs_cam, b.obs_cam))) return rc;
+    if ((rc = h2d(h, reinterpret_cast<float*>(d.obs_uv), b.obs_uv))) return rc;
+    if ((rc = h2d(h, d.cam_free, b.cam_free))) return rc;
+    if ((rc = h2d(h, d.cam_prob, b.cam_prob))) return rc;
+    if ((rc = h2d(h, d.prob_cam0, b.prob_cam0))) return rc;
+    if ((rc = h2d(h, d.prob_tri0, b.prob_tri0))) return rc;
+    if ((rc = h2d(h, d.prob_nfree, b.prob_nfree))) return rc;
+    if ((rc = h2d(h, reinterpret_cast<int32_t*>(d.pairs), b.pairs))) return rc;
+    if ((rc = h2d(h, reinterpret_cast<int32_t*>(d.items), b.items))) return rc;
+    if ((rc = h2d(h, d.diag_items, b.diag_items))) return rc;
+    if ((rc = h2d(h, d.block_item_ptr, b.block_item_ptr))) return rc;
+    if ((rc = h2d(h, d.block_cam, b.block_cam))) return rc;
+    if ((rc = h2d(h, reinterpret_cast<int32_t*>(d.chunks), b.chunks))) return rc;
+    if ((rc = h2d(h, d.prob_chunk_ptr, b.prob_chunk_ptr))) return rc;
+    // state: normalised quaternions (Sophus keeps unit quaternions), buffer 0 current
+    std::vector<double> poses = h->poses;
+    for (int64_t c = 0; c < Nc; ++c) {
+        double* q = &poses[(size_t)c * 7];
+        const double n = 1.0 / std::sqrt(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3]);
+        for (int i = 0; i < 4; ++i) q[i] *= n;
+    }
+    if ((rc = h2d(h, d.pose_init, poses))) return rc;
+    if ((rc = h2d(h, d.pts_init, h->points))) return rc;
+    CU(cudaStreamSynchronize(h->stream)); // `poses` and `b` die at the end of this scope
+
+    DevProblem& P = h->P;
+    std::memset(&P, 0, sizeof(P));
+    P.n_cams = (int32_t)Nc, P.n_points = (int32_t)Np, P.n_problems = (int32_t)B;
+    P.pt_begin = h->shard_pt[(size_t)h->rank], P.pt_end = h->shard_pt[(size_t)h->rank + 1];
+    P.n_obs = Ne, P.n_pairs = b.n_pairs;
+    P.n_items = (int32_t)(b.items.size() / 4), P.n_diag_items = (int32_t)b.diag_items.size();
+    P.n_blocks = b.n_blocks, P.n_chunks = (int32_t)(b.chunks.size() / 4);
+    P.fx = h->cfg.fx, P.fy = h->cfg.fy, P.cx = h->cfg.cx, P.cy = h->cfg.cy, P.huber_delta = h->cfg.huber_delta;
+    P.pt_ptr = d.pt_ptr, P.pt_prob = d.pt_prob, P.obs_cam = d.obs_cam, P.obs_uv = d.obs_uv;
+    P.cam_free = d.cam_free, P.cam_prob = d.cam_prob, P.prob_cam0 = d.prob_cam0, P.prob_tri0 = d.prob_tri0;
+    P.prob_nfree = d.prob_nfree, P.pairs = d.pairs, P.items = d.items, P.diag_items = d.diag_items;
+    P.block_item_ptr = d.block_item_ptr, P.block_cam = d.block_cam, P.chunks = d.chunks, P.prob_chunk_ptr = d.prob_chunk_ptr;
+    for (int k = 0; k < 2; ++k) P.pts[k] = d.pts[k], P.pose[k] = d.pose[k], P.cam_rt[k] = d.cam_rt[k];
+    P.lm = d.lm, P.iter_stats = (B == 1) ? d.iter_stats : nullptr;
+    P.rec = d.rec, P.ptinfo = d.ptinfo, P.cost_pt = d.cost_pt, P.cost_new_pt = d.cost_new_pt, P.scale_pt = d.scale_pt;
+    P.item_part = d.item_part, P.S_blk = d.S_blk, P.bs = d.bs, P.dp = d.dp, P.chunk_part = d.chunk_part;
+    P.prob_sums = d.prob_sums, P.maxdiag_bits = d.maxdiag_bits, P.n_active = d.n_active;
+    P.lambda_scale = h->rank == 0 ? 1.0 : 0.0;
+    h->d_pose_init = d.pose_init, h->d_pts_init = d.pts_init, h->d_pose_out = d.pose_out, h->d_pts_out = d.pts_out;
+    h->d_allreduce = d.S_blk;
+    h->allreduce_count = (size_t)b.n_blocks * 36 + (size_t)Nc * 6;
+    std::memset(&h->L, 0, sizeof(h->L));
+    if (h->use_large) {
+        h->L.n = b.max_n, h->L.ld = ldL, h->L.A = d.LA, h->L.Dd = d.LDd, h->L.x = d.Lx, h->L.fail = d.Lfail;
+    }
+    CU(cudaMemsetAsync(d.S_blk, 0, sizeof(double) * (h->allreduce_count + (size_t)B * 2), h->stream));
+    CU(cudaMemsetAsync(d.bs, 0, sizeof(double) * (size_t)Nc * 6, h->stream));
+    CU(cudaMemsetAsync(d.dp, 0, sizeof(double) * (size_t)Nc * 6, h->stream));
+    h->uploaded = true;
+    if ((rc = viso_ba_reset_state(h))) {
+        h->uploaded = false;
+        return rc;
+    }
+    CU(cudaStreamSynchronize(h->stream));
+    h->setup_ms = (float)(now_ms() - t0);
+    return VISO_BA_OK;
+}
+
+extern "C" int32_t viso_ba_reset_state(viso_ba* h)
+{
+    if (!h) return VISO_BA_ERR_ARG;
+    if (!h->uploaded) return viso_ba_upload(h); // upload ends with a reset
+    int32_t rc = ensure_cuda(h);
+    if (rc) return rc;
+    const DevProblem& P = h->P;
+    CU(cudaMemcpyAsync(P.pose[0], h->d_pose_init, sizeof(double) * 7 * (size_t)P.n_cams, cudaMemcpyDeviceToDevice, h->stream));
+    CU(cudaMemcpyAsync(P.pts[0], h->d_pts_init, sizeof(double) * 3 * (size_t)P.n_points, cudaMemcpyDeviceToDevice, h->stream));
+    CU(cudaMemsetAsync(P.lm, 0, sizeof(LmState) * (size_t)P.n_problems, h->stream)); // cur = 0
+    run_k(h, "state_init", [&] { return launch_state_init(P, 0, h->cfg.lm_max_trials, 0.0, h->stream); });
+    run_k(h, "cam_rt", [&] { return launch_cam_rt(P, 0, h->stream); });
+    CU(cudaGetLastError());
+    return VISO_BA_OK;
+}
+
+// ==========================================================================================
+// the LM driver: optimizer_.initializeOptimization() + optimize(n), which the reference never
+// calls.  All decisions (gain ratio, accept / reject, lambda) are taken on the
+// device by k_decide; the host only enqueues trials and polls one counter.
+// ==========================================================================================
+namespace {
+
+int32_t pin_reserve(viso_ba* h, size_t bytes)
+{
+    if (bytes <= h->pin_cap) return VISO_BA_OK;
+    if (h->pin) cudaFreeHost(h->pin);
+    h->pin = nullptr, h->pin_cap = 0;
+    CU(cudaHostAlloc(&h->pin, bytes, cudaHostAllocDefault));
+    h->pin_cap = bytes;
+    return VISO_BA_OK;
+}
+
+int32_t allreduce(viso_ba* h, double* buf, size_t count, int op)
+{
+    if (h->n_ranks <= 1) return VISO_BA_OK;
+    NcclApi* api = nccl_api();
+    if (!api || !h->comm) return fail(h, VISO_BA_ERR_NCCL, "sharded handle without a communicator");
+    NC(api->AllReduce(buf, buf, count, kNcclDouble, op, h->comm, h->stream));
+    return VISO_BA_OK;
+}
+
+int32_t enqueue_trial(viso_ba* h)
+{
+    const DevProblem& P = h->P;
+    cudaStream_t st = h->stream;
+    int32_t rc;
+    run_k(h, "linearize", [&] { return launch_linearize(P, 0, -1.0, st); });
+    run_k(h, "schur_blocks", [&] { return launch_schur_blocks(P, 0, st); });
+    run_k(h, "block_finalize", [&] { return launch_block_finalize(P, 0, -1.0, st); });
+    if ((rc = allreduce(h, h->d_allreduce, h->allreduce_count, kNcclSum))) return rc;
+    if (h->use_large) run_k(h, "solve_large", [&] { return launch_solve_large(P, h->L, st); });
+    else run_k(h, "solve_small", [&] { return launch_solve_small(P, h->max_n, st); });
+    run_k(h, "update", [&] { return launch_update(P, st); });
+    run_k(h, "reduce", [&] { return launch_reduce(P, 1, st); });
+    if ((rc = allreduce(h, P.prob_sums, 2 * (size_t)P.n_problems, kNcclSum))) return rc;
+    run_k(h, "decide", [&] { return launch_decide(P, st); });
+    return VISO_BA_OK;
+}
+
+int32_t run_trials(viso_ba* h, int count)
+{
+    const bool graph_ok = h->cfg.use_cuda_graph && !h->timing && h->n_ranks == 1;
+    if (!graph_ok) {
+        for (int i = 0; i < count; ++i) {
+            int32_t rc = enqueue_trial(h);
+            if (rc) return rc;
+        }
+        CU(cudaGetLastError());
+        return VISO_BA_OK;
+    }
+    if (!h->trial_graph) {
+        cudaGraph_t g = nullptr;
+        const int64_t before = h->launches;
+        CU(cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
+        int32_t rc = enqueue_trial(h);
+        cudaError_t e = cudaStreamEndCapture(h->stream, &g);
+        h->trial_graph_launches = (int)(h->launches - before);
+        h->launches = before;
+        if (rc) return rc;
+        if (e != cudaSuccess) return fail(h, VISO_BA_ERR_CUDA, "graph capture: %s", cudaGetErrorString(e));
+        e = cudaGraphInstantiate(&h->trial_graph, g, 0);
+        cudaGraphDestroy(g);
+        if (e != cudaSuccess) return fail(h, VISO_BA_ERR_CUDA, "graph instantiate: %s", cudaGetErrorString(e));
+    }
+    for (int i = 0; i < count; ++i) {
+        CU(cudaGraphLaunch(h->trial_graph, h->stream));
+        h->launches += h->trial_graph_launches;
+    }
+    return VISO_BA_OK;
+}
+
+int32_t run_lm(viso_ba* h, int iterations, viso_ba_summary* summary)
+{
+    const DevProblem& P = h->P;
+    cudaStream_t st = h->stream;
+    int32_t rc;
+    if (iterations > kMaxIterStats) return fail(h, VISO_BA_ERR_ARG, "at most %d iterations per call", kMaxIterStats);
+    if (iterations < 0) iterations = 0;
+    CU(cudaEventRecord(h->ev0, st));
+    run_k(h, "state_init", [&] { return launch_state_init(P, iterations > 0 ? iterations : 1, h->cfg.lm_max_trials, h->cfg.lm_lambda_init, st); });
+    // first linearisation: cost of the start state, lambda_0 = tau * max diag(H)   (g2o computeLambdaInit)
+    run_k(h, "linearize", [&] { return launch_linearize(P, 1, -1.0, st); });
+    run_k(h, "schur_blocks", [&] { return launch_schur_blocks(P, 1, st); });
+    run_k(h, "block_finalize", [&] { return launch_block_finalize(P, 1, -1.0, st); });
+    run_k(h, "reduce", [&] { return launch_reduce(P, 0, st); });
+    if (h->n_ranks > 1) {
+        if ((rc = allreduce(h, h->d_allreduce, h->allreduce_count + 2 * (size_t)P.n_problems, kNcclSum))) return rc;
+        if ((rc = allreduce(h, reinterpret_cast<double*>(P.maxdiag_bits), (size_t)P.n_problems, kNcclMax))) return rc;
+    }
+    run_k(h, "lm_init", [&] { return launch_lm_init(P, h->cfg.lm_tau, h->cfg.lm_lambda_init, st); });
+    CU(cudaGetLastError());
+
+    if ((rc = pin_reserve(h, 64 + sizeof(LmState) * (size_t)P.n_problems))) return rc;
+    int32_t* n_active = static_cast<int32_t*>(h->pin);
+    int done = 0;
+    const long long max_rounds = (long long)iterations * h->cfg.lm_max_trials;
+    int batch = iterations;
+    while (iterations > 0 && done < max_rounds) {
+        batch = (int)std::min<long long>(batch, max_rounds - done);
+        if ((rc = run_trials(h, batch))) return rc;
+        done += batch;
+        CU(cudaMemcpyAsync(n_active, P.n_active, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+        if (*n_active <= 0) break;
+        batch = std::max(1, std::min(iterations, 4)); // stragglers: a few rejected trials to make up
+    }
+    CU(cudaEventRecord(h->ev1, st));
+    LmState* lm = reinterpret_cast<LmState*>(static_cast<char*>(h->pin) + 64);
+    CU(cudaMemcpyAsync(lm, P.lm, sizeof(LmState) * (size_t)P.n_problems, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    CU(cudaGetLastError());
+    h->lm_host.assign(lm, lm + P.n_problems);
+    resolve_timing(h);
+    if (summary) {
+        std::memset(summary, 0, sizeof(*summary));
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, h->ev0, h->ev1);
+        summary->device_ms = ms;
+        summary->setup_ms = h->setup_ms;
+        for (const LmState& s : h->lm_host) { // batched: totals over the problems
+            summary->initial_cost += s.chi_initial;
+            summary->final_cost += s.chi;
+            summary->iterations = std::max(summary->iterations, s.it);
+            summary->trials += s.trials;
+            summary->terminated += s.terminated;
+        }
+        summary->final_lambda = h->lm_host[0].lambda;
+    }
+    return VISO_BA_OK;
+}
+
+// current state -> contiguous device buffers -> host staging vectors
+int32_t read_back(viso_ba* h)
+{
+    const DevProblem& P = h->P;
+    run_k(h, "gather_current", [&] { return launch_gather_current(P, h->d_pose_out, h->d_pts_out, h->stream); });
+    if (h->n_ranks > 1) { // every rank moved only its own points
+        NcclApi* api = nccl_api();
+        NC(api->GroupStart());
+        for (int r = 0; r < h->n_ranks; ++r) {
+            const size_t a = 3 * (size_t)h->shard_pt[(size_t)r], n = 3 * (size_t)h->shard_pt[(size_t)r + 1] - a;
+            if (n) NC(api->Broadcast(h->d_pts_out + a, h->d_pts_out + a, n, kNcclDouble, r, h->comm, h->stream));
+        }
+        NC(api->GroupEnd());
+    }
+    const size_t nb_pose = sizeof(double) * 7 * (size_t)P.n_cams, nb_pts = sizeof(double) * 3 * (size_t)P.n_points;
+    int32_t rc = pin_reserve(h, nb_pose + nb_pts + 64 + sizeof(LmState) * (size_t)P.n_problems);
+    if (rc) return rc;
+    char* pin = static_cast<char*>(h->pin);
+    CU(cudaMemcpyAsync(pin, h->d_pose_out, nb_pose, cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaMemcpyAsync(pin + nb_pose, h->d_pts_out, nb_pts, cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    std::memcpy(h->poses.data(), pin, nb_pose);
+    std::memcpy(h->points.data(), pin + nb_pose, nb_pts);
+    return VISO_BA_OK;
+}
+
+} // namespace
+
+extern "C" int32_t viso_ba_optimize_resident(viso_ba* h, int32_t iterations, viso_ba_summary* summary)
+{
+    if (!h) return VISO_BA_ERR_ARG;
+    int32_t rc = viso_ba_upload(h);
+    if (rc) return rc;
+    if ((rc = ensure_cuda(h))) return rc;
+    return run_lm(h, iterations, summary);
+}
+
+extern "C" int32_t viso_ba_optimize(viso_ba* h, int32_t iterations, viso_ba_iter_stats* stats, viso_ba_summary* summary)
+{
+    if (!h) return VISO_BA_ERR_ARG;
+    int32_t rc = viso_ba_upload(h);
+    if (rc) return rc;
+    if ((rc = ensure_cuda(h))) return rc;
+    if (stats && h->n_problems != 1) return fail(h, VISO_BA_ERR_ARG, "per-iteration stats exist for single-problem handles only");
+    viso_ba_summary local;
+    if ((rc = run_lm(h, iterations, &local))) return rc;
+    if (summary) *summary = local;
+    if (stats && iterations > 0) {
+        std::vector<IterStat> tmp((size_t)iterations);
+        CU(cudaMemcpyAsync(tmp.data(), h->P.iter_stats, sizeof(IterStat) * (size_t)local.iterations, cudaMemcpyDeviceToHost, h->stream));
+        CU(cudaStreamSynchronize(h->stream));
+        for (int i = 0; i < iterations; ++i) {
+            if (i < local.iterations) {
+                stats[i].cost_before = tmp[(size_t)i].cost_before, stats[i].cost_after = tmp[(size_t)i].cost_after;
+                stats[i].lambda = tmp[(size_t)i].lambda, stats[i].trials = tmp[(size_t)i].trials, stats[i].accepted = tmp[(size_t)i].accepted;
+            } else {
+                std::memset(&stats[i], 0, sizeof(stats[i]));
+            }
+        }
+    }
+    // the host copy now holds the refined state; the device keeps it too (uploaded stays true)
+    return read_back(h);
+}
+
+extern "C" int32_t viso_ba_get_poses(viso_ba* h, int64_t first, int64_t count, double* out7)
+{
+    if (!h || !out7 || first < 0 || count < 0) return VISO_BA_ERR_ARG;
+    if (first + count > (int64_t)h->poses.size() / 7) return fail(h, VISO_BA_ERR_INDEX, "poses [%lld, %lld) out of range", (long long)first, (long long)(first + count));
+    std::memcpy(out7, h->poses.data() + 7 * first, sizeof(double) * 7 * (size_t)count);
+    return VISO_BA_OK;
+}
+
+extern "C" int32_t viso_ba_get_points(viso_ba* h, int64_t first, int64_t count, double* out3)
+{
+    if (!h || !out3 || first < 0 || count < 0) return VISO_BA_ERR_ARG;
+    if (first + count > (int64_t)h->points.size() / 3) return fail(h, VISO_BA_ERR_INDEX, "points [%lld, %lld) out of range", (long long)first, (long long)(first + count));
+    std::memcpy(out3, h->points.data() + 3 * first, sizeof(double) * 3 * (size_t)count);
+    return VISO_BA_OK;
+}
+
+extern "C" int32_t viso_ba_get_problem_summaries(viso_ba* h, viso_ba_summary* out)
+{
+    if (!h || !out) return VISO_BA_ERR_ARG;
+    if (h->lm_host.size() != (size_t)h->n_problems) return fail(h, VISO_BA_ERR_STATE, "no optimize call yet");
+    for (size_t b = 0; b < h->lm_host.size(); ++b) {
+        const LmState& s = h->lm_host[b];
+        std::memset(&out[b], 0, sizeof(out[b]));
+        out[b].initial_cost = s.chi_initial, out[b].final_cost = s.chi, out[b].final_lambda = s.lambda;
+        out[b].iterations = s.it, out[b].trials = s.trials, out[b].terminated = s.terminated;
+    }
+    return VISO_BA_OK;
+}
+
+extern "C" int32_t viso_ba_eval_cost(viso_ba* h, double* cost)
+{
+    if (!h || !cost) return VISO_BA_ERR_ARG;
+    int32_t rc = viso_ba_upload(h);
+    if (rc) return rc;
+    if ((rc = ensure_cuda(h))) return rc;
+    const DevProblem& P = h->P;
+    run_k(h, "eval_cost", [&] { return launch_eval_cost(P, h->stream); });
+    run_k(h, "reduce", [&] { return launch_reduce(P, 2, h->stream); });
+    if ((rc = allreduce(h, P.prob_sums, 2 * (size_t)P.n_problems, kNcclSum))) return rc;
+    if ((rc = pin_reserve(h, sizeof(double) * 2 * (size_t)P.n_problems))) return rc;
+    CU(cudaMemcpyAsync(h->pin, P.prob_sums, sizeof(double) * 2 * (size_t)P.n_problems, cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    CU(cudaGetLastError());
+    resolve_timing(h);
+    double s = 0.0;
+    for (int b = 0; b < P.n_problems; ++b) s += static_cast<double*>(h->pin)[2 * b];
+    *cost = s;
+    return VISO_BA_OK;
+}
+
+extern "C" int32_t viso_ba_debug_reduced_system(viso_ba* h, double lambda, int32_t n_cap, double* S, double* bs, int32_t* n_out)
+{
+    if (!h || !n_out) return VISO_BA_ERR_ARG;
+    int32_t rc = viso_ba_upload(h);
+    if (rc) return rc;
+    if ((rc = ensure_cuda(h))) return rc;
+    if (h->n_problems != 1) return fail(h, VISO_BA_ERR_UNSUPPORTED, "debug hook works on single-problem handles");
+    const DevProblem& P = h->P;
+    const int n = h->max_n, nf = n / 6;
+    *n_out = n;
+    if (!S && !bs) return VISO_BA_OK;
+    if (n_cap < n) return fail(h, VISO_BA_ERR_CAPACITY, "reduced system is %d x %d", n, n);
+    cudaStream_t st = h->stream;
+    run_k(h, "state_init", [&] { return launch_state_init(P, 1, h->cfg.lm_max_trials, lambda, st); });
+    run_k(h, "linearize", [&] { return launch_linearize(P, 0, lambda, st); });
+    run_k(h, "schur_blocks", [&] { return launch_schur_blocks(P, 0, st); });
+    run_k(h, "block_finalize", [&] { return launch_block_finalize(P, 0, lambda, st); });
+    if ((rc = allreduce(h, h->d_allreduce, h->allreduce_count, kNcclSum))) return rc;
+    run_k(h, "state_init", [&] { return launch_state_init(P, 0, h->cfg.lm_max_trials, 0.0, st); });
+    std::vector<double> blk((size_t)P.n_blocks * 36), b6((size_t)P.n_cams * 6);
+    std::vector<int32_t> cam_free((size_t)P.n_cams);
+    CU(cudaMemcpyAsync(blk.data(), P.S_blk, sizeof(double) * blk.size(), cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(b6.data(), P.bs, sizeof(double) * b6.size(), cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(cam_free.data(), P.cam_free, sizeof(int32_t) * cam_free.size(), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    CU(cudaGetLastError());
+    resolve_timing(h);
+    if (S)
+        for (int I = 0; I < nf; ++I)
+            for (int J = 0; J <= I; ++J) {
+                const double* x = &blk[36 * (size_t)(I * (I + 1) / 2 + J)];
+                for (int r = 0; r < 6; ++r)
+                    for (int c = 0; c < 6; ++c) {
+                        S[(size_t)(6 * I + r) * n + 6 * J + c] = x[6 * r + c];
+                        S[(size_t)(6 * J + c) * n + 6 * I + r] = x[6 * r + c];
+                    }
+            }
+    if (bs)
+        for (int c = 0; c < P.n_cams; ++c)
+            if (cam_free[(size_t)c] >= 0)
+                for (int r = 0; r < 6; ++r) bs[6 * cam_free[(size_t)c] + r] = b6[6 * (size_t)c + r];
+    return VISO_BA_OK;
+}
+
+extern "C" int32_t viso_ba_set_kernel_timing(viso_ba* h, int32_t on)
+{
+    if (!h) return VISO_BA_ERR_ARG;
+    h->timing = on != 0;
+    h->ktimes.clear();
+    return VISO_BA_OK;
+}
+
+extern "C" int32_t viso_ba_get_kernel_times(viso_ba* h, int32_t cap, viso_ba_kernel_time* out, int32_t* n_out)
+{
+    if (!h || !n_out) return VISO_BA_ERR_ARG;
+    resolve_timing(h);
+    *n_out = (int32_t)h->ktimes.size();
+    if (!out) return VISO_BA_OK;
+    int i = 0;
+    for (const auto& kv : h->ktimes) {
+        if (i >= cap) break;
+        std::memset(&out[i], 0, sizeof(out[i]));
+        std::strncpy(out[i].name, kv.first.c_str(), sizeof(out[i].name) - 1);
+        out[i].launches = kv.second.launches;
+        out[i].device_ms = kv.second.ms;
+        ++i;
+    }
+    return VISO_BA_OK;
+}
+
+// ==========================================================================================
+// sharding over the GPUs of one box
+// ==========================================================================================
+extern "C" int32_t viso_ba_nccl_unique_id(void* out128)
+{
+    if (!out128) return VISO_BA_ERR_ARG;
+    NcclApi* api = nccl_api();
+    if (!api) return VISO_BA_ERR_NCCL;
+    return api->GetUniqueId(out128) == 0 ? VISO_BA_OK : VISO_BA_ERR_NCCL;
+}
+
+extern "C" int32_t viso_ba_shard_init(viso_ba* h, int32_t rank, int32_t n_ranks, const void* id128)
+{
+    if (!h || n_ranks < 1 || rank < 0 || rank >= n_ranks) return VISO_BA_ERR_ARG;
+    if (n_ranks == 1) {
+        h->rank = 0, h->n_ranks = 1;
+        return VISO_BA_OK;
+    }
+    if (!id128) return VISO_BA_ERR_ARG;
+    int32_t rc = ensure_cuda(h);
+    if (rc) return rc;
+    NcclApi* api = nccl_api();
+    if (!api) return fail(h, VISO_BA_ERR_NCCL, "libnccl.so.2 not found: %s", dlerror());
+    if (h->comm) {
+        api->CommDestroy(h->comm);
+        h->comm = nullptr;
+    }
+    Id128 id;
+    std::memcpy(id.b, id128, 128);
+    NC(api->CommInitRank(&h->comm, n_ranks, id, rank));
+    h->rank = rank, h->n_ranks = n_ranks;
+    h->uploaded = false;
+    drop_graph(h);
+    return VISO_BA_OK;
+}
