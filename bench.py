@@ -1,0 +1,484 @@
+#!/usr/bin/env python
+"""bench.py — bundle-adjustment throughput on B200 (BASELINE.json metric: BA observations/sec
+and LM iterations/sec), one JSON line on stdout.
+
+    python bench.py --gpus N --steps K --warmup W [--workload c5|c1|c2|c3] [--impl reference]
+
+A "step" is one bundle adjustment of the workload: `--lm-iters` (10) Levenberg-Marquardt
+iterations from the same perturbed start.  observations/sec = sum over problems of
+(edges x LM trials executed) / time, a trial being one linearise + Schur + solve + update +
+cost evaluation.
+
+  value : device-resident leg (inputs already in HBM), CUDA-event time of the LM loop on the
+          stream the kernels are launched on, max over ranks.
+  e2e   : the same metric through the C ABI with HOST buffers: set_problem (pinned host arrays)
+          + Optimize (H2D, structure build, LM, D2H of poses and points), wall clock.
+  --impl reference : the CPU oracle (the reference adjuster itself cannot be compiled, see
+          DESIGN.md) on all host cores over a bounded sample of the same workload.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for _p in (ROOT, os.path.join(ROOT, "tests")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+import numpy as np  # noqa: E402
+
+METRIC = "ba_observations_per_sec"
+UNIT = "obs/s"
+WORKLOADS = {
+    "c1": "BASELINE configs[0]: one window, 10 keyframes / 2k points / ~15k observations, L2",
+    "c2": "BASELINE configs[1]: one sliding window, 20 keyframes / 10k points / ~80k observations, Huber",
+    "c3": "BASELINE configs[2]: global BA, 200 keyframes / 100k points / ~1M observations (sharded by point for N>1)",
+    "c5": "BASELINE configs[4]: 1024 concurrent 10-keyframe / 2k-point / ~15k-observation windows per GPU",
+}
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="c5", choices=sorted(WORKLOADS))
+    ap.add_argument("--lm-iters", type=int, default=10)
+    ap.add_argument("--windows", type=int, default=1024, help="windows per GPU (workload c5)")
+    ap.add_argument("--cpu-sample-s", type=float, default=12.0, help="target seconds of the CPU baseline sample")
+    ap.add_argument("--no-others", action="store_true", help="skip the secondary workloads in the JSON line")
+    ap.add_argument("--no-e2e", action="store_true", help="skip the end-to-end leg (profiling runs)")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg (profiling runs)")
+    return ap.parse_args()
+
+
+# ---------------------------------------------------------------------------------------------
+# workloads
+# ---------------------------------------------------------------------------------------------
+def make_workload(vb, name, rank, windows):
+    """returns (list of problems, huber delta, sharded?)"""
+    if name == "c5":
+        probs = [vb.synth_config(5, rank * windows + w) for w in range(windows)]
+        return probs, 0.0
+    cid = {"c1": 1, "c2": 2, "c3": 3}[name]
+    if name == "c3":
+        p = vb.synth_config(cid)  # every rank holds the SAME problem; it is sharded by point
+    else:
+        sp = vb.synth_preset(cid)
+        sp.seed += 0x1000 * rank  # replicas: every GPU its own window
+        p = vb.synth_problem(sp)
+    return [p], p["huber_delta"]
+
+
+def pinned_copy(torch, a):
+    t = torch.from_numpy(np.ascontiguousarray(a)).pin_memory()
+    return t, t.numpy()
+
+
+def make_adjuster(vb, batch, huber, device):
+    ba = vb.BundleAdjuster(len(batch["points_init"]), len(batch["poses_init"]), len(batch["edge_pose"]),
+                           huber_delta=huber, device=device)
+    return ba
+
+
+def set_problem(ba, batch):
+    if len(batch["pose_off"]) > 2:
+        ba.set_problem_batched(batch["pose_off"], batch["point_off"], batch["edge_off"], batch["poses_init"],
+                               batch["points_init"], batch["edge_pose"], batch["edge_point"], batch["edge_uv"])
+    else:
+        ba.set_problem(batch["poses_init"], batch["points_init"], batch["edge_pose"], batch["edge_point"], batch["edge_uv"])
+
+
+def units_of(ba, batch):
+    """sum over problems of edges x trials of the last optimize call"""
+    sums = ba.problem_summaries()
+    ne = np.diff(batch["edge_off"])
+    return float(sum(int(n) * s.trials for n, s in zip(ne, sums))), sum(s.trials for s in sums)
+
+
+# ---------------------------------------------------------------------------------------------
+# clocks during the timed region (pynvml; falls back to nvidia-smi)
+# ---------------------------------------------------------------------------------------------
+class ClockSampler:
+    REASONS = {0x1: "gpu_idle", 0x2: "applications_clocks_setting", 0x4: "sw_power_cap", 0x8: "hw_slowdown",
+               0x10: "sync_boost", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
+               0x80: "hw_power_brake_slowdown", 0x100: "display_clock_setting"}
+
+    def __init__(self, index):
+        self.samples, self.reasons, self.stop_flag, self.max_mhz = [], set(), False, None
+        self.thread = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def _loop(self):
+        nv = self.nv
+        while not self.stop_flag:
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                bits = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h) if hasattr(nv, "nvmlDeviceGetCurrentClocksEventReasons") \
+                    else nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for b, n in self.REASONS.items():
+                    if bits & b and n != "gpu_idle":
+                        self.reasons.add(n)
+            except Exception:
+                pass
+            time.sleep(0.01)
+
+    def start(self):
+        if self.nv:
+            self.thread = threading.Thread(target=self._loop, daemon=True)
+            self.thread.start()
+
+    def stop(self):
+        self.stop_flag = True
+        if self.thread:
+            self.thread.join()
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": ["unavailable"]}
+        return {"sm_mhz": float(np.median(self.samples)), "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(self.samples)}
+
+
+# ---------------------------------------------------------------------------------------------
+# CPU baseline: the oracle on all host cores, one problem per thread (windows are independent)
+# ---------------------------------------------------------------------------------------------
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def cpu_leg(vb, workload, lm_iters, target_s, windows):
+    """returns dict(value, unit, cores, kind, sample, seconds, units)"""
+    import oracle_lib as orc
+    from concurrent.futures import ThreadPoolExecutor
+    cores = host_cores()
+
+    def solve(p, threads):
+        c = orc.cfg(K=p["K"], huber_delta=p["huber_delta"], threads=threads)
+        _, _, _, _, st = orc.optimize(c, p["poses_init"], p["points_init"], p["edge_pose"], p["edge_point"], p["edge_uv"], lm_iters)
+        return len(p["edge_pose"]) * sum(s.trials for s in st)
+
+    if workload == "c5":
+        probe = vb.synth_config(5, 0)
+        t0 = time.perf_counter()
+        solve(probe, 1)
+        t1 = time.perf_counter() - t0
+        n = int(max(cores, min(windows, cores * max(1.0, target_s / max(t1, 1e-3)))))
+        n = (n // cores) * cores
+        probs = [vb.synth_config(5, w) for w in range(n)]
+        t0 = time.perf_counter()
+        with ThreadPoolExecutor(cores) as ex:  # ctypes releases the GIL: `cores` windows in flight
+            units = sum(ex.map(lambda q: solve(q, 1), probs))
+        dt = time.perf_counter() - t0
+        sample = "%d of the %d windows, one window per thread, %d LM iterations each" % (n, windows, lm_iters)
+    else:
+        p = vb.synth_config({"c1": 1, "c2": 2, "c3": 3}[workload])
+        reps, units, dt = 0, 0.0, 0.0
+        while dt < target_s and reps < 200:
+            t0 = time.perf_counter()
+            units += solve(p, cores)
+            dt += time.perf_counter() - t0
+            reps += 1
+        sample = "the whole problem, %d repetitions of %d LM iterations, OpenMP over points" % (reps, lm_iters)
+    return {"value": units / dt, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample,
+            "seconds": round(dt, 3), "units": units}
+
+
+def run_reference(args):
+    """--impl reference: the CPU oracle port is the only runnable statement of the reference path
+    (the reference adjuster does not compile; no oracle/_ref exists).  Rank 0 only."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    import viso_b200 as vb
+    per = max(2.0, min(args.cpu_sample_s, 120.0 / max(1, args.steps + args.warmup)))
+    for _ in range(args.warmup):
+        cpu_leg(vb, args.workload, args.lm_iters, per / 4, args.windows)
+    units, secs, last = 0.0, 0.0, None
+    for _ in range(args.steps):
+        last = cpu_leg(vb, args.workload, args.lm_iters, per, args.windows)
+        units += last["units"]
+        secs += last["seconds"]
+    value = units / secs
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * secs / max(1, args.steps), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": args.workload, "description": WORKLOADS[args.workload], "lm_iterations": args.lm_iters,
+                   "note": "each step is a bounded sample of the workload on the host cores"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": last["cores"], "kind": "port", "sample": last["sample"]},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ---------------------------------------------------------------------------------------------
+# roofline of the dominant kernel: algorithmic bytes per launch (DESIGN.md "Algorithmic bytes")
+# ---------------------------------------------------------------------------------------------
+def algorithmic_bytes(No, Np, Nc, Nblocks):
+    """SURVEY 8(d) per LM iteration, split by pass.  Storage: observation = 16 B (u, v fp32 + two
+    int32 indices), point = 24 B, per-point saved (Hll^-1, g_l) = 72 B, S block = 288 B, pose = 96 B."""
+    S = 288.0 * Nblocks + 48.0 * Nc
+    return {
+        "L": 16.0 * No + (24.0 + 72.0) * Np + 96.0 * Nc + S,           # linearise + Schur
+        "B": 16.0 * No + (24.0 + 72.0 + 24.0) * Np + 48.0 * Nc,        # back-substitute + update
+        "C": 16.0 * No + 24.0 * Np + 96.0 * Nc,                         # cost at the candidate
+    }
+
+
+# which pass each kernel belongs to (kernels of one pass are timed together)
+PASS_OF = {"linearize": "L", "schur_blocks": "L", "block_finalize": "L", "window_linearize_schur": "L",
+           "update": "BC", "solve_small": None, "solve_large": None, "reduce": None, "decide": None}
+
+
+def measured_peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as fh:
+            return float(json.load(fh)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def roofline(ktimes, trials_per_problem, sizes):
+    """ktimes: name -> (launches, total ms) of ONE optimize call timed kernel by kernel."""
+    No, Np, Nc, Nblocks = sizes
+    A = algorithmic_bytes(No, Np, Nc, Nblocks)
+    A["BC"] = A["B"] + A["C"]
+    A_iter = A["L"] + A["B"] + A["C"]
+    peak, peak_src = measured_peak()
+    per_kernel = {k: {"launches": n, "avg_us": 1e3 * ms / max(1, n), "total_ms": ms} for k, (n, ms) in ktimes.items()}
+    top = max(ktimes, key=lambda k: ktimes[k][1])
+    ps = PASS_OF.get(top)
+    if ps is None:  # a solve kernel dominates: it has no HBM-bound share worth a roofline; use pass L anyway
+        ps = "L"
+    members = [k for k in ktimes if PASS_OF.get(k) == ps]
+    # one launch of every member per trial (plus the init linearisation): time per launch of the pass
+    t_us = sum(per_kernel[k]["avg_us"] for k in members)
+    achieved = A[ps] / (t_us * 1e-6) / 1e9
+    traffic = None
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as fh:
+            tr = json.load(fh)
+        traffic = sum(tr[k] for k in members)
+    except Exception:
+        pass
+    return {
+        "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+        "kernel": top, "pass": ps, "pass_kernels": members, "pass_us_per_launch": t_us,
+        "algorithmic_bytes_per_launch": A[ps], "algorithmic_bytes_per_lm_iteration": A_iter,
+        "peak_source": peak_src, "kernels": per_kernel,
+    }
+
+
+# ---------------------------------------------------------------------------------------------
+# the B200 arm
+# ---------------------------------------------------------------------------------------------
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    import viso_b200 as vb
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        raise SystemExit("--gpus %d but WORLD_SIZE=%d: launch with torch.distributed.run --nproc-per-node %d"
+                         % (args.gpus, world, args.gpus))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a B200: no CUDA device is visible and this backend has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    sharded = args.workload == "c3" and world > 1
+    probs, huber = make_workload(vb, args.workload, rank, args.windows)
+    batch = vb.batch_problems(probs)
+    # pinned host copies: what the e2e leg hands to the C ABI every step
+    keep, host = [], {}
+    for k, v in batch.items():
+        t, a = pinned_copy(torch, v)
+        keep.append(t)
+        host[k] = a
+    No, Np, Nc = len(host["edge_pose"]), len(host["points_init"]), len(host["poses_init"])
+    nprob = len(probs)
+    nfree = [len(p["poses_init"]) - 1 for p in probs]
+    Nblocks = sum(f * (f + 1) // 2 for f in nfree)
+
+    ba = make_adjuster(vb, host, huber, local)
+    if sharded:
+        ident = [vb.nccl_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(ident, src=0)
+        ba.shard_init(rank, world, ident[0])
+    set_problem(ba, host)
+    ba.upload()
+
+    flush = None
+    working_set = 12.0 * No + 96.0 * No  # observations + per-observation records
+    if working_set < 2 * 126e6:
+        flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+
+    def step_resident():
+        if flush is not None:
+            flush.zero_()
+            torch.cuda.synchronize()
+        ba.reset_state()
+        return ba.optimize_resident(args.lm_iters)
+
+    # ---- device-resident leg ----
+    for _ in range(max(3, args.warmup)):
+        s = step_resident()
+    units_step, trials_step = units_of(ba, host)
+    if sharded:
+        units_job = units_step           # one problem, every rank reports the same trials
+    else:
+        units_job = sum_over_ranks(units_step)
+    clocks = ClockSampler(local)
+    launches0 = ba.kernel_launches()
+    barrier()
+    clocks.start()
+    t_wall0 = time.perf_counter()
+    dev_ms = 0.0
+    for _ in range(args.steps):
+        s = step_resident()
+        dev_ms += s.device_ms
+    barrier()
+    wall_s = time.perf_counter() - t_wall0
+    clk = clocks.stop()
+    launches = ba.kernel_launches() - launches0
+    dev_ms = max_over_ranks(dev_ms)
+    ms_per_step = dev_ms / args.steps
+    value = units_job / (ms_per_step * 1e-3)
+    lm_trials_job = trials_step if sharded else sum_over_ranks(float(trials_step))
+
+    # ---- kernel-by-kernel pass for the roofline (not part of any reported throughput) ----
+    ba.reset_state()
+    ba.set_kernel_timing(True)
+    ba.optimize_resident(args.lm_iters)
+    ktimes = ba.kernel_times()
+    ba.set_kernel_timing(False)
+    ktimes = {k: v for k, v in ktimes.items() if k not in ("state_init", "cam_rt", "lm_init", "gather_current")}
+    roof = roofline(ktimes, trials_step / nprob, (No, Np, Nc, Nblocks))
+    A_iter = roof["algorithmic_bytes_per_lm_iteration"]
+    roof["iteration"] = {"achieved": A_iter * (trials_step / nprob) / (ms_per_step * 1e-3) / 1e9,
+                         "frac": A_iter * (trials_step / nprob) / (ms_per_step * 1e-3) / 1e9 / roof["peak"],
+                         "note": "whole LM loop incl. the reduced-system solve: A_iter x trials / device time"}
+
+    # ---- end-to-end leg: host buffers in, refined poses / points out, every step ----
+    h2d = sum(host[k].nbytes for k in ("poses_init", "points_init", "edge_pose", "edge_point", "edge_uv"))
+    d2h = host["poses_init"].nbytes + host["points_init"].nbytes
+    e2e_steps = 0 if args.no_e2e else args.steps
+    for _ in range(0 if args.no_e2e else 2):
+        set_problem(ba, host)
+        ba.Optimize(args.lm_iters)
+    barrier()
+    t0 = time.perf_counter()
+    loss = None
+    for _ in range(e2e_steps):
+        set_problem(ba, host)
+        s_e2e = ba.Optimize(args.lm_iters)
+        loss = s_e2e.final_cost  # the step's result, read on the host
+    barrier()
+    e2e_s = max_over_ranks(time.perf_counter() - t0)
+    e2e_value = units_job * e2e_steps / e2e_s if e2e_steps else None
+    loss = loss if e2e_steps else None
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
+        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong" if sharded else "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {
+            "workload": args.workload, "description": WORKLOADS[args.workload], "lm_iterations": args.lm_iters,
+            "problems_per_gpu": nprob, "observations_per_gpu": No, "points_per_gpu": Np, "poses_per_gpu": Nc,
+            "parallelism": ("point-sharded x%d + fp64 NCCL allreduce" % world) if sharded else ("replicas x%d" % world),
+            "l2": "flushed between steps (256 MiB write)" if flush is not None else "working set larger than L2 (126 MB)",
+        },
+        "lm_iters_per_sec": lm_trials_job / (ms_per_step * 1e-3),
+        "lm_trials_per_step": lm_trials_job, "final_cost": s.final_cost,
+        "wall_ms_per_step": 1e3 * wall_s / args.steps,
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "ms_per_step": 1e3 * e2e_s / max(1, e2e_steps), "final_cost": loss},
+        "gpu_launches": int(launches), "clocks": clk, "roofline": roof,
+    }
+    if rank == 0 and not args.no_others and world == 1:
+        line["others"] = others(vb, args, local)
+    if rank == 0 and not args.no_cpu:
+        line["cpu_baseline"] = {k: v for k, v in cpu_leg(vb, args.workload, args.lm_iters, args.cpu_sample_s, args.windows).items()
+                                if k in ("value", "unit", "cores", "kind", "sample")}
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def others(vb, args, device):
+    """device-resident numbers of the other single-GPU configurations (parity-test cases; context only)"""
+    out = {}
+    for name in ("c1", "c2", "c3"):
+        if name == args.workload:
+            continue
+        try:
+            probs, huber = make_workload(vb, name, 0, 0)
+            b = vb.batch_problems(probs)
+            ba = make_adjuster(vb, b, huber, device)
+            set_problem(ba, b)
+            ba.upload()
+            for _ in range(3):
+                ba.reset_state()
+                s = ba.optimize_resident(args.lm_iters)
+            ms = []
+            for _ in range(5):
+                ba.reset_state()
+                ms.append(ba.optimize_resident(args.lm_iters).device_ms)
+            m = float(np.median(ms))
+            out[name] = {"value": len(b["edge_pose"]) * s.trials / (m * 1e-3), "unit": UNIT, "ms_per_step": m,
+                         "lm_iters_per_sec": s.trials / (m * 1e-3), "observations": len(b["edge_pose"]),
+                         "final_cost": s.final_cost, "note": "device-resident, L2 not flushed"}
+            ba.close()
+        except Exception as e:  # context only: never fail the headline because of it
+            out[name] = {"error": str(e)}
+    return out
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -44,3 +44,39 @@ def run(cfg_id, iters=10, **kw):
 if __name__ == "__main__":
     for c in [int(x) for x in sys.argv[1:]] or [1, 2]:
         run(c)
+
+
+def run_batched(nwin, iters=10, check=4):
+    t = time.time()
+    probs = [vb.synth_config(5, w) for w in range(nwin)]
+    b = vb.batch_problems(probs)
+    print("batched", nwin, "windows; gen", time.time() - t, "s; edges", len(b["edge_pose"]))
+    ba = vb.BundleAdjuster(len(b["points_init"]), len(b["poses_init"]), len(b["edge_pose"]))
+    t = time.time()
+    ba.set_problem_batched(b["pose_off"], b["point_off"], b["edge_off"], b["poses_init"], b["points_init"], b["edge_pose"], b["edge_point"], b["edge_uv"])
+    t1 = time.time(); ba.upload(); t2 = time.time()
+    print("  set_problem", t1 - t, "upload", t2 - t1)
+    s = ba.Optimize(iters)
+    print("  optimize", s.as_dict(), "wall", time.time() - t2)
+    sums = ba.problem_summaries()
+    poses, pts = ba.poses(), ba.points()
+    c = orc.cfg(threads=8)
+    for w in range(min(check, nwin)):
+        p = probs[w]
+        po, pt, fc, it, so = orc.optimize(c, p["poses_init"], p["points_init"], p["edge_pose"], p["edge_point"], p["edge_uv"], iters)
+        gp = poses[b["pose_off"][w]:b["pose_off"][w + 1]]
+        gq = pts[b["point_off"][w]:b["point_off"][w + 1]]
+        print("   win", w, "cost rel", abs(sums[w].final_cost - fc) / fc, "pose", np.abs(gp - po).max(), "pt", np.abs(gq - pt).max(), "trials", sums[w].trials, sum(x.trials for x in so))
+    ba.reset_state(); ba.set_kernel_timing(True)
+    s2 = ba.optimize_resident(iters)
+    kt = ba.kernel_times()
+    print("  resident timed", s2.device_ms, "ms;", {k: (v[0], round(v[1], 3)) for k, v in kt.items()})
+    ba.set_kernel_timing(False)
+    for _ in range(3):
+        ba.reset_state(); s3 = ba.optimize_resident(iters)
+    ne = len(b["edge_pose"])
+    print("  resident graph", s3.device_ms, "ms ->", ne * s3.trials / nwin / (s3.device_ms * 1e-3) / 1e9, "G obs/s; trials", s3.trials)
+
+
+if __name__ == "__main__" and os.environ.get("BATCH"):
+    run_batched(int(os.environ["BATCH"]))
