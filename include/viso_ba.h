@@ -139,6 +139,11 @@ int32_t viso_ba_set_huber_delta(viso_ba* h, double delta);
 int32_t viso_ba_nccl_unique_id(void* out128);
 int32_t viso_ba_shard_init(viso_ba* h, int32_t rank, int32_t n_ranks, const void* nccl_id128);
 
+/* the partition viso_ba_shard_init uses (host-only, needs no GPU): rank r owns the points
+ * [out_bounds[r], out_bounds[r+1]); contiguous ranges balanced on edge count */
+int32_t viso_ba_shard_point_ranges(int64_t n_points, int64_t n_edges, const int32_t* edge_point,
+                                   int32_t n_ranks, int64_t* out_bounds);
+
 /* run on a caller-provided cudaStream_t (NULL: the handle's own stream) */
 int32_t viso_ba_set_stream(viso_ba* h, void* cuda_stream);
 

@@ -5,5 +5,5 @@ include/viso_ba.h) and api.py (ctypes binding + the Python mirror of the referen
 """
 from .api import (  # noqa: F401
     BundleAdjuster, Config, IterStats, KernelTime, Summary, SynthSpec, VisoBaError, LIB_PATH, SYMBOLS,
-    batch_problems, default_config, load_library, nccl_unique_id, synth_config, synth_preset, synth_problem,
+    batch_problems, default_config, load_library, nccl_unique_id, shard_point_ranges, synth_config, synth_preset, synth_problem,
 )

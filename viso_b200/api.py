@@ -95,6 +95,7 @@ SYMBOLS = {
     "viso_ba_set_huber_delta": (C.c_int32, [_P, C.c_double]),
     "viso_ba_nccl_unique_id": (C.c_int32, [_P]),
     "viso_ba_shard_init": (C.c_int32, [_P, C.c_int32, C.c_int32, _P]),
+    "viso_ba_shard_point_ranges": (C.c_int32, [C.c_int64, C.c_int64, _I32, C.c_int32, _I64]),
     "viso_ba_set_stream": (C.c_int32, [_P, _P]),
     "viso_ba_upload": (C.c_int32, [_P]),
     "viso_ba_optimize": (C.c_int32, [_P, C.c_int32, C.POINTER(IterStats), C.POINTER(Summary)]),
@@ -352,6 +353,17 @@ def nccl_unique_id():
     if st != OK:
         raise VisoBaError(st, "ncclGetUniqueId failed (libnccl.so.2 not loadable?)")
     return buf.raw
+
+
+def shard_point_ranges(n_points, edge_point, n_ranks):
+    """the contiguous point ranges a sharded handle assigns to the ranks (host-only)"""
+    edge_point = _c(edge_point, np.int32)
+    out = np.zeros(n_ranks + 1, np.int64)
+    st = load_library().viso_ba_shard_point_ranges(int(n_points), edge_point.size, edge_point.ctypes.data_as(_I32),
+                                                   int(n_ranks), out.ctypes.data_as(_I64))
+    if st != OK:
+        raise VisoBaError(st, "viso_ba_shard_point_ranges failed")
+    return out
 
 
 # ---- synthetic problems (SURVEY 8d); host-only, needs no GPU ------------------------------------

@@ -533,6 +533,18 @@ struct Built {
     int32_t n_blocks = 0, max_n = 0;
 };
 
+// rank r owns points [out[r], out[r+1]): the first point whose CSR offset reaches r/n of the edges
+template <typename T> void shard_bounds(const T* pt_ptr, int64_t Np, int64_t Ne, int n_ranks, int64_t* out)
+{
+    out[0] = 0;
+    out[n_ranks] = Np;
+    for (int r = 1; r < n_ranks; ++r) {
+        const int64_t target = Ne * r / n_ranks;
+        const T* it = std::lower_bound(pt_ptr, pt_ptr + Np + 1, (T)target);
+        out[r] = std::min<int64_t>(Np, it - pt_ptr);
+    }
+}
+
 int32_t build_structure(viso_ba* h, Built& b)
 {
     const int64_t Nc = (int64_t)h->poses.size() / 7, Np = (int64_t)h->points.size() / 3;
@@ -608,12 +620,10 @@ int32_t build_structure(viso_ba* h, Built& b)
     }
 
     // ---- this rank's point range (sharding: contiguous points, balanced on edge count) ----
-    h->shard_pt.assign((size_t)h->n_ranks + 1, (int32_t)Np);
-    h->shard_pt[0] = 0;
-    for (int r = 1; r < h->n_ranks; ++r) {
-        const int64_t target = Ne * r / h->n_ranks;
-        const auto it = std::lower_bound(b.pt_ptr.begin(), b.pt_ptr.end(), (int32_t)target);
-        h->shard_pt[(size_t)r] = (int32_t)std::min<int64_t>(Np, it - b.pt_ptr.begin());
+    {
+        std::vector<int64_t> bounds((size_t)h->n_ranks + 1);
+        shard_bounds(b.pt_ptr.data(), Np, Ne, h->n_ranks, bounds.data());
+        h->shard_pt.assign(bounds.begin(), bounds.end());
     }
     const int32_t pt_begin = h->shard_pt[(size_t)h->rank], pt_end = h->shard_pt[(size_t)h->rank + 1];
 
@@ -1227,6 +1237,20 @@ extern "C" int32_t viso_ba_nccl_unique_id(void* out128)
     NcclApi* api = nccl_api();
     if (!api) return VISO_BA_ERR_NCCL;
     return api->GetUniqueId(out128) == 0 ? VISO_BA_OK : VISO_BA_ERR_NCCL;
+}
+
+extern "C" int32_t viso_ba_shard_point_ranges(int64_t n_points, int64_t n_edges, const int32_t* edge_point,
+    int32_t n_ranks, int64_t* out)
+{
+    if (n_points < 0 || n_edges < 0 || n_ranks < 1 || !out || (n_edges && !edge_point)) return VISO_BA_ERR_ARG;
+    std::vector<int64_t> ptr((size_t)n_points + 1, 0);
+    for (int64_t e = 0; e < n_edges; ++e) {
+        if (edge_point[e] < 0 || edge_point[e] >= n_points) return VISO_BA_ERR_INDEX;
+        ptr[(size_t)edge_point[e] + 1]++;
+    }
+    for (int64_t p = 0; p < n_points; ++p) ptr[(size_t)p + 1] += ptr[(size_t)p];
+    shard_bounds(ptr.data(), n_points, n_edges, n_ranks, out);
+    return VISO_BA_OK;
 }
 
 extern "C" int32_t viso_ba_shard_init(viso_ba* h, int32_t rank, int32_t n_ranks, const void* id128)
