@@ -239,8 +239,8 @@ def algorithmic_bytes(No, Np, Nc, Nblocks):
 
 
 # which pass each kernel belongs to (kernels of one pass are timed together)
-PASS_OF = {"linearize": "L", "schur_blocks": "L", "block_finalize": "L", "window_linearize_schur": "L",
-           "update": "BC", "solve_small": None, "solve_large": None, "reduce": None, "decide": None}
+PASS_OF = {"linearize": "L", "schur_blocks": "L", "block_finalize": "L", "win_linearize_schur": "L", "win_finalize": "L",
+           "update": "BC", "win_update": "BC", "solve_small": None, "solve_large": None, "reduce": None, "decide": None}
 
 
 def measured_peak():

@@ -64,6 +64,11 @@ typedef struct {
     int32_t fix_first_pose;/* gauge: fix the first pose of every problem (viso keeps frame 0
                               at identity, keyframe.h:34-35); default 1                  */
     int32_t use_cuda_graph;/* replay one captured LM trial instead of re-launching; default 1 */
+    int32_t path;          /* which kernels linearise: 0 = auto (default), 1 = window fast path
+                              whenever eligible (every problem <= 32 keyframes and <= 27 free
+                              poses, no duplicate edges, not sharded), 2 = general pair-list
+                              path.  Auto takes the window path when its tiles fill the GPU.   */
+    int32_t reserved;
 } viso_ba_config;
 
 /* per outer LM iteration (single-problem handles) */

@@ -13,6 +13,9 @@ pytestmark = pytest.mark.gpu
 
 COST_RTOL, POSE_ATOL, POINT_ATOL = 1e-5, 1e-6, 1e-5  # BASELINE.json north_star
 GOLDEN = sorted(glob.glob(os.path.join(os.path.dirname(__file__), "golden", "*.npz")))
+# problems of <= 32 keyframes take the window fast path (tile kernels, ba_window.cu) unless told
+# otherwise; the tests that matter run both it and the general pair-list path
+BOTH_PATHS = pytest.mark.parametrize("path", [1, 2], ids=["window", "general"])
 
 
 def _adjuster(vb, p, **cfg):
@@ -35,6 +38,8 @@ def _check_against_oracle(vb, oracle, p, iters, huber=0.0, tight=True, threads=8
     ba = _adjuster(vb, p, huber_delta=huber, **cfg)
     c = oracle.cfg(K=p["K"], huber_delta=huber, threads=threads, tau=cfg.get("lm_tau", 1e-5))
     s, stats = ba.Optimize(iters, with_stats=True)
+    if cfg.get("path") in (1, 2):
+        assert ("win_update" in _kernel_names(vb, p, huber, cfg)) == (cfg["path"] == 1)
     poses, points, fc, it, ostats = oracle.optimize(c, *_args(p), iters)
     assert s.iterations == it
     assert [x.trials for x in stats] == [x.trials for x in ostats]  # identical accept / reject decisions
@@ -46,23 +51,34 @@ def _check_against_oracle(vb, oracle, p, iters, huber=0.0, tight=True, threads=8
     return ba, s
 
 
-def test_c1_window_l2_matches_oracle(vb, oracle):
+def _kernel_names(vb, p, huber, cfg):
+    """which kernels a handle with this configuration launches (kernel timing on, one iteration)"""
+    ba = _adjuster(vb, p, huber_delta=huber, **cfg)
+    ba.set_kernel_timing(True)
+    ba.Optimize(1)
+    return set(ba.kernel_times())
+
+
+@BOTH_PATHS
+def test_c1_window_l2_matches_oracle(vb, oracle, path):
     """BASELINE configs[0]: 10 keyframes, 2k points, ~15k observations, 10 LM iterations"""
     p = vb.synth_config(1)
-    ba, s = _check_against_oracle(vb, oracle, p, 10)
+    ba, s = _check_against_oracle(vb, oracle, p, 10, path=path)
     assert s.trials == 10 and s.terminated == 0
     assert ba.kernel_launches() > 0
 
 
-def test_c1_window_huber_matches_oracle(vb, oracle):
+@BOTH_PATHS
+def test_c1_window_huber_matches_oracle(vb, oracle, path):
     p = vb.synth_config(1, outlier_frac=0.05)
-    _check_against_oracle(vb, oracle, p, 10, huber=2.0)
+    _check_against_oracle(vb, oracle, p, 10, huber=2.0, path=path)
 
 
-def test_c2_sliding_window_huber_matches_oracle(vb, oracle):
+@BOTH_PATHS
+def test_c2_sliding_window_huber_matches_oracle(vb, oracle, path):
     """BASELINE configs[1]: 20 keyframes, 10k points, Huber"""
     p = vb.synth_config(2)
-    _check_against_oracle(vb, oracle, p, 10, huber=2.0)
+    _check_against_oracle(vb, oracle, p, 10, huber=2.0, path=path)
 
 
 def test_c3_global_ba_matches_oracle(vb, oracle):
@@ -77,11 +93,12 @@ def test_mid_size_reduced_system_uses_large_solver(vb, oracle):
     _check_against_oracle(vb, oracle, p, 6)
 
 
+@pytest.mark.parametrize("kpath", [1, 2], ids=["window", "general"])
 @pytest.mark.parametrize("path", GOLDEN, ids=[os.path.basename(x)[:-4] for x in GOLDEN])
-def test_golden_vectors(vb, path):
+def test_golden_vectors(vb, path, kpath):
     g = np.load(path)
     ba = vb.BundleAdjuster(len(g["points_init"]), len(g["poses_init"]), len(g["edge_pose"]),
-                           huber_delta=float(g["huber_delta"]), lm_tau=float(g["tau"]))
+                           huber_delta=float(g["huber_delta"]), lm_tau=float(g["tau"]), path=kpath)
     ba.SetIntrinsics(*g["K"])
     ba.set_problem(g["poses_init"], g["points_init"], g["edge_pose"], g["edge_point"], g["edge_uv"])
     for f in g["fixed"]:
@@ -99,17 +116,19 @@ def test_golden_vectors(vb, path):
     assert np.abs(ba.points() - g["points_final"]).max() < (1e-7 if tight else POINT_ATOL)
 
 
-def test_rejected_trials_follow_the_oracle(vb, oracle):
+@BOTH_PATHS
+def test_rejected_trials_follow_the_oracle(vb, oracle, path):
     """far start, tiny damping: LM has to reject steps; GPU and oracle must take the same decisions"""
     p = vb.synth_config(1, n_poses=5, n_points=50, target_edges=200, seed=0x601D0006, point_sigma=0.25,
                         pose_rot_sigma=0.08, pose_trans_sigma=0.15)
-    ba, s = _check_against_oracle(vb, oracle, p, 8, tight=False, lm_tau=1e-8)
+    ba, s = _check_against_oracle(vb, oracle, p, 8, tight=False, lm_tau=1e-8, path=path)
     assert s.trials > 8
 
 
-def test_reduced_system_and_cost_match_oracle(vb, oracle):
+@BOTH_PATHS
+def test_reduced_system_and_cost_match_oracle(vb, oracle, path):
     p = vb.synth_config(2)
-    ba = _adjuster(vb, p, huber_delta=2.0)
+    ba = _adjuster(vb, p, huber_delta=2.0, path=path)
     c = oracle.cfg(huber_delta=2.0, threads=8)
     assert ba.eval_cost() == pytest.approx(oracle.cost(c, *_args(p)), rel=1e-13)
     for lam in (0.0, 1.0, 1e4):
@@ -172,11 +191,12 @@ def test_fixed_poses_and_gauge(vb, oracle):
     assert s2.final_cost == pytest.approx(fc2, rel=1e-8)
 
 
-def test_batched_windows_match_per_window_oracle(vb, oracle):
+@BOTH_PATHS
+def test_batched_windows_match_per_window_oracle(vb, oracle, path):
     """BASELINE configs[4] in small: independent 10-keyframe windows, each with its own LM state"""
     probs = [vb.synth_config(5, w, n_points=300 + 40 * w, target_edges=2200 + 300 * w) for w in range(6)]
     b = vb.batch_problems(probs)
-    ba = vb.BundleAdjuster(len(b["points_init"]), len(b["poses_init"]), len(b["edge_pose"]))
+    ba = vb.BundleAdjuster(len(b["points_init"]), len(b["poses_init"]), len(b["edge_pose"]), path=path)
     ba.set_problem_batched(b["pose_off"], b["point_off"], b["edge_off"], b["poses_init"], b["points_init"],
                            b["edge_pose"], b["edge_point"], b["edge_uv"])
     s = ba.Optimize(7)
@@ -192,12 +212,14 @@ def test_batched_windows_match_per_window_oracle(vb, oracle):
     assert s.final_cost == pytest.approx(total, rel=1e-12)
 
 
-def test_batched_windows_with_diverging_trial_counts(vb, oracle):
+@BOTH_PATHS
+def test_batched_windows_with_diverging_trial_counts(vb, oracle, path):
     """windows that need different numbers of trials must not disturb each other"""
     kw = dict(n_poses=5, n_points=50, target_edges=200, point_sigma=0.25, pose_rot_sigma=0.08, pose_trans_sigma=0.15)
     probs = [vb.synth_config(1, seed=0x601D0004 + i, **kw) for i in range(5)]
     b = vb.batch_problems(probs)
-    ba = vb.BundleAdjuster(len(b["points_init"]), len(b["poses_init"]), len(b["edge_pose"]), lm_tau=1e-8)
+    ba = vb.BundleAdjuster(len(b["points_init"]), len(b["poses_init"]), len(b["edge_pose"]), lm_tau=1e-8,
+                           path=path)
     ba.set_problem_batched(b["pose_off"], b["point_off"], b["edge_off"], b["poses_init"], b["points_init"],
                            b["edge_pose"], b["edge_point"], b["edge_uv"])
     ba.Optimize(8)
@@ -305,3 +327,34 @@ def test_degenerate_inputs(vb):
     with pytest.raises(vb.VisoBaError) as e:
         vb.BundleAdjuster().Optimize(1)
     assert e.value.status == 7
+
+
+def test_window_path_ragged_tiles_and_duplicate_fallback(vb, oracle):
+    """tile edge cases of the window path: a tile boundary inside a problem, problems smaller than
+    one tile, 32 keyframes (the mask is full), and a duplicate (point, pose) edge, which must fall
+    back to the general path and still match the oracle"""
+    p32 = vb.synth_config(1, n_poses=28, n_points=500, target_edges=9000, seed=77)
+    ba, _ = _check_against_oracle(vb, oracle, p32, 5, path=1)
+    tiny = vb.synth_config(1, n_poses=3, n_points=9, target_edges=24, seed=78)
+    _check_against_oracle(vb, oracle, tiny, 5, path=1)
+    dup = dict(tiny)
+    dup["edge_pose"] = np.concatenate([tiny["edge_pose"], tiny["edge_pose"][:1]])
+    dup["edge_point"] = np.concatenate([tiny["edge_point"], tiny["edge_point"][:1]])
+    dup["edge_uv"] = np.concatenate([tiny["edge_uv"], tiny["edge_uv"][:1] + 0.5])
+    ba = _adjuster(vb, dup, path=1)
+    s = ba.Optimize(5)
+    _, _, fc, _, _ = oracle.optimize(oracle.cfg(), *_args(dup), 5)
+    assert s.final_cost == pytest.approx(fc, rel=1e-10)
+    ba.set_kernel_timing(True)
+    ba.reset_state()
+    ba.optimize_resident(1)
+    assert "schur_blocks" in ba.kernel_times()  # the pair-list kernels ran
+
+
+def test_window_and_general_paths_agree(vb):
+    p = vb.synth_config(2)
+    a, b = _adjuster(vb, p, huber_delta=2.0, path=1), _adjuster(vb, p, huber_delta=2.0, path=2)
+    sa, sb = a.Optimize(10), b.Optimize(10)
+    assert sa.trials == sb.trials
+    assert sa.final_cost == pytest.approx(sb.final_cost, rel=1e-11)
+    assert np.abs(a.poses() - b.poses()).max() < 1e-10 and np.abs(a.points() - b.points()).max() < 1e-9

@@ -23,6 +23,21 @@ constexpr int kPtInfoDoubles = 9; // per-point record
 constexpr int kItemPart = 42;     // 36 block entries + 6 rhs entries per work item
 constexpr int kChunkPoints = 1024;
 constexpr int kSmallMaxN = 162; // dense per-problem solve in shared memory up to 27 free poses
+// window fast path (ba_window.cu): one CTA per tile of consecutive points of one problem
+constexpr int kWinThreads = 128;
+constexpr int kWinObsCap = 640; // observations per tile (their records live in shared memory)
+constexpr int kWinPtCap = 88;   // points per tile
+constexpr int kWinMaxCams = 32; // keyframes per problem (visibility mask is 32 bits)
+constexpr int kWinAutoMinTiles = 2 * 148; // "auto": fewer tiles than this cannot fill the GPU -> general path
+
+struct WinTile { // one CTA's share of a problem: consecutive points and all their observations
+    int32_t prob, p0, np, o0, no, cam0, ncam, nf;
+    int64_t part_off;   // offset (doubles) of this tile's partial S blocks in tile_part
+    int64_t blkptr_off; // first of the tile's nf (nf + 1) / 2 + 1 entries of win_blkptr
+    int64_t list_off;   // first of the tile's entries of win_pairs
+    int64_t pad;
+};
+static_assert(sizeof(WinTile) == 64, "WinTile is read as four int4");
 
 struct LmState { // one per problem, lives in device memory; g2o OptimizationAlgorithmLevenberg state
     double lambda;
@@ -75,6 +90,20 @@ struct DevProblem {
     const int32_t* block_cam;  // [n_blocks] global cam of the block row if diagonal else -1
     const int4* chunks;        // {problem, pt_begin, pt_end, 0}
     const int32_t* prob_chunk_ptr; // [B+1]
+    // window fast path: tiles, visibility masks, per-observation meta word
+    int32_t n_tiles;
+    const WinTile* tiles;
+    const uint32_t* pt_mask;       // [Np] bit c: keyframe c of the point's problem observes it
+    // observations once more, tile by tile and KEYFRAME-major inside a tile (slot order)
+    const uint32_t* win_meta;      // [No] local keyframe | local point << 8
+    const float2* win_uv;          // [No]
+    const uint16_t* win_slot;      // [No] point-major observation -> slot inside its tile
+    const uint32_t* win_blkptr;    // per tile: offsets of each S block's pair list (relative to list_off)
+    const uint32_t* win_pairs;     // slot_a | slot_b << 16, per tile and S block, points in order
+    const int32_t* prob_tile_ptr;  // [B+1]
+    const int64_t* prob_part_off;  // [B+1] offset (doubles) of the problem's tile partials
+    double* tile_part;             // per tile: [nblocks of its problem][kItemPart]
+    double* tile_sums;             // [n_tiles][2]  {cost, scale} of the tile
     // state
     double* pts[2];
     double* pose[2];
@@ -122,6 +151,12 @@ int launch_solve_large(const DevProblem& P, const LargeSolve& L, cudaStream_t st
 int launch_update(const DevProblem& P, cudaStream_t st);
 int launch_decide(const DevProblem& P, cudaStream_t st);
 int launch_eval_cost(const DevProblem& P, cudaStream_t st); // cost of current state -> cost_pt
+// window fast path
+size_t win_shared_bytes();
+int launch_win_linearize_schur(const DevProblem& P, int init_pass, double lambda_override, cudaStream_t st);
+int launch_win_finalize(const DevProblem& P, int init_pass, double lambda_override, cudaStream_t st);
+int launch_win_update(const DevProblem& P, cudaStream_t st);
+int launch_win_prob_sums(const DevProblem& P, int even_if_inactive, cudaStream_t st);
 
 } // namespace visoba
 #endif

@@ -1,0 +1,602 @@
+// ba_window.cu — the window fast path: sliding-window / batched-window bundle adjustment
+// (BASELINE configs 1, 2 and 5) where every problem has at most 32 keyframes.
+//
+// Same math as ba_kernels.cu (reference citations there and in ba_math.cuh), different data
+// movement.  A problem's points are cut into TILES of consecutive points (<= kWinPtCap points,
+// <= kWinObsCap observations).  One CTA owns one tile and keeps every per-observation
+// quantity of the tile in shared memory, so that per LM trial HBM sees only
+//     linearize_schur : observations (12 B) + points (24 B) in, per-point 72 B + per-tile
+//                       partial reduced-system blocks out
+//     update          : observations + points + per-point 72 B in, points out
+// and no per-observation record, no materialised 6x3 cross block and no pair list exists in
+// global memory.  Which observations of a point meet in which S block is derived on the fly
+// from a 32-bit visibility mask per point (bit c = keyframe c of the window sees the point).
+//
+// Shared-memory layout of the records: structure of arrays (six 16-byte chunks per
+// observation), observations ordered KEYFRAME-major inside the tile.  The pair phase of block
+// (I, J) then reads nearly consecutive slots of keyframe I and of keyframe J, which keeps the
+// 16-byte gathers of a quarter warp on distinct banks (point-major order made them collide
+// 2.3-fold, and the pair phase is bound by shared-memory wavefronts, not by the FP64 pipe).
+//
+// Scatter-free and deterministic: a sub-warp of 8 lanes owns one 6x6 block of S at a time,
+// every lane keeps 36 + 6 fp64 accumulators in registers over "its" observation pairs, the 8
+// lanes are folded with a fixed butterfly, and the per-tile partial blocks are summed in tile
+// order by k_win_finalize.  No atomics on floating-point data anywhere.
+#include "ba_math.cuh"
+
+namespace visoba {
+
+namespace {
+
+constexpr int kSub = 8;                         // lanes per S block
+constexpr int kSubsPerCta = kWinThreads / kSub; // blocks in flight per CTA
+constexpr int kWarps = kWinThreads / 32;
+constexpr int kObsPerThread = (kWinObsCap + kWinThreads - 1) / kWinThreads;
+constexpr int kPtStride = kWinPtCap + 1; // odd stride: the (point, coordinate) transposes stay conflict-free
+
+__host__ __device__ constexpr size_t align16(size_t x) { return (x + 15) & ~(size_t)15; }
+
+// ---- shared memory of k_win_linearize_schur (byte offsets) ----
+constexpr size_t kLsRec = 0;                                                   // double2 [6][kWinObsCap]
+constexpr size_t kLsPt = kLsRec + 6 * sizeof(double2) * kWinObsCap;            // double [3][kPtStride]
+constexpr size_t kLsInfo = kLsPt + sizeof(double) * 3 * kPtStride;             // double [9][kPtStride]
+constexpr size_t kLsRt = kLsPt + align16(sizeof(double) * 12 * kPtStride);
+constexpr int kMaxBlkPtr = (kSmallMaxN / 6) * (kSmallMaxN / 6 + 1) / 2 + 1;
+constexpr size_t kLsBlkPtr = kLsRt + sizeof(double) * 12 * kWinMaxCams;        // u32 [kMaxBlkPtr]
+constexpr size_t kLsObs0 = kLsBlkPtr + align16(sizeof(unsigned) * kMaxBlkPtr); // u16 [kWinPtCap + 1]
+constexpr size_t kLsSlot = kLsObs0 + align16(sizeof(unsigned short) * (kWinPtCap + 1)); // u16 [kWinObsCap]
+constexpr size_t kLsRed = kLsSlot + align16(sizeof(unsigned short) * kWinObsCap);       // double [kWarps]
+constexpr size_t kLsBytes = kLsRed + sizeof(double) * kWarps;
+
+// ---- shared memory of k_win_update ----
+constexpr size_t kUsTmp = 0;                                                   // double2 [2][kWinObsCap]
+constexpr size_t kUsPt = kUsTmp + 2 * sizeof(double2) * kWinObsCap;            // double [3][kPtStride]
+constexpr size_t kUsInfo = kUsPt + sizeof(double) * 3 * kPtStride;             // double [9][kPtStride]
+constexpr size_t kUsRt = align16(kUsInfo + sizeof(double) * 9 * kPtStride);    // double [kWinMaxCams][12] current
+constexpr size_t kUsRt2 = kUsRt + sizeof(double) * 12 * kWinMaxCams;           // candidate
+constexpr size_t kUsDp = kUsRt2 + sizeof(double) * 12 * kWinMaxCams;           // double [kWinMaxCams][6]
+constexpr size_t kUsObs0 = kUsDp + sizeof(double) * 6 * kWinMaxCams;           // u16 [kWinPtCap + 1]
+constexpr size_t kUsSlot = kUsObs0 + align16(sizeof(unsigned short) * (kWinPtCap + 1)); // u16 [kWinObsCap]
+constexpr size_t kUsRed = kUsSlot + align16(sizeof(unsigned short) * kWinObsCap);       // double [2][kWarps]
+constexpr size_t kUsBytes = kUsRed + sizeof(double) * 2 * kWarps;
+
+// fixed-shape sum over the CTA: shuffles inside a warp, then the warp totals in warp order
+__device__ __forceinline__ double cta_sum(double v, double* red, int tid)
+{
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
+    if ((tid & 31) == 0) red[tid >> 5] = v;
+    __syncthreads();
+    double s = 0.0;
+#pragma unroll
+    for (int w = 0; w < kWarps; ++w) s += red[w];
+    return s;
+}
+
+__device__ __forceinline__ WinTile load_tile(const DevProblem& P)
+{
+    const int4* src = reinterpret_cast<const int4*>(P.tiles + blockIdx.x);
+    const int4 a = __ldg(src), b = __ldg(src + 1), c = __ldg(src + 2), d = __ldg(src + 3);
+    WinTile t;
+    t.prob = a.x, t.p0 = a.y, t.np = a.z, t.o0 = a.w;
+    t.no = b.x, t.cam0 = b.y, t.ncam = b.z, t.nf = b.w;
+    t.part_off = ((long long)(unsigned)c.x) | ((long long)c.y << 32);
+    t.blkptr_off = ((long long)(unsigned)c.z) | ((long long)c.w << 32);
+    t.list_off = ((long long)(unsigned)d.x) | ((long long)d.y << 32);
+    t.pad = 0;
+    return t;
+}
+
+} // namespace
+
+// ------------------------------------------------------------------------------------------
+// W1 linearize + Schur, one CTA per tile
+//   A1 (thread per observation)  projection, residual, Huber weight, 2x3 point Jacobian
+//   A2 (thread per point)        H_ll, b_l, 3x3 Cholesky of H_ll + lambda I  -> L^-1, L^-1 b_l
+//   A3 (thread per observation)  G~ = F w Jl L^-T,  v~ = F (w r + G zb)
+//   B  (8 lanes per S block)     S_IJ -= Jp_a^T G_a G_b^T Jp_b, S_II += w Jp^T Jp, bs_I -= Jp^T v~
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kWinThreads, 3) k_win_linearize_schur(DevProblem P, int init_pass, double lambda_override)
+{
+    extern __shared__ __align__(16) unsigned char sm[];
+    double2* const rec = reinterpret_cast<double2*>(sm + kLsRec);
+    double* const s_pt = reinterpret_cast<double*>(sm + kLsPt);
+    double* const s_info = reinterpret_cast<double*>(sm + kLsInfo);
+    double* const s_rt = reinterpret_cast<double*>(sm + kLsRt);
+    unsigned int* const s_bp = reinterpret_cast<unsigned int*>(sm + kLsBlkPtr);
+    unsigned short* const s_obs0 = reinterpret_cast<unsigned short*>(sm + kLsObs0);
+    unsigned short* const s_slot = reinterpret_cast<unsigned short*>(sm + kLsSlot);
+    double* const s_red = reinterpret_cast<double*>(sm + kLsRed);
+#define REC(c, o) rec[(c) * kWinObsCap + (o)]
+
+    const int tid = threadIdx.x;
+    const WinTile t = load_tile(P);
+    const LmState& st = P.lm[t.prob];
+    if (!st.active && lambda_override < 0.0) return;
+    const int cur = st.cur;
+    const double lambda = init_pass ? 0.0 : (lambda_override >= 0.0 ? lambda_override : st.lambda);
+
+    // ---- A0: everything the tile needs from HBM, issued at once.  Thread <-> slot: the
+    // observations of the tile in keyframe-major order, so that consecutive threads share the
+    // keyframe (R|t reads broadcast) and touch consecutive record slots (no bank conflicts) ----
+    unsigned int meta[kObsPerThread];
+    float2 uv[kObsPerThread];
+#pragma unroll
+    for (int i = 0; i < kObsPerThread; ++i) {
+        const int o = tid + i * kWinThreads;
+        meta[i] = 0u, uv[i] = make_float2(0.f, 0.f);
+        if (o < t.no) {
+            meta[i] = __ldg(P.win_meta + t.o0 + o);
+            uv[i] = __ldg(P.win_uv + t.o0 + o);
+        }
+    }
+    const int nblk_all = t.nf * (t.nf + 1) / 2;
+    {
+        for (int o = tid; o < t.no; o += kWinThreads) s_slot[o] = __ldg(P.win_slot + t.o0 + o);
+        for (int k = tid; k <= nblk_all; k += kWinThreads) s_bp[k] = __ldg(P.win_blkptr + t.blkptr_off + k);
+        const double* __restrict__ gp = P.pts[cur] + 3 * (size_t)t.p0;
+        for (int i = tid; i < 3 * t.np; i += kWinThreads) {
+            const int p = i / 3, k = i - 3 * p;
+            s_pt[k * kPtStride + p] = gp[i];
+        }
+        const double* __restrict__ grt = P.cam_rt[cur] + 12 * (size_t)t.cam0;
+        for (int i = tid; i < 12 * t.ncam; i += kWinThreads) s_rt[i] = grt[i];
+        for (int p = tid; p <= t.np; p += kWinThreads) s_obs0[p] = (unsigned short)(__ldg(P.pt_ptr + t.p0 + p) - t.o0);
+    }
+    __syncthreads();
+
+    // ---- A1 ----
+    double cost = 0.0;
+#pragma unroll
+    for (int i = 0; i < kObsPerThread; ++i) {
+        const int o = tid + i * kWinThreads;
+        if (o < t.no) {
+            const int c = meta[i] & 0xff, p = (meta[i] >> 8) & 0xff, sl = o;
+            ObsGeom g;
+            obs_geometry(P, s_rt + 12 * c, s_pt[p], s_pt[kPtStride + p], s_pt[2 * kPtStride + p], uv[i], g);
+            cost += g.rho;
+            REC(0, sl) = make_double2(g.xn, g.yn);
+            REC(1, sl) = make_double2(g.iz, g.w);
+            REC(2, sl) = make_double2(g.jl0[0], g.jl0[1]);
+            REC(3, sl) = make_double2(g.jl0[2], g.jl1[0]);
+            REC(4, sl) = make_double2(g.jl1[1], g.jl1[2]);
+            REC(5, sl) = make_double2(g.ru, g.rv);
+        }
+    }
+    if (init_pass) { // cost of the start state: fixed-tree sum of the tile
+        const double c = cta_sum(cost, s_red, tid);
+        if (tid == 0) {
+            P.tile_sums[2 * (size_t)blockIdx.x] = c;
+            P.tile_sums[2 * (size_t)blockIdx.x + 1] = 0.0;
+        }
+    }
+    __syncthreads();
+
+    // ---- A2 ----
+    for (int p = tid; p < t.np; p += kWinThreads) {
+        double h00 = 0, h10 = 0, h11 = 0, h20 = 0, h21 = 0, h22 = 0, b0 = 0, b1 = 0, b2 = 0;
+        for (int o = s_obs0[p]; o < s_obs0[p + 1]; ++o) {
+            const int sl = s_slot[o];
+            const double w = REC(1, sl).y;
+            const double2 j01 = REC(2, sl), j2a = REC(3, sl), jb = REC(4, sl), r = REC(5, sl);
+            const double a0 = j01.x, a1 = j01.y, a2 = j2a.x, c0 = j2a.y, c1 = jb.x, c2 = jb.y;
+            h00 += w * (a0 * a0 + c0 * c0);
+            h10 += w * (a1 * a0 + c1 * c0);
+            h11 += w * (a1 * a1 + c1 * c1);
+            h20 += w * (a2 * a0 + c2 * c0);
+            h21 += w * (a2 * a1 + c2 * c1);
+            h22 += w * (a2 * a2 + c2 * c2);
+            b0 -= w * (a0 * r.x + c0 * r.y);
+            b1 -= w * (a1 * r.x + c1 * r.y);
+            b2 -= w * (a2 * r.x + c2 * r.y);
+        }
+        double i00 = 0, i10 = 0, i11 = 0, i20 = 0, i21 = 0, i22 = 0, z0 = 0, z1 = 0, z2 = 0;
+        if (init_pass) { // g2o computeLambdaInit: point part of max diag(H); max is order-free
+            const double m = fmax(h00, fmax(h11, h22));
+            if (m > 0.0) atomicMax(P.maxdiag_bits + t.prob, (unsigned long long)__double_as_longlong(m));
+        } else {
+            h00 += lambda, h11 += lambda, h22 += lambda;
+            const double l00 = sqrt(h00);
+            i00 = 1.0 / l00;
+            const double l10 = h10 * i00, l20 = h20 * i00;
+            const double l11 = sqrt(h11 - l10 * l10);
+            i11 = 1.0 / l11;
+            const double l21 = (h21 - l20 * l10) * i11;
+            const double l22 = sqrt(h22 - l20 * l20 - l21 * l21);
+            i22 = 1.0 / l22;
+            i10 = -l10 * i00 * i11;
+            i21 = -l21 * i11 * i22;
+            i20 = -(l20 * i00 + l21 * i10) * i22;
+            z0 = i00 * b0;
+            z1 = i10 * b0 + i11 * b1;
+            z2 = i20 * b0 + i21 * b1 + i22 * b2;
+        }
+        const double v[9] = { i00, i10, i11, i20, i21, i22, z0, z1, z2 };
+        double* gi = P.ptinfo + kPtInfoDoubles * (size_t)(t.p0 + p);
+#pragma unroll
+        for (int k = 0; k < 9; ++k) {
+            s_info[k * kPtStride + p] = v[k];
+            gi[k] = v[k];
+        }
+    }
+    __syncthreads();
+
+    // ---- A3 ----
+#pragma unroll
+    for (int i = 0; i < kObsPerThread; ++i) {
+        const int o = tid + i * kWinThreads;
+        if (o < t.no) {
+            const int p = (meta[i] >> 8) & 0xff, sl = o;
+            const double i00 = s_info[p], i10 = s_info[kPtStride + p], i11 = s_info[2 * kPtStride + p];
+            const double i20 = s_info[3 * kPtStride + p], i21 = s_info[4 * kPtStride + p], i22 = s_info[5 * kPtStride + p];
+            const double z0 = s_info[6 * kPtStride + p], z1 = s_info[7 * kPtStride + p], z2 = s_info[8 * kPtStride + p];
+            const double w = REC(1, sl).y;
+            const double2 j01 = REC(2, sl), j2a = REC(3, sl), jb = REC(4, sl), r = REC(5, sl);
+            const double g00 = w * (j01.x * i00);
+            const double g01 = w * (j01.x * i10 + j01.y * i11);
+            const double g02 = w * (j01.x * i20 + j01.y * i21 + j2a.x * i22);
+            const double g10 = w * (j2a.y * i00);
+            const double g11 = w * (j2a.y * i10 + jb.x * i11);
+            const double g12 = w * (j2a.y * i20 + jb.x * i21 + jb.y * i22);
+            const double v0 = w * r.x + g00 * z0 + g01 * z1 + g02 * z2;
+            const double v1 = w * r.y + g10 * z0 + g11 * z1 + g12 * z2;
+            REC(2, sl) = make_double2(P.fx * g00, P.fx * g01);
+            REC(3, sl) = make_double2(P.fx * g02, P.fy * g10);
+            REC(4, sl) = make_double2(P.fy * g11, P.fy * g12);
+            REC(5, sl) = make_double2(P.fx * v0, P.fy * v1);
+        }
+    }
+    __syncthreads();
+
+    // ---- B ----
+    const int l8 = tid & (kSub - 1);
+    const int g = tid / kSub; // sub-warp index inside the CTA
+    const int nf = t.nf;
+    const int nblk = init_pass ? nf : nblk_all; // init pass: diagonal blocks only (H_pp)
+    const double fx2 = P.fx * P.fx, fy2 = P.fy * P.fy;
+    double* part = P.tile_part + t.part_off;
+    const unsigned int* __restrict__ pairs = P.win_pairs + t.list_off;
+    const int npass = (nblk + kSubsPerCta - 1) / kSubsPerCta;
+    for (int pass = 0; pass < npass; ++pass) {
+        // slot -> block: the nf diagonal blocks first, then the strictly lower ones row by row
+        const int slot = pass * kSubsPerCta + g;
+        const bool have = slot < nblk;
+        int I = 0, J = 0;
+        if (have) {
+            if (slot < nf) I = J = slot;
+            else {
+                const int q = slot - nf;
+                I = (int)((sqrtf(8.0f * (float)q + 1.0f) + 1.0f) * 0.5f);
+                while (I * (I - 1) / 2 > q) --I;
+                while ((I + 1) * I / 2 <= q) ++I;
+                J = q - I * (I - 1) / 2;
+            }
+        }
+        const bool diag = I == J;
+        const int blk = I * (I + 1) / 2 + J;
+        // the block's pair list inside this tile (built once at upload): points both keyframes see
+        const int beg = have ? (int)s_bp[blk] : 0;
+        const int cnt = have ? (int)s_bp[blk + 1] - beg : 0;
+        const unsigned int* __restrict__ list = pairs + beg;
+        int maxcnt = cnt;
+        maxcnt = max(maxcnt, __shfl_xor_sync(0xffffffffu, maxcnt, 8));
+        maxcnt = max(maxcnt, __shfl_xor_sync(0xffffffffu, maxcnt, 16));
+        unsigned int pr_next = l8 < cnt ? __ldg(list + l8) : 0u;
+
+        double v[48];
+#pragma unroll
+        for (int i = 0; i < 48; ++i) v[i] = 0.0;
+        for (int i0 = 0; i0 < maxcnt; i0 += kSub) {
+            const int i = i0 + l8;
+            const unsigned int pr = pr_next;
+            pr_next = i + kSub < cnt ? __ldg(list + i + kSub) : 0u; // one round ahead: hides the L2 latency
+            if (i < cnt) {
+                const int oa = pr & 0xffffu, ob = pr >> 16;
+                const double2 a0 = REC(0, oa), a1 = REC(1, oa), a2 = REC(2, oa), a3 = REC(3, oa), a4 = REC(4, oa);
+                const double2 b0 = REC(0, ob), b1 = REC(1, ob), b2 = REC(2, ob), b3 = REC(3, ob), b4 = REC(4, ob);
+                // M = -G~_a G~_b^T  (+ w F^2 on the diagonal block);  G~ = (c2.x c2.y c3.x ; c3.y c4.x c4.y)
+                double m00 = -fma(a2.x, b2.x, fma(a2.y, b2.y, a3.x * b3.x));
+                double m01 = -fma(a2.x, b3.y, fma(a2.y, b4.x, a3.x * b4.y));
+                double m10 = -fma(a3.y, b2.x, fma(a4.x, b2.y, a4.y * b3.x));
+                double m11 = -fma(a3.y, b3.y, fma(a4.x, b4.x, a4.y * b4.y));
+                if (diag) {
+                    m00 = fma(a1.y, fx2, m00);
+                    m11 = fma(a1.y, fy2, m11);
+                }
+                // J~ rows (viso.cpp:653-655 without fx, fy):
+                //   r0 = [iz, 0, -x iz, -x y, 1 + x^2, -y]    r1 = [0, iz, -y iz, -(1 + y^2), x y, x]
+                const double xb = b0.x, yb = b0.y, zb = b1.x;
+                const double bxz = xb * zb, byz = yb * zb, bxy = xb * yb, bxx = fma(xb, xb, 1.0), byy = fma(yb, yb, 1.0);
+                double t0[6], t1[6];
+                t0[0] = m00 * zb, t1[0] = m10 * zb;
+                t0[1] = m01 * zb, t1[1] = m11 * zb;
+                t0[2] = -fma(m00, bxz, m01 * byz), t1[2] = -fma(m10, bxz, m11 * byz);
+                t0[3] = -fma(m00, bxy, m01 * byy), t1[3] = -fma(m10, bxy, m11 * byy);
+                t0[4] = fma(m00, bxx, m01 * bxy), t1[4] = fma(m10, bxx, m11 * bxy);
+                t0[5] = fma(m01, xb, -(m00 * yb)), t1[5] = fma(m11, xb, -(m10 * yb));
+                const double xa = a0.x, ya = a0.y, za = a1.x;
+                const double axz = -(xa * za), ayz = -(ya * za), axy = xa * ya, axx = fma(xa, xa, 1.0), ayy = -fma(ya, ya, 1.0);
+                const double naxy = -axy, nya = -ya;
+#pragma unroll
+                for (int c = 0; c < 6; ++c) {
+                    v[c] = fma(za, t0[c], v[c]);
+                    v[6 + c] = fma(za, t1[c], v[6 + c]);
+                    v[12 + c] = fma(axz, t0[c], fma(ayz, t1[c], v[12 + c]));
+                    v[18 + c] = fma(naxy, t0[c], fma(ayy, t1[c], v[18 + c]));
+                    v[24 + c] = fma(axx, t0[c], fma(axy, t1[c], v[24 + c]));
+                    v[30 + c] = fma(nya, t0[c], fma(xa, t1[c], v[30 + c]));
+                }
+                if (diag) { // rhs: Jp^T v~
+                    const double2 a5 = REC(5, oa);
+                    v[36] = fma(za, a5.x, v[36]);
+                    v[37] = fma(za, a5.y, v[37]);
+                    v[38] = fma(axz, a5.x, fma(ayz, a5.y, v[38]));
+                    v[39] = fma(naxy, a5.x, fma(ayy, a5.y, v[39]));
+                    v[40] = fma(axx, a5.x, fma(axy, a5.y, v[40]));
+                    v[41] = fma(nya, a5.x, fma(xa, a5.y, v[41]));
+                }
+            }
+        }
+        // fold the 8 lanes of the sub-warp: afterwards lane l8 holds entries 6 l8 .. 6 l8 + 5
+#pragma unroll
+        for (int off = 4, n = 24; off >= 1; off >>= 1, n >>= 1) {
+            const bool upper = (l8 & off) != 0;
+#pragma unroll
+            for (int i = 0; i < n; ++i) {
+                const double send = upper ? v[i] : v[i + n];
+                const double keep = upper ? v[i + n] : v[i];
+                v[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+            }
+        }
+        if (have && l8 < 7) {
+            double* out = part + (size_t)blk * kItemPart + 6 * l8;
+#pragma unroll
+            for (int i = 0; i < 6; ++i) out[i] = v[i];
+        }
+    }
+#undef REC
+}
+
+// ------------------------------------------------------------------------------------------
+// W2 finalize: one CTA per problem sums the per-tile partial blocks in tile order, adds lambda on
+// the diagonal (g2o setLambda) and writes S_blk / bs (g2o solves H x = b, b = -J^T r).
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_win_finalize(DevProblem P, int init_pass, double lambda_override)
+{
+    const int b = blockIdx.x;
+    const LmState& st = P.lm[b];
+    if (!st.active && lambda_override < 0.0) return;
+    const double lambda = init_pass ? 0.0 : (lambda_override >= 0.0 ? lambda_override : st.lambda);
+    const int nf = P.prob_nfree[b];
+    const int nblk = nf * (nf + 1) / 2;
+    const int t0 = P.prob_tile_ptr[b], t1 = P.prob_tile_ptr[b + 1];
+    const double* __restrict__ part = P.tile_part + P.prob_part_off[b];
+    const size_t stride = (size_t)nblk * kItemPart;
+    const int tri0 = P.prob_tri0[b];
+    for (int idx = threadIdx.x; idx < nblk * kItemPart; idx += blockDim.x) {
+        const int blk = idx / kItemPart, e = idx - blk * kItemPart;
+        const int cam = P.block_cam[tri0 + blk];
+        if (cam < 0 && (e >= 36 || init_pass)) continue;
+        double s = 0.0;
+        for (int t = 0; t < t1 - t0; ++t) s += part[(size_t)t * stride + idx];
+        if (e < 36) {
+            if (cam >= 0 && (e % 7) == 0) s += lambda;
+            P.S_blk[36 * (size_t)(tri0 + blk) + e] = s;
+        } else {
+            P.bs[6 * (size_t)cam + (e - 36)] = -s;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// W3 update, one CTA per tile: back substitution, candidate points and their robust cost.
+//   U1 (thread per observation)  everything of the observation is RECOMPUTED from the current
+//                                state (cheaper than 96 B/obs of HBM traffic):  t = Jp d_p,
+//                                its share of  sum_a G_a^T Jp_a d_p  and of g2o's computeScale
+//   U2 (thread per point)        d_l = L^-T (zb - sum),  P' = P + d_l
+//   U3 (thread per observation)  robust cost at the candidate state
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kWinThreads, 5) k_win_update(DevProblem P)
+{
+    extern __shared__ __align__(16) unsigned char sm[];
+    double2* const tmp = reinterpret_cast<double2*>(sm + kUsTmp);
+    double* const s_pt = reinterpret_cast<double*>(sm + kUsPt);
+    double* const s_info = reinterpret_cast<double*>(sm + kUsInfo);
+    double* const s_rt = reinterpret_cast<double*>(sm + kUsRt);
+    double* const s_rt2 = reinterpret_cast<double*>(sm + kUsRt2);
+    double* const s_dp = reinterpret_cast<double*>(sm + kUsDp);
+    unsigned short* const s_obs0 = reinterpret_cast<unsigned short*>(sm + kUsObs0);
+    unsigned short* const s_slot = reinterpret_cast<unsigned short*>(sm + kUsSlot);
+    double* const s_red = reinterpret_cast<double*>(sm + kUsRed);
+
+    const int tid = threadIdx.x;
+    const WinTile t = load_tile(P);
+    const LmState& st = P.lm[t.prob];
+    if (!st.active) return;
+    const int cur = st.cur, cand = cur ^ 1;
+    const double lambda = st.lambda;
+
+    unsigned int meta[kObsPerThread];
+    float2 uv[kObsPerThread];
+#pragma unroll
+    for (int i = 0; i < kObsPerThread; ++i) {
+        const int o = tid + i * kWinThreads;
+        meta[i] = 0u, uv[i] = make_float2(0.f, 0.f);
+        if (o < t.no) {
+            meta[i] = __ldg(P.win_meta + t.o0 + o);
+            uv[i] = __ldg(P.win_uv + t.o0 + o);
+        }
+    }
+    {
+        for (int o = tid; o < t.no; o += kWinThreads) s_slot[o] = __ldg(P.win_slot + t.o0 + o);
+        const double* __restrict__ gp = P.pts[cur] + 3 * (size_t)t.p0;
+        for (int i = tid; i < 3 * t.np; i += kWinThreads) {
+            const int p = i / 3, k = i - 3 * p;
+            s_pt[k * kPtStride + p] = gp[i];
+        }
+        const double* __restrict__ gi = P.ptinfo + kPtInfoDoubles * (size_t)t.p0;
+        for (int i = tid; i < 9 * t.np; i += kWinThreads) {
+            const int p = i / 9, k = i - 9 * p;
+            s_info[k * kPtStride + p] = gi[i];
+        }
+        const double* __restrict__ g1 = P.cam_rt[cur] + 12 * (size_t)t.cam0;
+        const double* __restrict__ g2 = P.cam_rt[cand] + 12 * (size_t)t.cam0;
+        for (int i = tid; i < 12 * t.ncam; i += kWinThreads) s_rt[i] = g1[i], s_rt2[i] = g2[i];
+        const double* __restrict__ gd = P.dp + 6 * (size_t)t.cam0;
+        for (int i = tid; i < 6 * t.ncam; i += kWinThreads) s_dp[i] = gd[i];
+        for (int p = tid; p <= t.np; p += kWinThreads) s_obs0[p] = (unsigned short)(__ldg(P.pt_ptr + t.p0 + p) - t.o0);
+    }
+    __syncthreads();
+
+    // ---- U1 ----
+#pragma unroll
+    for (int i = 0; i < kObsPerThread; ++i) {
+        const int o = tid + i * kWinThreads;
+        if (o < t.no) {
+            const int c = meta[i] & 0xff, p = (meta[i] >> 8) & 0xff;
+            ObsGeom g;
+            obs_geometry(P, s_rt + 12 * c, s_pt[p], s_pt[kPtStride + p], s_pt[2 * kPtStride + p], uv[i], g);
+            const double i00 = s_info[p], i10 = s_info[kPtStride + p], i11 = s_info[2 * kPtStride + p];
+            const double i20 = s_info[3 * kPtStride + p], i21 = s_info[4 * kPtStride + p], i22 = s_info[5 * kPtStride + p];
+            const double g00 = P.fx * (g.w * (g.jl0[0] * i00));
+            const double g01 = P.fx * (g.w * (g.jl0[0] * i10 + g.jl0[1] * i11));
+            const double g02 = P.fx * (g.w * (g.jl0[0] * i20 + g.jl0[1] * i21 + g.jl0[2] * i22));
+            const double g10 = P.fy * (g.w * (g.jl1[0] * i00));
+            const double g11 = P.fy * (g.w * (g.jl1[0] * i10 + g.jl1[1] * i11));
+            const double g12 = P.fy * (g.w * (g.jl1[0] * i20 + g.jl1[1] * i21 + g.jl1[2] * i22));
+            double ja0[6], ja1[6];
+            jtilde(g.xn, g.yn, g.iz, ja0, ja1);
+            const double* d = s_dp + 6 * c;
+            double t0 = 0.0, t1 = 0.0;
+#pragma unroll
+            for (int k = 0; k < 6; ++k) {
+                t0 += ja0[k] * d[k];
+                t1 += ja1[k] * d[k];
+            }
+            // pose part of computeScale: d_p . b_p = -sum t~ . (F w r)
+            const double sc = -(t0 * (P.fx * (g.w * g.ru)) + t1 * (P.fy * (g.w * g.rv)));
+            tmp[o] = make_double2(g00 * t0 + g10 * t1, g01 * t0 + g11 * t1);
+            tmp[kWinObsCap + o] = make_double2(g02 * t0 + g12 * t1, sc);
+        }
+    }
+    __syncthreads();
+
+    // ---- U2 ----
+    double scale = 0.0;
+    for (int p = tid; p < t.np; p += kWinThreads) {
+        const double i00 = s_info[p], i10 = s_info[kPtStride + p], i11 = s_info[2 * kPtStride + p];
+        const double i20 = s_info[3 * kPtStride + p], i21 = s_info[4 * kPtStride + p], i22 = s_info[5 * kPtStride + p];
+        const double z0 = s_info[6 * kPtStride + p], z1 = s_info[7 * kPtStride + p], z2 = s_info[8 * kPtStride + p];
+        double y0 = z0, y1 = z1, y2 = z2, sc = 0.0;
+        for (int o = s_obs0[p]; o < s_obs0[p + 1]; ++o) {
+            const int sl = s_slot[o];
+            const double2 q0 = tmp[sl], q1 = tmp[kWinObsCap + sl];
+            y0 -= q0.x;
+            y1 -= q0.y;
+            y2 -= q1.x;
+            sc += q1.y;
+        }
+        const double d0 = i00 * y0 + i10 * y1 + i20 * y2;
+        const double d1 = i11 * y1 + i21 * y2;
+        const double d2 = i22 * y2;
+        sc += y0 * z0 + y1 * z1 + y2 * z2 + lambda * (d0 * d0 + d1 * d1 + d2 * d2);
+        scale += sc;
+        s_pt[p] += d0, s_pt[kPtStride + p] += d1, s_pt[2 * kPtStride + p] += d2;
+    }
+    __syncthreads();
+    { // candidate points out, coalesced
+        double* __restrict__ gp = P.pts[cand] + 3 * (size_t)t.p0;
+        for (int i = tid; i < 3 * t.np; i += kWinThreads) {
+            const int p = i / 3, k = i - 3 * p;
+            gp[i] = s_pt[k * kPtStride + p];
+        }
+    }
+
+    // ---- U3 ----
+    double cost = 0.0;
+#pragma unroll
+    for (int i = 0; i < kObsPerThread; ++i) {
+        const int o = tid + i * kWinThreads;
+        if (o < t.no) {
+            const int c = meta[i] & 0xff, p = (meta[i] >> 8) & 0xff;
+            const double* rt = s_rt2 + 12 * c;
+            const double X = s_pt[p], Y = s_pt[kPtStride + p], Z = s_pt[2 * kPtStride + p];
+            const double x = rt[0] * X + rt[1] * Y + rt[2] * Z + rt[9];
+            const double y = rt[3] * X + rt[4] * Y + rt[5] * Z + rt[10];
+            const double z = rt[6] * X + rt[7] * Y + rt[8] * Z + rt[11];
+            const double iz = 1.0 / z;
+            const double ru = P.fx * (x * iz) + P.cx - (double)uv[i].x;
+            const double rv = P.fy * (y * iz) + P.cy - (double)uv[i].y;
+            double w;
+            cost += huber_rho(ru * ru + rv * rv, P.huber_delta, w);
+        }
+    }
+    const double c = cta_sum(cost, s_red, tid);
+    const double sc = cta_sum(scale, s_red + kWarps, tid);
+    if (tid == 0) {
+        P.tile_sums[2 * (size_t)blockIdx.x] = c;
+        P.tile_sums[2 * (size_t)blockIdx.x + 1] = sc;
+    }
+}
+
+// per-problem totals of the tile sums, in tile order
+__global__ void k_win_prob_sums(DevProblem P, int even_if_inactive)
+{
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= P.n_problems) return;
+    if (!P.lm[b].active && !even_if_inactive) return;
+    double s0 = 0.0, s1 = 0.0;
+    for (int t = P.prob_tile_ptr[b]; t < P.prob_tile_ptr[b + 1]; ++t) {
+        s0 += P.tile_sums[2 * (size_t)t];
+        s1 += P.tile_sums[2 * (size_t)t + 1];
+    }
+    P.prob_sums[2 * (size_t)b] = s0;
+    P.prob_sums[2 * (size_t)b + 1] = s1;
+}
+
+// ------------------------------------------------------------------------------------------
+// launchers
+// ------------------------------------------------------------------------------------------
+size_t win_shared_bytes() { return kLsBytes; }
+
+static bool win_configure()
+{
+    static int state = 0; // 0 unknown, 1 ok, -1 failed
+    if (state == 0) {
+        cudaError_t e1 = cudaFuncSetAttribute(k_win_linearize_schur, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kLsBytes);
+        cudaError_t e2 = cudaFuncSetAttribute(k_win_update, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kUsBytes);
+        state = (e1 == cudaSuccess && e2 == cudaSuccess) ? 1 : -1;
+    }
+    return state == 1;
+}
+
+int launch_win_linearize_schur(const DevProblem& P, int init_pass, double lambda_override, cudaStream_t st)
+{
+    if (P.n_tiles <= 0 || !win_configure()) return 0;
+    k_win_linearize_schur<<<P.n_tiles, kWinThreads, kLsBytes, st>>>(P, init_pass, lambda_override);
+    return 1;
+}
+
+int launch_win_finalize(const DevProblem& P, int init_pass, double lambda_override, cudaStream_t st)
+{
+    k_win_finalize<<<P.n_problems, 256, 0, st>>>(P, init_pass, lambda_override);
+    return 1;
+}
+
+int launch_win_update(const DevProblem& P, cudaStream_t st)
+{
+    if (P.n_tiles <= 0 || !win_configure()) return 0;
+    k_win_update<<<P.n_tiles, kWinThreads, kUsBytes, st>>>(P);
+    return 1;
+}
+
+int launch_win_prob_sums(const DevProblem& P, int even_if_inactive, cudaStream_t st)
+{
+    k_win_prob_sums<<<(P.n_problems + 127) / 128, 128, 0, st>>>(P, even_if_inactive);
+    return 1;
+}
+
+static_assert(3 * (kLsBytes + 1024) <= 227 * 1024, "three linearize CTAs per SM must fit in shared memory");
+static_assert(kWinPtCap <= 255 && kWinObsCap <= 65535 && kWinMaxCams <= 32, "meta word packing");
+
+} // namespace visoba

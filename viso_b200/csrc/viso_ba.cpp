@@ -132,6 +132,7 @@ struct viso_ba {
     DevProblem P;
     LargeSolve L;
     bool use_large = false;
+    bool window = false; // tile fast path (ba_window.cu) instead of the pair-list kernels
     int max_n = 0; // largest reduced system over the problems
     double *d_pose_init = nullptr, *d_pts_init = nullptr, *d_pose_out = nullptr, *d_pts_out = nullptr;
     double* d_allreduce = nullptr; // S_blk | bs   (contiguous)
@@ -299,6 +300,7 @@ extern "C" void viso_ba_default_config(viso_ba_config* c)
     c->verbose = 0;
     c->fix_first_pose = 1;
     c->use_cuda_graph = 1;
+    c->path = 0;
 }
 
 extern "C" int32_t viso_ba_create(const viso_ba_config* cfg, viso_ba** out)
@@ -529,6 +531,14 @@ struct Built {
     std::vector<int32_t> diag_items, block_item_ptr, block_cam;
     std::vector<int32_t> chunks;     // 4 per chunk
     std::vector<int32_t> prob_chunk_ptr;
+    // window fast path
+    bool window = false;
+    std::vector<uint32_t> pt_mask, win_meta, win_blkptr, win_pairs;
+    std::vector<float> win_uv;
+    std::vector<uint16_t> win_slot;
+    std::vector<WinTile> tiles;
+    std::vector<int32_t> prob_tile_ptr;
+    std::vector<int64_t> prob_part_off;
     int64_t n_pairs = 0;
     int32_t n_blocks = 0, max_n = 0;
 };
@@ -627,9 +637,104 @@ int32_t build_structure(viso_ba* h, Built& b)
     }
     const int32_t pt_begin = h->shard_pt[(size_t)h->rank], pt_end = h->shard_pt[(size_t)h->rank + 1];
 
+    // ---- window fast path: visibility masks and tiles instead of a pair list ----
+    b.window = h->cfg.path != 2 && h->n_ranks == 1 && b.max_n <= kSmallMaxN && Np > 0;
+    if (h->cfg.path == 0 && Ne < (int64_t)kWinAutoMinTiles * kWinObsCap) b.window = false; // too few tiles to fill the GPU
+    for (int64_t p = 0; p < B && b.window; ++p)
+        if (b.prob_cam0[(size_t)p + 1] - b.prob_cam0[(size_t)p] > kWinMaxCams) b.window = false;
+    if (b.window) {
+        b.pt_mask.assign((size_t)Np, 0u);
+        for (int64_t p = 0; p < Np && b.window; ++p) {
+            const int32_t c0 = b.prob_cam0[(size_t)b.pt_prob[(size_t)p]];
+            uint32_t m = 0;
+            for (int32_t s = b.pt_ptr[(size_t)p]; s < b.pt_ptr[(size_t)p + 1]; ++s) {
+                const uint32_t bit = 1u << (b.obs_cam[(size_t)s] - c0);
+                if (m & bit) b.window = false; // duplicate (point, pose) edge: the general path handles it
+                m |= bit;
+            }
+            b.pt_mask[(size_t)p] = m;
+        }
+    }
+    if (b.window) {
+        b.prob_tile_ptr.assign((size_t)B + 1, 0);
+        b.prob_part_off.assign((size_t)B + 1, 0);
+        b.win_meta.resize((size_t)Ne);
+        b.win_uv.resize((size_t)Ne * 2);
+        b.win_slot.resize((size_t)Ne);
+        int64_t part_off = 0;
+        for (int64_t p = 0; p < B; ++p) {
+            int32_t q = (int32_t)pt0[(size_t)p];
+            const int32_t hi = (int32_t)pt0[(size_t)p + 1];
+            const int32_t cam0 = b.prob_cam0[(size_t)p], ncam = b.prob_cam0[(size_t)p + 1] - cam0;
+            const int32_t nf = b.prob_nfree[(size_t)p];
+            const int32_t nblk = nf * (nf + 1) / 2;
+            while (q < hi) { // greedy: consecutive points while both caps hold
+                int32_t e = q;
+                const int32_t o0 = b.pt_ptr[(size_t)q];
+                while (e < hi && e - q < kWinPtCap && b.pt_ptr[(size_t)e + 1] - o0 <= kWinObsCap) ++e;
+                WinTile t;
+                std::memset(&t, 0, sizeof(t));
+                t.prob = (int32_t)p, t.p0 = q, t.np = e - q, t.o0 = o0, t.no = b.pt_ptr[(size_t)e] - o0;
+                t.cam0 = cam0, t.ncam = ncam, t.nf = nf, t.part_off = part_off;
+                t.blkptr_off = (int64_t)b.win_blkptr.size(), t.list_off = (int64_t)b.win_pairs.size();
+                part_off += (int64_t)nblk * kItemPart;
+                // slot of every observation of the tile: keyframe-major, points in order
+                int32_t start[kWinMaxCams + 1] = { 0 };
+                for (int32_t s = o0; s < o0 + t.no; ++s) start[b.obs_cam[(size_t)s] - cam0 + 1]++;
+                for (int32_t c = 0; c < ncam; ++c) start[c + 1] += start[c];
+                for (int32_t pp = q; pp < e; ++pp)
+                    for (int32_t s = b.pt_ptr[(size_t)pp]; s < b.pt_ptr[(size_t)pp + 1]; ++s) {
+                        const int32_t c = b.obs_cam[(size_t)s] - cam0;
+                        const int32_t sl = start[c]++;
+                        b.win_slot[(size_t)s] = (uint16_t)sl;
+                        b.win_meta[(size_t)(o0 + sl)] = (uint32_t)c | ((uint32_t)(pp - q) << 8);
+                        b.win_uv[2 * (size_t)(o0 + sl)] = b.obs_uv[2 * (size_t)s];
+                        b.win_uv[2 * (size_t)(o0 + sl) + 1] = b.obs_uv[2 * (size_t)s + 1];
+                    }
+                // pair list of every S block (I >= J, free indices) inside the tile, points in order
+                const size_t bp0 = b.win_blkptr.size();
+                b.win_blkptr.resize(bp0 + (size_t)nblk + 1, 0u);
+                uint32_t* bp = b.win_blkptr.data() + bp0;
+                for (int32_t pp = q; pp < e; ++pp) { // count
+                    const int32_t s0 = b.pt_ptr[(size_t)pp], s1 = b.pt_ptr[(size_t)pp + 1];
+                    for (int32_t a = s0; a < s1; ++a) {
+                        const int32_t fa = b.cam_free[(size_t)b.obs_cam[(size_t)a]];
+                        if (fa < 0) continue;
+                        for (int32_t c = s0; c <= a; ++c) {
+                            const int32_t fc = b.cam_free[(size_t)b.obs_cam[(size_t)c]];
+                            if (fc >= 0) bp[fa * (fa + 1) / 2 + fc + 1]++;
+                        }
+                    }
+                }
+                for (int32_t k = 0; k < nblk; ++k) bp[k + 1] += bp[k];
+                const size_t l0 = b.win_pairs.size();
+                b.win_pairs.resize(l0 + bp[nblk]);
+                uint32_t* lst = b.win_pairs.data() + l0;
+                std::vector<uint32_t> cur(bp, bp + nblk);
+                for (int32_t pp = q; pp < e; ++pp) { // fill
+                    const int32_t s0 = b.pt_ptr[(size_t)pp], s1 = b.pt_ptr[(size_t)pp + 1];
+                    for (int32_t a = s0; a < s1; ++a) {
+                        const int32_t fa = b.cam_free[(size_t)b.obs_cam[(size_t)a]];
+                        if (fa < 0) continue;
+                        for (int32_t c = s0; c <= a; ++c) {
+                            const int32_t fc = b.cam_free[(size_t)b.obs_cam[(size_t)c]];
+                            if (fc >= 0)
+                                lst[cur[(size_t)(fa * (fa + 1) / 2 + fc)]++] = (uint32_t)b.win_slot[(size_t)a] | ((uint32_t)b.win_slot[(size_t)c] << 16);
+                        }
+                    }
+                }
+                b.tiles.push_back(t);
+                q = e;
+            }
+            b.prob_tile_ptr[(size_t)p + 1] = (int32_t)b.tiles.size();
+            b.prob_part_off[(size_t)p + 1] = part_off;
+        }
+    }
+
     // ---- pair list sorted by S block (two passes: count, fill) ----
     std::vector<int64_t> blk_ptr((size_t)b.n_blocks + 1, 0);
     auto for_pairs = [&](auto&& emit) {
+        if (b.window) return; // the tile kernels derive the pairs from the masks
         for (int32_t p = pt_begin; p < pt_end; ++p) {
             const int32_t tri0 = b.prob_tri0[(size_t)b.pt_prob[(size_t)p]];
             const int32_t s0 = b.pt_ptr[(size_t)p], s1 = b.pt_ptr[(size_t)p + 1];
@@ -721,6 +826,13 @@ struct DevPtrs { // everything carved out of the arena, in one place so that the
     int2* pairs;
     int4 *items, *chunks;
     int32_t *diag_items, *block_item_ptr, *block_cam, *prob_chunk_ptr;
+    WinTile* tiles;
+    uint32_t *pt_mask, *win_meta, *win_blkptr, *win_pairs;
+    float2* win_uv;
+    uint16_t* win_slot;
+    int32_t* prob_tile_ptr;
+    int64_t* prob_part_off;
+    double *tile_part, *tile_sums;
     double *pts[2], *pose[2], *cam_rt[2], *pose_init, *pts_init, *pose_out, *pts_out;
     LmState* lm;
     IterStat* iter_stats;
@@ -752,6 +864,17 @@ void carve(Arena& A, DevPtrs& d, int64_t Nc, int64_t Np, int64_t Ne, int64_t B, 
     d.block_cam = A.take<int32_t>((size_t)b.n_blocks);
     d.chunks = A.take<int4>(b.chunks.size() / 4);
     d.prob_chunk_ptr = A.take<int32_t>((size_t)B + 1);
+    d.tiles = A.take<WinTile>(b.tiles.size());
+    d.pt_mask = A.take<uint32_t>(b.pt_mask.size());
+    d.win_meta = A.take<uint32_t>(b.win_meta.size());
+    d.win_blkptr = A.take<uint32_t>(b.win_blkptr.size());
+    d.win_pairs = A.take<uint32_t>(b.win_pairs.size());
+    d.win_uv = A.take<float2>(b.win_uv.size() / 2);
+    d.win_slot = A.take<uint16_t>(b.win_slot.size());
+    d.prob_tile_ptr = A.take<int32_t>(b.prob_tile_ptr.size());
+    d.prob_part_off = A.take<int64_t>(b.prob_part_off.size());
+    d.tile_part = A.take<double>(b.window ? (size_t)b.prob_part_off.back() : 0);
+    d.tile_sums = A.take<double>(b.tiles.size() * 2);
     for (int k = 0; k < 2; ++k) {
         d.pts[k] = A.take<double>((size_t)Np * 3);
         d.pose[k] = A.take<double>((size_t)Nc * 7);
@@ -763,7 +886,7 @@ void carve(Arena& A, DevPtrs& d, int64_t Nc, int64_t Np, int64_t Ne, int64_t B, 
     d.pts_out = A.take<double>((size_t)Np * 3);
     d.lm = A.take<LmState>((size_t)B);
     d.iter_stats = A.take<IterStat>(kMaxIterStats);
-    d.rec = A.take<double>((size_t)Ne * kRecDoubles);
+    d.rec = A.take<double>(b.window ? 0 : (size_t)Ne * kRecDoubles);
     d.ptinfo = A.take<double>((size_t)Np * kPtInfoDoubles);
     d.cost_pt = A.take<double>((size_t)Np);
     d.cost_new_pt = A.take<double>((size_t)Np);
@@ -843,6 +966,15 @@ extern "C" int32_t viso_ba_upload(viso_ba* h)
     if ((rc = h2d(h, d.block_cam, b.block_cam))) return rc;
     if ((rc = h2d(h, reinterpret_cast<int32_t*>(d.chunks), b.chunks))) return rc;
     if ((rc = h2d(h, d.prob_chunk_ptr, b.prob_chunk_ptr))) return rc;
+    if ((rc = h2d(h, d.tiles, b.tiles))) return rc;
+    if ((rc = h2d(h, d.pt_mask, b.pt_mask))) return rc;
+    if ((rc = h2d(h, d.win_meta, b.win_meta))) return rc;
+    if ((rc = h2d(h, d.win_blkptr, b.win_blkptr))) return rc;
+    if ((rc = h2d(h, d.win_pairs, b.win_pairs))) return rc;
+    if ((rc = h2d(h, reinterpret_cast<float*>(d.win_uv), b.win_uv))) return rc;
+    if ((rc = h2d(h, d.win_slot, b.win_slot))) return rc;
+    if ((rc = h2d(h, d.prob_tile_ptr, b.prob_tile_ptr))) return rc;
+    if ((rc = h2d(h, d.prob_part_off, b.prob_part_off))) return rc;
     // state: normalised quaternions (Sophus keeps unit quaternions), buffer 0 current
     std::vector<double> poses = h->poses;
     for (int64_t c = 0; c < Nc; ++c) {
@@ -872,6 +1004,10 @@ extern "C" int32_t viso_ba_upload(viso_ba* h)
     P.item_part = d.item_part, P.S_blk = d.S_blk, P.bs = d.bs, P.dp = d.dp, P.chunk_part = d.chunk_part;
     P.prob_sums = d.prob_sums, P.maxdiag_bits = d.maxdiag_bits, P.n_active = d.n_active;
     P.lambda_scale = h->rank == 0 ? 1.0 : 0.0;
+    h->window = b.window;
+    P.n_tiles = (int32_t)b.tiles.size(), P.tiles = d.tiles, P.pt_mask = d.pt_mask;
+    P.win_meta = d.win_meta, P.win_blkptr = d.win_blkptr, P.win_pairs = d.win_pairs, P.win_uv = d.win_uv, P.win_slot = d.win_slot;
+    P.prob_tile_ptr = d.prob_tile_ptr, P.prob_part_off = d.prob_part_off, P.tile_part = d.tile_part, P.tile_sums = d.tile_sums;
     h->d_pose_init = d.pose_init, h->d_pts_init = d.pts_init, h->d_pose_out = d.pose_out, h->d_pts_out = d.pts_out;
     h->d_allreduce = d.S_blk;
     h->allreduce_count = (size_t)b.n_blocks * 36 + (size_t)Nc * 6;
@@ -934,14 +1070,36 @@ int32_t allreduce(viso_ba* h, double* buf, size_t count, int op)
     return VISO_BA_OK;
 }
 
+// linearise the current state and form the reduced camera system (S_blk, bs); init_pass: only
+// what g2o's computeLambdaInit needs (cost, diagonal blocks at lambda = 0)
+void enqueue_linearize(viso_ba* h, int init_pass, double lambda_override)
+{
+    const DevProblem& P = h->P;
+    cudaStream_t st = h->stream;
+    if (h->window) {
+        run_k(h, "win_linearize_schur", [&] { return launch_win_linearize_schur(P, init_pass, lambda_override, st); });
+        run_k(h, "win_finalize", [&] { return launch_win_finalize(P, init_pass, lambda_override, st); });
+    } else {
+        run_k(h, "linearize", [&] { return launch_linearize(P, init_pass, lambda_override, st); });
+        run_k(h, "schur_blocks", [&] { return launch_schur_blocks(P, init_pass, st); });
+        run_k(h, "block_finalize", [&] { return launch_block_finalize(P, init_pass, lambda_override, st); });
+    }
+}
+
 int32_t enqueue_trial(viso_ba* h)
 {
     const DevProblem& P = h->P;
     cudaStream_t st = h->stream;
     int32_t rc;
-    run_k(h, "linearize", [&] { return launch_linearize(P, 0, -1.0, st); });
-    run_k(h, "schur_blocks", [&] { return launch_schur_blocks(P, 0, st); });
-    run_k(h, "block_finalize", [&] { return launch_block_finalize(P, 0, -1.0, st); });
+    if (h->window) { // every problem has <= 32 keyframes: tile kernels, small solve
+        enqueue_linearize(h, 0, -1.0);
+        run_k(h, "solve_small", [&] { return launch_solve_small(P, h->max_n, st); });
+        run_k(h, "win_update", [&] { return launch_win_update(P, st); });
+        run_k(h, "reduce", [&] { return launch_win_prob_sums(P, 0, st); });
+        run_k(h, "decide", [&] { return launch_decide(P, st); });
+        return VISO_BA_OK;
+    }
+    enqueue_linearize(h, 0, -1.0);
     if ((rc = allreduce(h, h->d_allreduce, h->allreduce_count, kNcclSum))) return rc;
     if (h->use_large) run_k(h, "solve_large", [&] { return launch_solve_large(P, h->L, st); });
     else run_k(h, "solve_small", [&] { return launch_solve_small(P, h->max_n, st); });
@@ -994,10 +1152,9 @@ int32_t run_lm(viso_ba* h, int iterations, viso_ba_summary* summary)
     CU(cudaEventRecord(h->ev0, st));
     run_k(h, "state_init", [&] { return launch_state_init(P, iterations > 0 ? iterations : 1, h->cfg.lm_max_trials, h->cfg.lm_lambda_init, st); });
     // first linearisation: cost of the start state, lambda_0 = tau * max diag(H)   (g2o computeLambdaInit)
-    run_k(h, "linearize", [&] { return launch_linearize(P, 1, -1.0, st); });
-    run_k(h, "schur_blocks", [&] { return launch_schur_blocks(P, 1, st); });
-    run_k(h, "block_finalize", [&] { return launch_block_finalize(P, 1, -1.0, st); });
-    run_k(h, "reduce", [&] { return launch_reduce(P, 0, st); });
+    enqueue_linearize(h, 1, -1.0);
+    if (h->window) run_k(h, "reduce", [&] { return launch_win_prob_sums(P, 0, st); });
+    else run_k(h, "reduce", [&] { return launch_reduce(P, 0, st); });
     if (h->n_ranks > 1) {
         if ((rc = allreduce(h, h->d_allreduce, h->allreduce_count + 2 * (size_t)P.n_problems, kNcclSum))) return rc;
         if ((rc = allreduce(h, reinterpret_cast<double*>(P.maxdiag_bits), (size_t)P.n_problems, kNcclMax))) return rc;
@@ -1172,9 +1329,7 @@ extern "C" int32_t viso_ba_debug_reduced_system(viso_ba* h, double lambda, int32
     if (n_cap < n) return fail(h, VISO_BA_ERR_CAPACITY, "reduced system is %d x %d", n, n);
     cudaStream_t st = h->stream;
     run_k(h, "state_init", [&] { return launch_state_init(P, 1, h->cfg.lm_max_trials, lambda, st); });
-    run_k(h, "linearize", [&] { return launch_linearize(P, 0, lambda, st); });
-    run_k(h, "schur_blocks", [&] { return launch_schur_blocks(P, 0, st); });
-    run_k(h, "block_finalize", [&] { return launch_block_finalize(P, 0, lambda, st); });
+    enqueue_linearize(h, 0, lambda);
     if ((rc = allreduce(h, h->d_allreduce, h->allreduce_count, kNcclSum))) return rc;
     run_k(h, "state_init", [&] { return launch_state_init(P, 0, h->cfg.lm_max_trials, 0.0, st); });
     std::vector<double> blk((size_t)P.n_blocks * 36), b6((size_t)P.n_cams * 6);
