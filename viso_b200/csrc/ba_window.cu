@@ -281,15 +281,19 @@ __global__ void __launch_bounds__(kWinThreads, 3) k_win_linearize_schur(DevProbl
         int maxcnt = cnt;
         maxcnt = max(maxcnt, __shfl_xor_sync(0xffffffffu, maxcnt, 8));
         maxcnt = max(maxcnt, __shfl_xor_sync(0xffffffffu, maxcnt, 16));
-        unsigned int pr_next = l8 < cnt ? __ldg(list + l8) : 0u;
+        // pair words are prefetched three rounds ahead (a round is far shorter than an L2 miss)
+        unsigned int pr_q0 = l8 < cnt ? __ldg(list + l8) : 0u;
+        unsigned int pr_q1 = l8 + kSub < cnt ? __ldg(list + l8 + kSub) : 0u;
+        unsigned int pr_q2 = l8 + 2 * kSub < cnt ? __ldg(list + l8 + 2 * kSub) : 0u;
 
         double v[48];
 #pragma unroll
         for (int i = 0; i < 48; ++i) v[i] = 0.0;
         for (int i0 = 0; i0 < maxcnt; i0 += kSub) {
             const int i = i0 + l8;
-            const unsigned int pr = pr_next;
-            pr_next = i + kSub < cnt ? __ldg(list + i + kSub) : 0u; // one round ahead: hides the L2 latency
+            const unsigned int pr = pr_q0;
+            pr_q0 = pr_q1, pr_q1 = pr_q2;
+            pr_q2 = i + 3 * kSub < cnt ? __ldg(list + i + 3 * kSub) : 0u;
             if (i < cnt) {
                 const int oa = pr & 0xffffu, ob = pr >> 16;
                 const double2 a0 = REC(0, oa), a1 = REC(1, oa), a2 = REC(2, oa), a3 = REC(3, oa), a4 = REC(4, oa);

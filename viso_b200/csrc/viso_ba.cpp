@@ -8,6 +8,7 @@
 // comes from the kernels in ba_kernels.cu (there is deliberately no fallback).
 #include "../../include/viso_ba.h"
 #include "ba_device.h"
+#include "ba_setup.h"
 
 #include <cuda_runtime.h>
 #include <dlfcn.h>
@@ -94,6 +95,11 @@ struct Arena {
     }
 };
 
+struct DevBuf { // grow-only device buffer
+    void* p = nullptr;
+    size_t cap = 0;
+};
+
 struct KernelAcc {
     int64_t launches = 0;
     double ms = 0.0;
@@ -142,6 +148,13 @@ struct viso_ba {
     size_t pin_cap = 0;
     std::vector<LmState> lm_host;
     float setup_ms = 0.f;
+    // ---- bulk problems whose edges went straight to the device (window fast path) ----
+    bool no_window = false;       // a duplicate edge was seen: this problem stays on the general path
+    bool edges_on_device = false; // e_pose / e_point / e_uv are empty; the raw arrays live in `raw`
+    bool edges_local = false;     // raw indices are local to the edge's problem
+    int64_t n_edges_dev = 0;
+    std::vector<int64_t> edge_off_all; // B+1 (also for B == 1)
+    DevBuf raw, scratch, pairbuf;
     // ---- sharding ----
     int rank = 0, n_ranks = 1;
     void* comm = nullptr;
@@ -336,6 +349,8 @@ extern "C" void viso_ba_destroy(viso_ba* h)
         resolve_timing(h);
         if (h->comm && nccl_api()) nccl_api()->CommDestroy(h->comm);
         if (h->arena.base) cudaFree(h->arena.base);
+        for (DevBuf* b : { &h->raw, &h->scratch, &h->pairbuf })
+            if (b->p) cudaFree(b->p);
         if (h->pin) cudaFreeHost(h->pin);
         if (h->ev0) cudaEventDestroy(h->ev0);
         if (h->ev1) cudaEventDestroy(h->ev1);
@@ -351,7 +366,8 @@ extern "C" int32_t viso_ba_clear(viso_ba* h)
     if (!h) return VISO_BA_ERR_ARG;
     h->poses.clear(), h->points.clear(), h->e_pose.clear(), h->e_point.clear(), h->e_uv.clear();
     h->fixed.clear();
-    h->pose_off.clear(), h->point_off.clear(), h->edge_off.clear();
+    h->pose_off.clear(), h->point_off.clear(), h->edge_off.clear(), h->edge_off_all.clear();
+    h->edges_on_device = false, h->edges_local = false, h->n_edges_dev = 0, h->no_window = false;
     h->n_problems = 1;
     h->uploaded = false;
     drop_graph(h);
@@ -391,6 +407,7 @@ extern "C" int32_t viso_ba_add_edge(viso_ba* h, int64_t point, int64_t pose, flo
 {
     if (!h) return VISO_BA_ERR_ARG;
     if (!h->pose_off.empty()) return fail(h, VISO_BA_ERR_STATE, "handle holds a batched problem; clear it first");
+    if (h->edges_on_device) return fail(h, VISO_BA_ERR_STATE, "handle holds a bulk problem; clear it first");
     if ((int64_t)h->e_pose.size() >= h->cfg.max_edges) return fail(h, VISO_BA_ERR_CAPACITY, "edge pool full (%lld)", (long long)h->cfg.max_edges);
     if (point < 0 || point >= (int64_t)h->points.size() / 3) return fail(h, VISO_BA_ERR_INDEX, "edge refers to point %lld", (long long)point);
     if (pose < 0 || pose >= (int64_t)h->poses.size() / 7) return fail(h, VISO_BA_ERR_INDEX, "edge refers to pose %lld", (long long)pose);
@@ -412,6 +429,145 @@ int32_t check_finite(viso_ba* h, const double* a, size_t n, const char* what)
 }
 } // namespace
 
+// ------------------------------------------------------------------------------------------
+// bulk problems of the window fast path: the edge arrays go from the caller's memory straight
+// to the device (no host copy, no host pass over the edges); validation is a kernel
+// ------------------------------------------------------------------------------------------
+namespace {
+
+int32_t pin_reserve(viso_ba* h, size_t bytes);
+
+int32_t devbuf_reserve(viso_ba* h, DevBuf& b, size_t bytes)
+{
+    if (bytes <= b.cap) return VISO_BA_OK;
+    if (b.p) {
+        CU(cudaStreamSynchronize(h->stream));
+        CU(cudaFree(b.p));
+        b.p = nullptr, b.cap = 0;
+    }
+    const size_t want = bytes + bytes / 8;
+    CU(cudaMalloc(&b.p, want));
+    b.cap = want;
+    return VISO_BA_OK;
+}
+
+struct Carver { // bump allocation inside one buffer; base == nullptr: dry run for the size
+    char* base;
+    size_t used = 0;
+    explicit Carver(void* b) : base(static_cast<char*>(b)) {}
+    template <typename T> T* take(size_t count)
+    {
+        T* p = reinterpret_cast<T*>(base ? base + used : nullptr);
+        used += (count * sizeof(T) + 255) & ~(size_t)255;
+        return p;
+    }
+};
+
+struct RawEdges {
+    int32_t *e_pose, *e_point;
+    float2* e_uv;
+    int64_t* edge_off;
+    int32_t *prob_cam0, *prob_pt0;
+};
+
+size_t carve_raw(void* base, RawEdges& r, int64_t Ne, int64_t B)
+{
+    Carver c(base);
+    r.e_pose = c.take<int32_t>((size_t)Ne);
+    r.e_point = c.take<int32_t>((size_t)Ne);
+    r.e_uv = c.take<float2>((size_t)Ne);
+    r.edge_off = c.take<int64_t>((size_t)B + 1);
+    r.prob_cam0 = c.take<int32_t>((size_t)B + 1);
+    r.prob_pt0 = c.take<int32_t>((size_t)B + 1);
+    return c.used;
+}
+
+size_t carve_scratch(void* base, SetupWork& w, int64_t Ne, int64_t B, int64_t tiles_max)
+{
+    Carver c(base);
+    w.keys = c.take<unsigned long long>((size_t)Ne);
+    w.keys_sorted = c.take<unsigned long long>((size_t)Ne);
+    w.vals = c.take<unsigned int>((size_t)Ne);
+    w.vals_sorted = c.take<unsigned int>((size_t)Ne);
+    w.temp_bytes = std::max(setup_sort_temp_bytes(Ne), setup_sort_temp_bytes(tiles_max + 1));
+    w.temp = c.take<char>(w.temp_bytes);
+    w.prob_ntiles = c.take<int32_t>((size_t)B);
+    w.prob_blkptr_off = c.take<int64_t>((size_t)B + 1);
+    w.tile_pairs = c.take<int64_t>((size_t)tiles_max + 1);
+    w.tile_list_off = c.take<int64_t>((size_t)tiles_max + 1);
+    w.totals = c.take<int64_t>(4);
+    w.err = c.take<int>(4);
+    return c.used;
+}
+
+// a tile is closed when the next point would break a cap, so every tile but a problem's last
+// holds kWinPtCap points or more than kWinObsCap - kWinMaxCams observations
+int64_t tiles_upper_bound(int64_t B, const int64_t* point_off, const int64_t* edge_off)
+{
+    int64_t n = 0;
+    for (int64_t b = 0; b < B; ++b)
+        n += (point_off[b + 1] - point_off[b]) / kWinPtCap + (edge_off[b + 1] - edge_off[b]) / (kWinObsCap - kWinMaxCams + 1) + 2;
+    return n;
+}
+
+// can this problem take the window path whatever the gauge turns out to be?
+bool window_shape_ok(const viso_ba* h, int64_t B, const int64_t* pose_off, int64_t Ne, int max_free)
+{
+    if (h->cfg.path == 2 || h->n_ranks != 1 || h->no_window) return false;
+    if (h->cfg.path == 0 && Ne < (int64_t)kWinAutoMinTiles * kWinObsCap) return false; // too few tiles to fill the GPU
+    for (int64_t b = 0; b < B; ++b)
+        if (pose_off[b + 1] - pose_off[b] > std::min(max_free, kWinMaxCams)) return false;
+    return true;
+}
+
+// H2D of the caller's edge arrays + validation kernel.  `local`: indices are local to the problem.
+int32_t stage_edges_on_device(viso_ba* h, int64_t B, const int64_t* pose_off, const int64_t* point_off, const int64_t* edge_off,
+    const int32_t* edge_pose, const int32_t* edge_point, const float* edge_uv, bool local, SetupIn* in_out, SetupWork* w_out)
+{
+    const int64_t Ne = edge_off[B];
+    int32_t rc;
+    RawEdges r;
+    if ((rc = devbuf_reserve(h, h->raw, carve_raw(nullptr, r, Ne, B)))) return rc;
+    carve_raw(h->raw.p, r, Ne, B);
+    SetupWork w;
+    const int64_t tiles_max = tiles_upper_bound(B, point_off, edge_off);
+    if ((rc = devbuf_reserve(h, h->scratch, carve_scratch(nullptr, w, Ne, B, tiles_max)))) return rc;
+    carve_scratch(h->scratch.p, w, Ne, B, tiles_max);
+    cudaStream_t st = h->stream;
+    if (Ne) {
+        CU(cudaMemcpyAsync(r.e_pose, edge_pose, sizeof(int32_t) * (size_t)Ne, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(r.e_point, edge_point, sizeof(int32_t) * (size_t)Ne, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(r.e_uv, edge_uv, sizeof(float) * 2 * (size_t)Ne, cudaMemcpyHostToDevice, st));
+    }
+    std::vector<int32_t> c0((size_t)B + 1), p0((size_t)B + 1);
+    for (int64_t b = 0; b <= B; ++b) c0[(size_t)b] = (int32_t)pose_off[b], p0[(size_t)b] = (int32_t)point_off[b];
+    CU(cudaMemcpyAsync(r.edge_off, edge_off, sizeof(int64_t) * (size_t)(B + 1), cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(r.prob_cam0, c0.data(), sizeof(int32_t) * (size_t)(B + 1), cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(r.prob_pt0, p0.data(), sizeof(int32_t) * (size_t)(B + 1), cudaMemcpyHostToDevice, st));
+    SetupIn in;
+    std::memset(&in, 0, sizeof(in));
+    in.n_edges = Ne, in.n_points = (int32_t)point_off[B], in.n_cams = (int32_t)pose_off[B], in.n_problems = (int32_t)B;
+    in.local_indices = local ? 1 : 0;
+    in.e_pose = r.e_pose, in.e_point = r.e_point, in.e_uv = r.e_uv, in.edge_off = r.edge_off;
+    in.prob_cam0 = r.prob_cam0, in.prob_pt0 = r.prob_pt0;
+    run_k(h, "setup", [&] { return setup_stage0(in, w, st); });
+    if ((rc = pin_reserve(h, 64))) return rc;
+    CU(cudaMemcpyAsync(h->pin, w.err, 4 * sizeof(int), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st)); // the caller's arrays (and c0 / p0) are free again
+    CU(cudaGetLastError());
+    const int* err = static_cast<const int*>(h->pin);
+    if (err[0]) {
+        long long e = 0;
+        std::memcpy(&e, err + 2, sizeof(e));
+        return fail(h, err[0], err[0] == VISO_BA_ERR_INDEX ? "edge %lld refers to a point or pose outside its problem" : "edge_uv of edge %lld is not finite", e);
+    }
+    if (in_out) *in_out = in;
+    if (w_out) *w_out = w;
+    return VISO_BA_OK;
+}
+
+} // namespace
+
 extern "C" int32_t viso_ba_set_problem_batched(viso_ba* h, int64_t B, const int64_t* pose_off,
     const int64_t* point_off, const int64_t* edge_off, const double* poses7, const double* points3,
     const int32_t* edge_pose, const int32_t* edge_point, const float* edge_uv)
@@ -424,37 +580,49 @@ extern "C" int32_t viso_ba_set_problem_batched(viso_ba* h, int64_t B, const int6
     if (Nc > h->cfg.max_poses || Np > h->cfg.max_points || Ne > h->cfg.max_edges)
         return fail(h, VISO_BA_ERR_CAPACITY, "problem (%lld poses, %lld points, %lld edges) exceeds the pools (%lld, %lld, %lld)",
             (long long)Nc, (long long)Np, (long long)Ne, (long long)h->cfg.max_poses, (long long)h->cfg.max_points, (long long)h->cfg.max_edges);
-    for (int64_t b = 0; b < B; ++b) {
+    for (int64_t b = 0; b < B; ++b)
         if (pose_off[b + 1] < pose_off[b] || point_off[b + 1] < point_off[b] || edge_off[b + 1] < edge_off[b])
             return fail(h, VISO_BA_ERR_ARG, "offsets of problem %lld decrease", (long long)b);
-        const int64_t nc = pose_off[b + 1] - pose_off[b], np = point_off[b + 1] - point_off[b];
-        for (int64_t e = edge_off[b]; e < edge_off[b + 1]; ++e) {
-            if (edge_pose[e] < 0 || edge_pose[e] >= nc) return fail(h, VISO_BA_ERR_INDEX, "edge %lld refers to pose %d", (long long)e, edge_pose[e]);
-            if (edge_point[e] < 0 || edge_point[e] >= np) return fail(h, VISO_BA_ERR_INDEX, "edge %lld refers to point %d", (long long)e, edge_point[e]);
-        }
-    }
     int32_t rc;
     if ((rc = check_finite(h, poses7, (size_t)Nc * 7, "poses"))) return rc;
     if ((rc = check_finite(h, points3, (size_t)Np * 3, "points"))) return rc;
-    for (int64_t e = 0; e < 2 * Ne; ++e)
-        if (!std::isfinite(edge_uv[e])) return fail(h, VISO_BA_ERR_NONFINITE, "edge_uv[%lld] is not finite", (long long)e);
     for (int64_t c = 0; c < Nc; ++c) {
         const double* q = poses7 + 7 * c;
         if (!(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3] > 1e-12)) return fail(h, VISO_BA_ERR_ARG, "pose %lld has a zero quaternion", (long long)c);
     }
+    // window fast path for sure (<= 27 keyframes per problem: eligible whatever gets fixed later) and a
+    // usable device: the edges never touch host memory of this library
+    const bool direct = Nc > 0 && Np > 0 && window_shape_ok(h, B, pose_off, Ne, kSmallMaxN / 6) && ensure_cuda(h) == VISO_BA_OK;
+    if (!direct) {
+        for (int64_t b = 0; b < B; ++b) {
+            const int64_t nc = pose_off[b + 1] - pose_off[b], np = point_off[b + 1] - point_off[b];
+            for (int64_t e = edge_off[b]; e < edge_off[b + 1]; ++e) {
+                if (edge_pose[e] < 0 || edge_pose[e] >= nc) return fail(h, VISO_BA_ERR_INDEX, "edge %lld refers to pose %d", (long long)e, edge_pose[e]);
+                if (edge_point[e] < 0 || edge_point[e] >= np) return fail(h, VISO_BA_ERR_INDEX, "edge %lld refers to point %d", (long long)e, edge_point[e]);
+            }
+        }
+        for (int64_t e = 0; e < 2 * Ne; ++e)
+            if (!std::isfinite(edge_uv[e])) return fail(h, VISO_BA_ERR_NONFINITE, "edge_uv[%lld] is not finite", (long long)e);
+    }
     viso_ba_clear(h);
+    if (direct) {
+        if ((rc = stage_edges_on_device(h, B, pose_off, point_off, edge_off, edge_pose, edge_point, edge_uv, true, nullptr, nullptr))) return rc;
+        h->edges_on_device = true, h->edges_local = true, h->n_edges_dev = Ne;
+    } else {
+        h->e_uv.assign(edge_uv, edge_uv + 2 * Ne);
+        h->e_pose.resize((size_t)Ne);
+        h->e_point.resize((size_t)Ne);
+        for (int64_t b = 0; b < B; ++b) // store GLOBAL indices
+            for (int64_t e = edge_off[b]; e < edge_off[b + 1]; ++e) {
+                h->e_pose[(size_t)e] = (int32_t)(edge_pose[e] + pose_off[b]);
+                h->e_point[(size_t)e] = (int32_t)(edge_point[e] + point_off[b]);
+            }
+    }
     h->poses.assign(poses7, poses7 + 7 * Nc);
     h->points.assign(points3, points3 + 3 * Np);
-    h->e_uv.assign(edge_uv, edge_uv + 2 * Ne);
-    h->e_pose.resize((size_t)Ne);
-    h->e_point.resize((size_t)Ne);
-    for (int64_t b = 0; b < B; ++b) // store GLOBAL indices
-        for (int64_t e = edge_off[b]; e < edge_off[b + 1]; ++e) {
-            h->e_pose[(size_t)e] = (int32_t)(edge_pose[e] + pose_off[b]);
-            h->e_point[(size_t)e] = (int32_t)(edge_point[e] + point_off[b]);
-        }
     h->fixed.assign((size_t)Nc, -1);
     h->n_problems = B;
+    h->edge_off_all.assign(edge_off, edge_off + B + 1);
     if (B > 1) {
         h->pose_off.assign(pose_off, pose_off + B + 1);
         h->point_off.assign(point_off, point_off + B + 1);
@@ -512,7 +680,7 @@ extern "C" int32_t viso_ba_set_stream(viso_ba* h, void* s)
 
 extern "C" int64_t viso_ba_num_points(const viso_ba* h) { return h ? (int64_t)h->points.size() / 3 : -1; }
 extern "C" int64_t viso_ba_num_poses(const viso_ba* h) { return h ? (int64_t)h->poses.size() / 7 : -1; }
-extern "C" int64_t viso_ba_num_edges(const viso_ba* h) { return h ? (int64_t)h->e_pose.size() : -1; }
+extern "C" int64_t viso_ba_num_edges(const viso_ba* h) { return h ? (h->edges_on_device ? h->n_edges_dev : (int64_t)h->e_pose.size()) : -1; }
 extern "C" int64_t viso_ba_num_problems(const viso_ba* h) { return h ? h->n_problems : -1; }
 extern "C" int64_t viso_ba_kernel_launches(const viso_ba* h) { return h ? h->launches : -1; }
 
@@ -531,14 +699,10 @@ struct Built {
     std::vector<int32_t> diag_items, block_item_ptr, block_cam;
     std::vector<int32_t> chunks;     // 4 per chunk
     std::vector<int32_t> prob_chunk_ptr;
-    // window fast path
+    // window fast path: the structure is built on the device; the host only bounds its size
     bool window = false;
-    std::vector<uint32_t> pt_mask, win_meta, win_blkptr, win_pairs;
-    std::vector<float> win_uv;
-    std::vector<uint16_t> win_slot;
-    std::vector<WinTile> tiles;
-    std::vector<int32_t> prob_tile_ptr;
-    std::vector<int64_t> prob_part_off;
+    int64_t tiles_max = 0, part_max = 0, blkptr_max = 0;
+    std::vector<int64_t> pt0; // first point of every problem, B+1
     int64_t n_pairs = 0;
     int32_t n_blocks = 0, max_n = 0;
 };
@@ -555,21 +719,21 @@ template <typename T> void shard_bounds(const T* pt_ptr, int64_t Np, int64_t Ne,
     }
 }
 
-int32_t build_structure(viso_ba* h, Built& b)
+// problems, gauge, free indices, S block offsets: O(poses + problems); decides the path
+int32_t build_tables(viso_ba* h, Built& b)
 {
     const int64_t Nc = (int64_t)h->poses.size() / 7, Np = (int64_t)h->points.size() / 3;
-    const int64_t Ne = (int64_t)h->e_pose.size();
+    const int64_t Ne = h->edges_on_device ? h->n_edges_dev : (int64_t)h->e_pose.size();
     const int64_t B = h->n_problems;
     // ---- problems, gauge, free indices, block offsets ----
     b.cam_prob.assign((size_t)Nc, 0);
-    b.pt_prob.assign((size_t)Np, 0);
     b.prob_cam0.assign((size_t)B + 1, 0);
-    std::vector<int64_t> pt0((size_t)B + 1, 0);
+    std::vector<int64_t>& pt0 = b.pt0;
+    pt0.assign((size_t)B + 1, 0);
     if (B > 1) {
         for (int64_t p = 0; p <= B; ++p) b.prob_cam0[(size_t)p] = (int32_t)h->pose_off[(size_t)p], pt0[(size_t)p] = h->point_off[(size_t)p];
         for (int64_t p = 0; p < B; ++p) {
             for (int64_t c = h->pose_off[(size_t)p]; c < h->pose_off[(size_t)p + 1]; ++c) b.cam_prob[(size_t)c] = (int32_t)p;
-            for (int64_t q = h->point_off[(size_t)p]; q < h->point_off[(size_t)p + 1]; ++q) b.pt_prob[(size_t)q] = (int32_t)p;
         }
     } else {
         b.prob_cam0[1] = (int32_t)Nc;
@@ -596,6 +760,42 @@ int32_t build_structure(viso_ba* h, Built& b)
     b.prob_tri0[(size_t)B] = (int32_t)tri;
     b.n_blocks = (int32_t)tri;
 
+    b.block_cam.assign((size_t)b.n_blocks, -1);
+    for (int64_t p = 0; p < B; ++p)
+        for (int32_t c = b.prob_cam0[(size_t)p]; c < b.prob_cam0[(size_t)p + 1]; ++c) {
+            const int32_t f = b.cam_free[(size_t)c];
+            if (f >= 0) b.block_cam[(size_t)(b.prob_tri0[(size_t)p] + f * (f + 1) / 2 + f)] = c;
+        }
+    // ---- window fast path? (every problem <= 32 keyframes and <= 27 free poses, one GPU) ----
+    std::vector<int64_t> cam_off((size_t)B + 1);
+    for (int64_t p = 0; p <= B; ++p) cam_off[(size_t)p] = b.prob_cam0[(size_t)p];
+    b.window = Np > 0 && b.max_n <= kSmallMaxN && window_shape_ok(h, B, cam_off.data(), Ne, kWinMaxCams);
+    if (h->edges_on_device && !b.window) return fail(h, VISO_BA_ERR_STATE, "internal: device-resident edges without the window path");
+    if (b.window) {
+        if (B == 1) h->edge_off_all.assign({ 0, Ne }); // AddEdge may have grown a single problem since
+        b.tiles_max = tiles_upper_bound(B, pt0.data(), h->edge_off_all.data());
+        for (int64_t p = 0; p < B; ++p) {
+            const int64_t nf = b.prob_nfree[(size_t)p], nblk = nf * (nf + 1) / 2;
+            const int64_t tp = (pt0[(size_t)p + 1] - pt0[(size_t)p]) / kWinPtCap +
+                (h->edge_off_all[(size_t)p + 1] - h->edge_off_all[(size_t)p]) / (kWinObsCap - kWinMaxCams + 1) + 2;
+            b.part_max += tp * nblk * kItemPart;
+            b.blkptr_max += tp * (nblk + 1);
+        }
+    }
+    return VISO_BA_OK;
+}
+
+// general path: sort the edges, shard the points, list the observation pairs of every S block (host)
+int32_t build_general(viso_ba* h, Built& b)
+{
+    const int64_t Nc = (int64_t)h->poses.size() / 7, Np = (int64_t)h->points.size() / 3;
+    const int64_t Ne = (int64_t)h->e_pose.size();
+    const int64_t B = h->n_problems;
+    const std::vector<int64_t>& pt0 = b.pt0;
+    (void)Nc;
+    b.pt_prob.assign((size_t)Np, 0);
+    for (int64_t p = 0; p < B; ++p)
+        for (int64_t q = pt0[(size_t)p]; q < pt0[(size_t)p + 1]; ++q) b.pt_prob[(size_t)q] = (int32_t)p;
     // ---- stable counting sort by point, then by pose inside each point ----
     b.pt_ptr.assign((size_t)Np + 1, 0);
     for (int64_t e = 0; e < Ne; ++e) b.pt_ptr[(size_t)h->e_point[(size_t)e] + 1]++;
@@ -637,104 +837,9 @@ int32_t build_structure(viso_ba* h, Built& b)
     }
     const int32_t pt_begin = h->shard_pt[(size_t)h->rank], pt_end = h->shard_pt[(size_t)h->rank + 1];
 
-    // ---- window fast path: visibility masks and tiles instead of a pair list ----
-    b.window = h->cfg.path != 2 && h->n_ranks == 1 && b.max_n <= kSmallMaxN && Np > 0;
-    if (h->cfg.path == 0 && Ne < (int64_t)kWinAutoMinTiles * kWinObsCap) b.window = false; // too few tiles to fill the GPU
-    for (int64_t p = 0; p < B && b.window; ++p)
-        if (b.prob_cam0[(size_t)p + 1] - b.prob_cam0[(size_t)p] > kWinMaxCams) b.window = false;
-    if (b.window) {
-        b.pt_mask.assign((size_t)Np, 0u);
-        for (int64_t p = 0; p < Np && b.window; ++p) {
-            const int32_t c0 = b.prob_cam0[(size_t)b.pt_prob[(size_t)p]];
-            uint32_t m = 0;
-            for (int32_t s = b.pt_ptr[(size_t)p]; s < b.pt_ptr[(size_t)p + 1]; ++s) {
-                const uint32_t bit = 1u << (b.obs_cam[(size_t)s] - c0);
-                if (m & bit) b.window = false; // duplicate (point, pose) edge: the general path handles it
-                m |= bit;
-            }
-            b.pt_mask[(size_t)p] = m;
-        }
-    }
-    if (b.window) {
-        b.prob_tile_ptr.assign((size_t)B + 1, 0);
-        b.prob_part_off.assign((size_t)B + 1, 0);
-        b.win_meta.resize((size_t)Ne);
-        b.win_uv.resize((size_t)Ne * 2);
-        b.win_slot.resize((size_t)Ne);
-        int64_t part_off = 0;
-        for (int64_t p = 0; p < B; ++p) {
-            int32_t q = (int32_t)pt0[(size_t)p];
-            const int32_t hi = (int32_t)pt0[(size_t)p + 1];
-            const int32_t cam0 = b.prob_cam0[(size_t)p], ncam = b.prob_cam0[(size_t)p + 1] - cam0;
-            const int32_t nf = b.prob_nfree[(size_t)p];
-            const int32_t nblk = nf * (nf + 1) / 2;
-            while (q < hi) { // greedy: consecutive points while both caps hold
-                int32_t e = q;
-                const int32_t o0 = b.pt_ptr[(size_t)q];
-                while (e < hi && e - q < kWinPtCap && b.pt_ptr[(size_t)e + 1] - o0 <= kWinObsCap) ++e;
-                WinTile t;
-                std::memset(&t, 0, sizeof(t));
-                t.prob = (int32_t)p, t.p0 = q, t.np = e - q, t.o0 = o0, t.no = b.pt_ptr[(size_t)e] - o0;
-                t.cam0 = cam0, t.ncam = ncam, t.nf = nf, t.part_off = part_off;
-                t.blkptr_off = (int64_t)b.win_blkptr.size(), t.list_off = (int64_t)b.win_pairs.size();
-                part_off += (int64_t)nblk * kItemPart;
-                // slot of every observation of the tile: keyframe-major, points in order
-                int32_t start[kWinMaxCams + 1] = { 0 };
-                for (int32_t s = o0; s < o0 + t.no; ++s) start[b.obs_cam[(size_t)s] - cam0 + 1]++;
-                for (int32_t c = 0; c < ncam; ++c) start[c + 1] += start[c];
-                for (int32_t pp = q; pp < e; ++pp)
-                    for (int32_t s = b.pt_ptr[(size_t)pp]; s < b.pt_ptr[(size_t)pp + 1]; ++s) {
-                        const int32_t c = b.obs_cam[(size_t)s] - cam0;
-                        const int32_t sl = start[c]++;
-                        b.win_slot[(size_t)s] = (uint16_t)sl;
-                        b.win_meta[(size_t)(o0 + sl)] = (uint32_t)c | ((uint32_t)(pp - q) << 8);
-                        b.win_uv[2 * (size_t)(o0 + sl)] = b.obs_uv[2 * (size_t)s];
-                        b.win_uv[2 * (size_t)(o0 + sl) + 1] = b.obs_uv[2 * (size_t)s + 1];
-                    }
-                // pair list of every S block (I >= J, free indices) inside the tile, points in order
-                const size_t bp0 = b.win_blkptr.size();
-                b.win_blkptr.resize(bp0 + (size_t)nblk + 1, 0u);
-                uint32_t* bp = b.win_blkptr.data() + bp0;
-                for (int32_t pp = q; pp < e; ++pp) { // count
-                    const int32_t s0 = b.pt_ptr[(size_t)pp], s1 = b.pt_ptr[(size_t)pp + 1];
-                    for (int32_t a = s0; a < s1; ++a) {
-                        const int32_t fa = b.cam_free[(size_t)b.obs_cam[(size_t)a]];
-                        if (fa < 0) continue;
-                        for (int32_t c = s0; c <= a; ++c) {
-                            const int32_t fc = b.cam_free[(size_t)b.obs_cam[(size_t)c]];
-                            if (fc >= 0) bp[fa * (fa + 1) / 2 + fc + 1]++;
-                        }
-                    }
-                }
-                for (int32_t k = 0; k < nblk; ++k) bp[k + 1] += bp[k];
-                const size_t l0 = b.win_pairs.size();
-                b.win_pairs.resize(l0 + bp[nblk]);
-                uint32_t* lst = b.win_pairs.data() + l0;
-                std::vector<uint32_t> cur(bp, bp + nblk);
-                for (int32_t pp = q; pp < e; ++pp) { // fill
-                    const int32_t s0 = b.pt_ptr[(size_t)pp], s1 = b.pt_ptr[(size_t)pp + 1];
-                    for (int32_t a = s0; a < s1; ++a) {
-                        const int32_t fa = b.cam_free[(size_t)b.obs_cam[(size_t)a]];
-                        if (fa < 0) continue;
-                        for (int32_t c = s0; c <= a; ++c) {
-                            const int32_t fc = b.cam_free[(size_t)b.obs_cam[(size_t)c]];
-                            if (fc >= 0)
-                                lst[cur[(size_t)(fa * (fa + 1) / 2 + fc)]++] = (uint32_t)b.win_slot[(size_t)a] | ((uint32_t)b.win_slot[(size_t)c] << 16);
-                        }
-                    }
-                }
-                b.tiles.push_back(t);
-                q = e;
-            }
-            b.prob_tile_ptr[(size_t)p + 1] = (int32_t)b.tiles.size();
-            b.prob_part_off[(size_t)p + 1] = part_off;
-        }
-    }
-
     // ---- pair list sorted by S block (two passes: count, fill) ----
     std::vector<int64_t> blk_ptr((size_t)b.n_blocks + 1, 0);
     auto for_pairs = [&](auto&& emit) {
-        if (b.window) return; // the tile kernels derive the pairs from the masks
         for (int32_t p = pt_begin; p < pt_end; ++p) {
             const int32_t tri0 = b.prob_tri0[(size_t)b.pt_prob[(size_t)p]];
             const int32_t s0 = b.pt_ptr[(size_t)p], s1 = b.pt_ptr[(size_t)p + 1];
@@ -767,12 +872,6 @@ int32_t build_structure(viso_ba* h, Built& b)
     int64_t item_pairs = (b.n_pairs / 16384 + 31) / 32 * 32;
     item_pairs = std::max<int64_t>(64, std::min<int64_t>(512, item_pairs));
     b.block_item_ptr.assign((size_t)b.n_blocks + 1, 0);
-    b.block_cam.assign((size_t)b.n_blocks, -1);
-    for (int64_t p = 0; p < B; ++p)
-        for (int32_t c = b.prob_cam0[(size_t)p]; c < b.prob_cam0[(size_t)p + 1]; ++c) {
-            const int32_t f = b.cam_free[(size_t)c];
-            if (f >= 0) b.block_cam[(size_t)(b.prob_tri0[(size_t)p] + f * (f + 1) / 2 + f)] = c;
-        }
     {
         int32_t prob = 0;
         for (int32_t k = 0; k < b.n_blocks; ++k) {
@@ -827,10 +926,10 @@ struct DevPtrs { // everything carved out of the arena, in one place so that the
     int4 *items, *chunks;
     int32_t *diag_items, *block_item_ptr, *block_cam, *prob_chunk_ptr;
     WinTile* tiles;
-    uint32_t *pt_mask, *win_meta, *win_blkptr, *win_pairs;
+    uint32_t *pt_mask, *win_meta, *win_blkptr;
     float2* win_uv;
     uint16_t* win_slot;
-    int32_t* prob_tile_ptr;
+    int32_t *prob_tile_ptr, *prob_pt0;
     int64_t* prob_part_off;
     double *tile_part, *tile_sums;
     double *pts[2], *pose[2], *cam_rt[2], *pose_init, *pts_init, *pose_out, *pts_out;
@@ -858,23 +957,24 @@ void carve(Arena& A, DevPtrs& d, int64_t Nc, int64_t Np, int64_t Ne, int64_t B, 
     d.prob_tri0 = A.take<int32_t>((size_t)B + 1);
     d.prob_nfree = A.take<int32_t>((size_t)B);
     d.pairs = A.take<int2>((size_t)b.n_pairs);
+    const size_t NeW = b.window ? (size_t)Ne : 0, NpW = b.window ? (size_t)Np : 0, BW = b.window ? (size_t)B + 1 : 0;
     d.items = A.take<int4>(b.items.size() / 4);
     d.diag_items = A.take<int32_t>(b.diag_items.size());
     d.block_item_ptr = A.take<int32_t>((size_t)b.n_blocks + 1);
     d.block_cam = A.take<int32_t>((size_t)b.n_blocks);
     d.chunks = A.take<int4>(b.chunks.size() / 4);
     d.prob_chunk_ptr = A.take<int32_t>((size_t)B + 1);
-    d.tiles = A.take<WinTile>(b.tiles.size());
-    d.pt_mask = A.take<uint32_t>(b.pt_mask.size());
-    d.win_meta = A.take<uint32_t>(b.win_meta.size());
-    d.win_blkptr = A.take<uint32_t>(b.win_blkptr.size());
-    d.win_pairs = A.take<uint32_t>(b.win_pairs.size());
-    d.win_uv = A.take<float2>(b.win_uv.size() / 2);
-    d.win_slot = A.take<uint16_t>(b.win_slot.size());
-    d.prob_tile_ptr = A.take<int32_t>(b.prob_tile_ptr.size());
-    d.prob_part_off = A.take<int64_t>(b.prob_part_off.size());
-    d.tile_part = A.take<double>(b.window ? (size_t)b.prob_part_off.back() : 0);
-    d.tile_sums = A.take<double>(b.tiles.size() * 2);
+    d.tiles = A.take<WinTile>((size_t)b.tiles_max);
+    d.pt_mask = A.take<uint32_t>(NpW);
+    d.win_meta = A.take<uint32_t>(NeW);
+    d.win_blkptr = A.take<uint32_t>((size_t)b.blkptr_max);
+    d.win_uv = A.take<float2>(NeW);
+    d.win_slot = A.take<uint16_t>(NeW);
+    d.prob_tile_ptr = A.take<int32_t>(BW);
+    d.prob_part_off = A.take<int64_t>(BW);
+    d.prob_pt0 = A.take<int32_t>(BW);
+    d.tile_part = A.take<double>((size_t)b.part_max);
+    d.tile_sums = A.take<double>((size_t)b.tiles_max * 2);
     for (int k = 0; k < 2; ++k) {
         d.pts[k] = A.take<double>((size_t)Np * 3);
         d.pose[k] = A.take<double>((size_t)Nc * 7);
@@ -914,6 +1014,93 @@ void carve(Arena& A, DevPtrs& d, int64_t Nc, int64_t Np, int64_t Ne, int64_t B, 
 
 } // namespace
 
+namespace {
+
+// window fast path: sort, CSR, tiles, slots and pair lists are built by kernels (ba_setup.cu).
+// Returns VISO_BA_OK with *fallback = true when the problem has duplicate (point, pose) edges.
+int32_t build_window_on_device(viso_ba* h, const Built& b, const DevPtrs& d, bool* fallback)
+{
+    const int64_t Np = (int64_t)h->points.size() / 3, B = h->n_problems;
+    int32_t rc;
+    *fallback = false;
+    SetupIn in;
+    SetupWork w;
+    if (h->edges_on_device) { // staged (and validated) by set_problem; only the views are rebuilt
+        RawEdges r;
+        carve_raw(h->raw.p, r, h->n_edges_dev, B);
+        carve_scratch(h->scratch.p, w, h->n_edges_dev, B, b.tiles_max);
+        std::memset(&in, 0, sizeof(in));
+        in.n_edges = h->n_edges_dev, in.n_points = (int32_t)Np, in.n_cams = (int32_t)(h->poses.size() / 7), in.n_problems = (int32_t)B;
+        in.local_indices = h->edges_local ? 1 : 0;
+        in.e_pose = r.e_pose, in.e_point = r.e_point, in.e_uv = r.e_uv, in.edge_off = r.edge_off;
+        in.prob_cam0 = r.prob_cam0, in.prob_pt0 = r.prob_pt0;
+    } else { // incremental API or a small bulk problem: the host vectors hold global indices
+        std::vector<int64_t> cam_off((size_t)B + 1);
+        for (int64_t p = 0; p <= B; ++p) cam_off[(size_t)p] = b.prob_cam0[(size_t)p];
+        if ((rc = stage_edges_on_device(h, B, cam_off.data(), b.pt0.data(), h->edge_off_all.data(), h->e_pose.data(), h->e_point.data(),
+                 h->e_uv.data(), false, &in, &w)))
+            return rc;
+    }
+    in.prob_nfree = d.prob_nfree, in.cam_free = d.cam_free; // uploaded by the caller on the same stream
+    SetupOut o;
+    o.pt_ptr = d.pt_ptr, o.pt_prob = d.pt_prob, o.obs_cam = d.obs_cam, o.obs_uv = d.obs_uv;
+    o.prob_tile_ptr = d.prob_tile_ptr, o.prob_part_off = d.prob_part_off, o.tiles = d.tiles, o.pt_mask = d.pt_mask;
+    o.win_meta = d.win_meta, o.win_uv = d.win_uv, o.win_slot = d.win_slot, o.win_blkptr = d.win_blkptr, o.win_pairs = nullptr;
+    cudaStream_t st = h->stream;
+    run_k(h, "setup", [&] { return setup_stage1(in, w, o, st); });
+    if ((rc = pin_reserve(h, 128))) return rc;
+    char* pin = static_cast<char*>(h->pin);
+    CU(cudaMemcpyAsync(pin, w.err, 4 * sizeof(int), cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(pin + 32, w.totals, 4 * sizeof(int64_t), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    CU(cudaGetLastError());
+    if (reinterpret_cast<const int*>(pin)[1]) { // duplicate edges: the visibility-mask logic does not apply
+        *fallback = true;
+        return VISO_BA_OK;
+    }
+    const int64_t* totals = reinterpret_cast<const int64_t*>(pin + 32);
+    const int64_t n_tiles = totals[0];
+    if (n_tiles > b.tiles_max || totals[1] > b.part_max || totals[2] > b.blkptr_max || n_tiles > 0x7fffffff)
+        return fail(h, VISO_BA_ERR_STATE, "internal: tile bound exceeded (%lld tiles, bound %lld)", (long long)n_tiles, (long long)b.tiles_max);
+    run_k(h, "setup", [&] { return setup_stage2(in, w, o, (int32_t)n_tiles, st); });
+    CU(cudaMemcpyAsync(pin + 64, w.tile_list_off + n_tiles, sizeof(int64_t), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    CU(cudaGetLastError());
+    const int64_t n_pairs = n_tiles > 0 ? *reinterpret_cast<const int64_t*>(pin + 64) : 0;
+    if ((rc = devbuf_reserve(h, h->pairbuf, sizeof(uint32_t) * (size_t)std::max<int64_t>(n_pairs, 1)))) return rc;
+    o.win_pairs = static_cast<uint32_t*>(h->pairbuf.p);
+    run_k(h, "setup", [&] { return setup_stage3(in, w, o, (int32_t)n_tiles, st); });
+    CU(cudaGetLastError());
+    DevProblem& P = h->P;
+    P.n_tiles = (int32_t)n_tiles, P.n_pairs = n_pairs;
+    P.win_pairs = o.win_pairs;
+    return VISO_BA_OK;
+}
+
+// after a duplicate edge sent a device-staged problem to the general path: bring the edges back
+int32_t edges_back_to_host(viso_ba* h)
+{
+    if (!h->edges_on_device) return VISO_BA_OK;
+    const int64_t Ne = h->n_edges_dev, B = h->n_problems;
+    RawEdges r;
+    carve_raw(h->raw.p, r, Ne, B);
+    h->e_pose.resize((size_t)Ne), h->e_point.resize((size_t)Ne), h->e_uv.resize(2 * (size_t)Ne);
+    CU(cudaMemcpyAsync(h->e_pose.data(), r.e_pose, sizeof(int32_t) * (size_t)Ne, cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaMemcpyAsync(h->e_point.data(), r.e_point, sizeof(int32_t) * (size_t)Ne, cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaMemcpyAsync(h->e_uv.data(), r.e_uv, sizeof(float) * 2 * (size_t)Ne, cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    if (h->edges_local && B > 1)
+        for (int64_t b = 0; b < B; ++b)
+            for (int64_t e = h->edge_off[(size_t)b]; e < h->edge_off[(size_t)b + 1]; ++e) {
+                h->e_pose[(size_t)e] += (int32_t)h->pose_off[(size_t)b];
+                h->e_point[(size_t)e] += (int32_t)h->point_off[(size_t)b];
+            }
+    h->edges_on_device = false, h->edges_local = false, h->n_edges_dev = 0;
+    return VISO_BA_OK;
+}
+
+} // namespace
+
 extern "C" int32_t viso_ba_upload(viso_ba* h)
 {
     if (!h) return VISO_BA_ERR_ARG;
@@ -922,102 +1109,121 @@ extern "C" int32_t viso_ba_upload(viso_ba* h)
     if (rc) return rc;
     const double t0 = now_ms();
     const int64_t Nc = (int64_t)h->poses.size() / 7, Np = (int64_t)h->points.size() / 3;
-    const int64_t Ne = (int64_t)h->e_pose.size(), B = h->n_problems;
+    const int64_t B = h->n_problems;
     if (Nc < 1 || Np < 1) return fail(h, VISO_BA_ERR_STATE, "nothing to optimise: %lld poses, %lld points", (long long)Nc, (long long)Np);
     drop_graph(h);
-    Built b;
-    if ((rc = build_structure(h, b))) return rc;
-    h->max_n = b.max_n;
-    h->use_large = b.max_n > kSmallMaxN;
-    if (h->use_large && B > 1)
-        return fail(h, VISO_BA_ERR_UNSUPPORTED, "batched problems need <= %d free poses each (got a reduced system of %d)", kSmallMaxN / 6, b.max_n);
-    if (h->n_ranks > 1 && B > 1) return fail(h, VISO_BA_ERR_UNSUPPORTED, "batched problems are not sharded: run replicas instead");
-    const int ldL = (b.max_n + 8) & ~7;
-
-    DevPtrs d;
-    Arena dry;
-    carve(dry, d, Nc, Np, Ne, B, b, h->use_large, ldL);
-    if (dry.used > h->arena.cap) {
-        if (h->arena.base) {
-            CU(cudaStreamSynchronize(h->stream));
-            CU(cudaFree(h->arena.base));
-            h->arena.base = nullptr, h->arena.cap = 0;
+    for (int attempt = 0;; ++attempt) {
+        const int64_t Ne = h->edges_on_device ? h->n_edges_dev : (int64_t)h->e_pose.size();
+        Built b;
+        if ((rc = build_tables(h, b))) break;
+        if (!b.window && (rc = build_general(h, b))) break;
+        h->max_n = b.max_n;
+        h->use_large = b.max_n > kSmallMaxN;
+        if (h->use_large && B > 1) {
+            rc = fail(h, VISO_BA_ERR_UNSUPPORTED, "batched problems need <= %d free poses each (got a reduced system of %d)", kSmallMaxN / 6, b.max_n);
+            break;
         }
-        const size_t want = dry.used + dry.used / 8; // head-room so that a slightly larger window re-uses it
-        CU(cudaMalloc((void**)&h->arena.base, want));
-        h->arena.cap = want;
-    }
-    carve(h->arena, d, Nc, Np, Ne, B, b, h->use_large, ldL);
+        if (h->n_ranks > 1 && B > 1) {
+            rc = fail(h, VISO_BA_ERR_UNSUPPORTED, "batched problems are not sharded: run replicas instead");
+            break;
+        }
+        const int ldL = (b.max_n + 8) & ~7;
 
-    // topology
-    if ((rc = h2d(h, d.pt_ptr, b.pt_ptr))) return rc;
-    if ((rc = h2d(h, d.pt_prob, b.pt_prob))) return rc;
-    if ((rc = h2d(h, d.obs_cam, b.obs_cam))) return rc;
-    if ((rc = h2d(h, reinterpret_cast<float*>(d.obs_uv), b.obs_uv))) return rc;
-    if ((rc = h2d(h, d.cam_free, b.cam_free))) return rc;
-    if ((rc = h2d(h, d.cam_prob, b.cam_prob))) return rc;
-    if ((rc = h2d(h, d.prob_cam0, b.prob_cam0))) return rc;
-    if ((rc = h2d(h, d.prob_tri0, b.prob_tri0))) return rc;
-    if ((rc = h2d(h, d.prob_nfree, b.prob_nfree))) return rc;
-    if ((rc = h2d(h, reinterpret_cast<int32_t*>(d.pairs), b.pairs))) return rc;
-    if ((rc = h2d(h, reinterpret_cast<int32_t*>(d.items), b.items))) return rc;
-    if ((rc = h2d(h, d.diag_items, b.diag_items))) return rc;
-    if ((rc = h2d(h, d.block_item_ptr, b.block_item_ptr))) return rc;
-    if ((rc = h2d(h, d.block_cam, b.block_cam))) return rc;
-    if ((rc = h2d(h, reinterpret_cast<int32_t*>(d.chunks), b.chunks))) return rc;
-    if ((rc = h2d(h, d.prob_chunk_ptr, b.prob_chunk_ptr))) return rc;
-    if ((rc = h2d(h, d.tiles, b.tiles))) return rc;
-    if ((rc = h2d(h, d.pt_mask, b.pt_mask))) return rc;
-    if ((rc = h2d(h, d.win_meta, b.win_meta))) return rc;
-    if ((rc = h2d(h, d.win_blkptr, b.win_blkptr))) return rc;
-    if ((rc = h2d(h, d.win_pairs, b.win_pairs))) return rc;
-    if ((rc = h2d(h, reinterpret_cast<float*>(d.win_uv), b.win_uv))) return rc;
-    if ((rc = h2d(h, d.win_slot, b.win_slot))) return rc;
-    if ((rc = h2d(h, d.prob_tile_ptr, b.prob_tile_ptr))) return rc;
-    if ((rc = h2d(h, d.prob_part_off, b.prob_part_off))) return rc;
-    // state: normalised quaternions (Sophus keeps unit quaternions), buffer 0 current
-    std::vector<double> poses = h->poses;
-    for (int64_t c = 0; c < Nc; ++c) {
-        double* q = &poses[(size_t)c * 7];
-        const double n = 1.0 / std::sqrt(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3]);
-        for (int i = 0; i < 4; ++i) q[i] *= n;
-    }
-    if ((rc = h2d(h, d.pose_init, poses))) return rc;
-    if ((rc = h2d(h, d.pts_init, h->points))) return rc;
-    CU(cudaStreamSynchronize(h->stream)); // `poses` and `b` die at the end of this scope
+        DevPtrs d;
+        Arena dry;
+        carve(dry, d, Nc, Np, Ne, B, b, h->use_large, ldL);
+        if (dry.used > h->arena.cap) {
+            if (h->arena.base) {
+                CU(cudaStreamSynchronize(h->stream));
+                CU(cudaFree(h->arena.base));
+                h->arena.base = nullptr, h->arena.cap = 0;
+            }
+            const size_t want = dry.used + dry.used / 8; // head-room so that a slightly larger window re-uses it
+            CU(cudaMalloc((void**)&h->arena.base, want));
+            h->arena.cap = want;
+        }
+        carve(h->arena, d, Nc, Np, Ne, B, b, h->use_large, ldL);
 
-    DevProblem& P = h->P;
-    std::memset(&P, 0, sizeof(P));
-    P.n_cams = (int32_t)Nc, P.n_points = (int32_t)Np, P.n_problems = (int32_t)B;
-    P.pt_begin = h->shard_pt[(size_t)h->rank], P.pt_end = h->shard_pt[(size_t)h->rank + 1];
-    P.n_obs = Ne, P.n_pairs = b.n_pairs;
-    P.n_items = (int32_t)(b.items.size() / 4), P.n_diag_items = (int32_t)b.diag_items.size();
-    P.n_blocks = b.n_blocks, P.n_chunks = (int32_t)(b.chunks.size() / 4);
-    P.fx = h->cfg.fx, P.fy = h->cfg.fy, P.cx = h->cfg.cx, P.cy = h->cfg.cy, P.huber_delta = h->cfg.huber_delta;
-    P.pt_ptr = d.pt_ptr, P.pt_prob = d.pt_prob, P.obs_cam = d.obs_cam, P.obs_uv = d.obs_uv;
-    P.cam_free = d.cam_free, P.cam_prob = d.cam_prob, P.prob_cam0 = d.prob_cam0, P.prob_tri0 = d.prob_tri0;
-    P.prob_nfree = d.prob_nfree, P.pairs = d.pairs, P.items = d.items, P.diag_items = d.diag_items;
-    P.block_item_ptr = d.block_item_ptr, P.block_cam = d.block_cam, P.chunks = d.chunks, P.prob_chunk_ptr = d.prob_chunk_ptr;
-    for (int k = 0; k < 2; ++k) P.pts[k] = d.pts[k], P.pose[k] = d.pose[k], P.cam_rt[k] = d.cam_rt[k];
-    P.lm = d.lm, P.iter_stats = (B == 1) ? d.iter_stats : nullptr;
-    P.rec = d.rec, P.ptinfo = d.ptinfo, P.cost_pt = d.cost_pt, P.cost_new_pt = d.cost_new_pt, P.scale_pt = d.scale_pt;
-    P.item_part = d.item_part, P.S_blk = d.S_blk, P.bs = d.bs, P.dp = d.dp, P.chunk_part = d.chunk_part;
-    P.prob_sums = d.prob_sums, P.maxdiag_bits = d.maxdiag_bits, P.n_active = d.n_active;
-    P.lambda_scale = h->rank == 0 ? 1.0 : 0.0;
-    h->window = b.window;
-    P.n_tiles = (int32_t)b.tiles.size(), P.tiles = d.tiles, P.pt_mask = d.pt_mask;
-    P.win_meta = d.win_meta, P.win_blkptr = d.win_blkptr, P.win_pairs = d.win_pairs, P.win_uv = d.win_uv, P.win_slot = d.win_slot;
-    P.prob_tile_ptr = d.prob_tile_ptr, P.prob_part_off = d.prob_part_off, P.tile_part = d.tile_part, P.tile_sums = d.tile_sums;
-    h->d_pose_init = d.pose_init, h->d_pts_init = d.pts_init, h->d_pose_out = d.pose_out, h->d_pts_out = d.pts_out;
-    h->d_allreduce = d.S_blk;
-    h->allreduce_count = (size_t)b.n_blocks * 36 + (size_t)Nc * 6;
-    std::memset(&h->L, 0, sizeof(h->L));
-    if (h->use_large) {
-        h->L.n = b.max_n, h->L.ld = ldL, h->L.A = d.LA, h->L.Dd = d.LDd, h->L.x = d.Lx, h->L.fail = d.Lfail;
+        DevProblem& P = h->P;
+        std::memset(&P, 0, sizeof(P));
+        // tables every path needs
+        if ((rc = h2d(h, d.cam_free, b.cam_free))) break;
+        if ((rc = h2d(h, d.cam_prob, b.cam_prob))) break;
+        if ((rc = h2d(h, d.prob_cam0, b.prob_cam0))) break;
+        if ((rc = h2d(h, d.prob_tri0, b.prob_tri0))) break;
+        if ((rc = h2d(h, d.prob_nfree, b.prob_nfree))) break;
+        if ((rc = h2d(h, d.block_cam, b.block_cam))) break;
+        if (b.window) {
+            bool fallback = false;
+            if ((rc = build_window_on_device(h, b, d, &fallback))) break;
+            if (fallback) { // duplicate (point, pose) edges: the general path sums them correctly
+                if (attempt > 0) {
+                    rc = fail(h, VISO_BA_ERR_STATE, "internal: window fallback loop");
+                    break;
+                }
+                if ((rc = edges_back_to_host(h))) break;
+                h->no_window = true;
+                continue;
+            }
+        } else {
+            if ((rc = h2d(h, d.pt_ptr, b.pt_ptr))) break;
+            if ((rc = h2d(h, d.pt_prob, b.pt_prob))) break;
+            if ((rc = h2d(h, d.obs_cam, b.obs_cam))) break;
+            if ((rc = h2d(h, reinterpret_cast<float*>(d.obs_uv), b.obs_uv))) break;
+            if ((rc = h2d(h, reinterpret_cast<int32_t*>(d.pairs), b.pairs))) break;
+            if ((rc = h2d(h, reinterpret_cast<int32_t*>(d.items), b.items))) break;
+            if ((rc = h2d(h, d.diag_items, b.diag_items))) break;
+            if ((rc = h2d(h, d.block_item_ptr, b.block_item_ptr))) break;
+            if ((rc = h2d(h, reinterpret_cast<int32_t*>(d.chunks), b.chunks))) break;
+            if ((rc = h2d(h, d.prob_chunk_ptr, b.prob_chunk_ptr))) break;
+        }
+        // state: normalised quaternions (Sophus keeps unit quaternions), buffer 0 current
+        std::vector<double> poses = h->poses;
+        for (int64_t c = 0; c < Nc; ++c) {
+            double* q = &poses[(size_t)c * 7];
+            const double n = 1.0 / std::sqrt(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3]);
+            for (int i = 0; i < 4; ++i) q[i] *= n;
+        }
+        if ((rc = h2d(h, d.pose_init, poses))) break;
+        if ((rc = h2d(h, d.pts_init, h->points))) break;
+        CU(cudaStreamSynchronize(h->stream)); // `poses` and `b` die at the end of this scope
+
+        P.n_cams = (int32_t)Nc, P.n_points = (int32_t)Np, P.n_problems = (int32_t)B;
+        if (b.window) P.pt_begin = 0, P.pt_end = (int32_t)Np;
+        else P.pt_begin = h->shard_pt[(size_t)h->rank], P.pt_end = h->shard_pt[(size_t)h->rank + 1];
+        P.n_obs = Ne;
+        if (!b.window) P.n_pairs = b.n_pairs;
+        P.n_items = (int32_t)(b.items.size() / 4), P.n_diag_items = (int32_t)b.diag_items.size();
+        P.n_blocks = b.n_blocks, P.n_chunks = (int32_t)(b.chunks.size() / 4);
+        P.fx = h->cfg.fx, P.fy = h->cfg.fy, P.cx = h->cfg.cx, P.cy = h->cfg.cy, P.huber_delta = h->cfg.huber_delta;
+        P.pt_ptr = d.pt_ptr, P.pt_prob = d.pt_prob, P.obs_cam = d.obs_cam, P.obs_uv = d.obs_uv;
+        P.cam_free = d.cam_free, P.cam_prob = d.cam_prob, P.prob_cam0 = d.prob_cam0, P.prob_tri0 = d.prob_tri0;
+        P.prob_nfree = d.prob_nfree, P.pairs = d.pairs, P.items = d.items, P.diag_items = d.diag_items;
+        P.block_item_ptr = d.block_item_ptr, P.block_cam = d.block_cam, P.chunks = d.chunks, P.prob_chunk_ptr = d.prob_chunk_ptr;
+        for (int k = 0; k < 2; ++k) P.pts[k] = d.pts[k], P.pose[k] = d.pose[k], P.cam_rt[k] = d.cam_rt[k];
+        P.lm = d.lm, P.iter_stats = (B == 1) ? d.iter_stats : nullptr;
+        P.rec = d.rec, P.ptinfo = d.ptinfo, P.cost_pt = d.cost_pt, P.cost_new_pt = d.cost_new_pt, P.scale_pt = d.scale_pt;
+        P.item_part = d.item_part, P.S_blk = d.S_blk, P.bs = d.bs, P.dp = d.dp, P.chunk_part = d.chunk_part;
+        P.prob_sums = d.prob_sums, P.maxdiag_bits = d.maxdiag_bits, P.n_active = d.n_active;
+        P.lambda_scale = h->rank == 0 ? 1.0 : 0.0;
+        h->window = b.window;
+        P.tiles = d.tiles, P.pt_mask = d.pt_mask; // n_tiles, n_pairs, win_pairs: set by build_window_on_device
+        P.win_meta = d.win_meta, P.win_blkptr = d.win_blkptr, P.win_uv = d.win_uv, P.win_slot = d.win_slot;
+        P.prob_tile_ptr = d.prob_tile_ptr, P.prob_part_off = d.prob_part_off, P.tile_part = d.tile_part, P.tile_sums = d.tile_sums;
+        h->d_pose_init = d.pose_init, h->d_pts_init = d.pts_init, h->d_pose_out = d.pose_out, h->d_pts_out = d.pts_out;
+        h->d_allreduce = d.S_blk;
+        h->allreduce_count = (size_t)b.n_blocks * 36 + (size_t)Nc * 6;
+        std::memset(&h->L, 0, sizeof(h->L));
+        if (h->use_large) {
+            h->L.n = b.max_n, h->L.ld = ldL, h->L.A = d.LA, h->L.Dd = d.LDd, h->L.x = d.Lx, h->L.fail = d.Lfail;
+        }
+        CU(cudaMemsetAsync(d.S_blk, 0, sizeof(double) * (h->allreduce_count + (size_t)B * 2), h->stream));
+        CU(cudaMemsetAsync(d.bs, 0, sizeof(double) * (size_t)Nc * 6, h->stream));
+        CU(cudaMemsetAsync(d.dp, 0, sizeof(double) * (size_t)Nc * 6, h->stream));
+        rc = VISO_BA_OK;
+        break;
     }
-    CU(cudaMemsetAsync(d.S_blk, 0, sizeof(double) * (h->allreduce_count + (size_t)B * 2), h->stream));
-    CU(cudaMemsetAsync(d.bs, 0, sizeof(double) * (size_t)Nc * 6, h->stream));
-    CU(cudaMemsetAsync(d.dp, 0, sizeof(double) * (size_t)Nc * 6, h->stream));
+    if (rc) return rc;
     h->uploaded = true;
     if ((rc = viso_ba_reset_state(h))) {
         h->uploaded = false;
@@ -1301,8 +1507,13 @@ extern "C" int32_t viso_ba_eval_cost(viso_ba* h, double* cost)
     if (rc) return rc;
     if ((rc = ensure_cuda(h))) return rc;
     const DevProblem& P = h->P;
-    run_k(h, "eval_cost", [&] { return launch_eval_cost(P, h->stream); });
-    run_k(h, "reduce", [&] { return launch_reduce(P, 2, h->stream); });
+    if (h->window) { // the init pass of the tile kernel leaves the cost of every tile in tile_sums
+        run_k(h, "win_linearize_schur", [&] { return launch_win_linearize_schur(P, 1, 0.0, h->stream); });
+        run_k(h, "reduce", [&] { return launch_win_prob_sums(P, 1, h->stream); });
+    } else {
+        run_k(h, "eval_cost", [&] { return launch_eval_cost(P, h->stream); });
+        run_k(h, "reduce", [&] { return launch_reduce(P, 2, h->stream); });
+    }
     if ((rc = allreduce(h, P.prob_sums, 2 * (size_t)P.n_problems, kNcclSum))) return rc;
     if ((rc = pin_reserve(h, sizeof(double) * 2 * (size_t)P.n_problems))) return rc;
     CU(cudaMemcpyAsync(h->pin, P.prob_sums, sizeof(double) * 2 * (size_t)P.n_problems, cudaMemcpyDeviceToHost, h->stream));
