@@ -221,7 +221,7 @@ def run_reference(args):
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ---------------------------------------------------------------------------------------------
@@ -437,7 +437,7 @@ def run_b200(args):
         line["cpu_baseline"] = {k: v for k, v in cpu_leg(vb, args.workload, args.lm_iters, args.cpu_sample_s, args.windows).items()
                                 if k in ("value", "unit", "cores", "kind", "sample")}
     if rank == 0:
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -472,8 +472,21 @@ def others(vb, args, device):
     return out
 
 
+def emit(line):
+    """the ONE JSON line goes to the real stdout; everything else any library prints while the
+    bench runs (NCCL prints its version banner on stdout) has been sent to stderr by main()"""
+    os.write(_REAL_STDOUT, (json.dumps(line) + "\n").encode())
+
+
+_REAL_STDOUT = 1
+
+
 def main():
+    global _REAL_STDOUT
     args = parse_args()
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     if args.impl == "reference":
         run_reference(args)
     else:
