@@ -131,7 +131,7 @@ struct LargeSolve { // dense path for one problem with n > kSmallMaxN
     int32_t n;      // 6 * free poses
     int32_t ld;     // leading dimension (doubles) of A, row-major, rows 0..n (row n = rhs)
     double* A;
-    double* Dd;     // factorised diagonal blocks, [ceil(n/32)][32][32] (A's own are stale)
+    double* Dd;     // factorised diagonal blocks, [ceil(n/64)][64][64] (A's own are stale)
     double* x;      // [n]
     int32_t* fail;  // [1]
 };
@@ -147,7 +147,9 @@ int launch_block_finalize(const DevProblem& P, int init_pass, double lambda_over
 int launch_reduce(const DevProblem& P, int which, cudaStream_t st); // 0/2: cost_pt (2: even if inactive), 1: cost_new+scale
 int launch_lm_init(const DevProblem& P, double tau, double lambda_init, cudaStream_t st);
 int launch_solve_small(const DevProblem& P, int max_n, cudaStream_t st);
-int launch_solve_large(const DevProblem& P, const LargeSolve& L, cudaStream_t st);
+int launch_solve_large(const DevProblem& P, const LargeSolve& L, cudaStream_t st); // ba_dense.cu
+size_t large_solve_diag_doubles(int n); // size of LargeSolve::Dd
+int large_solve_max_n();                // largest n the dense solver takes
 int launch_update(const DevProblem& P, cudaStream_t st);
 int launch_decide(const DevProblem& P, cudaStream_t st);
 int launch_eval_cost(const DevProblem& P, cudaStream_t st); // cost of current state -> cost_pt

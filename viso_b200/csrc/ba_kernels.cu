@@ -487,208 +487,7 @@ __global__ void __launch_bounds__(256) k_solve_small(DevProblem P)
     }
 }
 
-// ------------------------------------------------------------------------------------------
-// K3 (large, one problem): dense lower matrix in global memory, rhs as row n.
-// Blocked right-looking Cholesky with NB = 32: panel kernel (diagonal block factorised
-// redundantly by every CTA + triangular solve of its rows), trailing-update kernel.
-// ------------------------------------------------------------------------------------------
-constexpr int kNB = 32;
-
-__global__ void __launch_bounds__(256) k_dense_assemble(DevProblem P, LargeSolve L)
-{ // one warp per S block (problem 0)
-    const int lane = threadIdx.x & 31;
-    const int blk = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const int nf = P.prob_nfree[0];
-    const int nblk = nf * (nf + 1) / 2;
-    if (blk == 0 && lane == 0) *L.fail = 0;
-    if (blk < nblk) {
-        int I = (int)((sqrt(8.0 * (double)blk + 1.0) - 1.0) * 0.5);
-        while ((I + 1) * (I + 2) / 2 <= blk) ++I;
-        while (I * (I + 1) / 2 > blk) --I;
-        const int J = blk - I * (I + 1) / 2;
-        for (int e = lane; e < 36; e += 32) {
-            const int r = e / 6, c = e - 6 * r;
-            L.A[(size_t)(6 * I + r) * L.ld + 6 * J + c] = P.S_blk[36 * (size_t)blk + e];
-        }
-    } else if (blk < nblk + P.n_cams) {
-        const int c = blk - nblk;
-        const int f = P.cam_free[c];
-        if (f >= 0 && lane < 6) L.A[(size_t)L.n * L.ld + 6 * f + lane] = P.bs[6 * (size_t)c + lane];
-    }
-}
-
-__global__ void __launch_bounds__(128) k_chol_panel(LargeSolve L, int j0)
-{
-    __shared__ double D[kNB][kNB + 1];
-    __shared__ int s_fail;
-    const int tid = threadIdx.x;
-    const int nb = min(kNB, L.n - j0);
-    if (tid == 0) s_fail = 0;
-    for (int idx = tid; idx < nb * nb; idx += blockDim.x) {
-        const int r = idx / nb, c = idx - r * nb;
-        D[r][c] = c <= r ? L.A[(size_t)(j0 + r) * L.ld + j0 + c] : 0.0;
-    }
-    __syncthreads();
-    for (int j = 0; j < nb; ++j) {
-        if (tid == 0) {
-            const double d = D[j][j];
-            if (!(d > 0.0) || !isfinite(d)) s_fail = 1;
-            D[j][j] = sqrt(d);
-        }
-        __syncthreads();
-        if (s_fail) break;
-        if (tid > j && tid < nb) D[tid][j] /= D[j][j];
-        __syncthreads();
-        for (int idx = tid; idx < nb * nb; idx += blockDim.x) {
-            const int r = idx / nb, c = idx - r * nb;
-            if (c > j && r >= c) D[r][c] -= D[r][j] * D[c][j];
-        }
-        __syncthreads();
-    }
-    if (s_fail) {
-        if (blockIdx.x == 0 && tid == 0) *L.fail = 1;
-        return;
-    }
-    if (blockIdx.x == 0) { // not into A: the other CTAs may still be reading the unfactorised block
-        double* dd = L.Dd + (size_t)(j0 / kNB) * kNB * kNB;
-        for (int idx = tid; idx < nb * nb; idx += blockDim.x) {
-            const int r = idx / nb, c = idx - r * nb;
-            dd[r * kNB + c] = D[r][c];
-        }
-    }
-    // rows below the diagonal block (including the rhs row n): X L^T = A  ->  one thread per row
-    const int row = j0 + nb + blockIdx.x * blockDim.x + tid;
-    if (row > L.n) return;
-    double* a = L.A + (size_t)row * L.ld + j0;
-    double x[kNB];
-#pragma unroll
-    for (int c = 0; c < kNB; ++c) x[c] = c < nb ? a[c] : 0.0;
-#pragma unroll
-    for (int c = 0; c < kNB; ++c) {
-        if (c < nb) {
-            double s = x[c];
-#pragma unroll
-            for (int k = 0; k < kNB; ++k)
-                if (k < c) s -= x[k] * D[c][k];
-            x[c] = s / D[c][c];
-        }
-    }
-#pragma unroll
-    for (int c = 0; c < kNB; ++c)
-        if (c < nb) a[c] = x[c];
-}
-
-// trailing update: A[i][l] -= sum_k P[i][k] P[l][k] over 64x64 tiles of the lower triangle
-__global__ void __launch_bounds__(256) k_chol_trail(LargeSolve L, int j0, int nb)
-{
-    __shared__ double Pi[64][kNB + 1];
-    __shared__ double Pl[64][kNB + 1];
-    if (*L.fail) return;
-    // decode the tile (ti >= tl) from the linear block index
-    const int t = blockIdx.x;
-    int ti = (int)((sqrt(8.0 * (double)t + 1.0) - 1.0) * 0.5);
-    while ((ti + 1) * (ti + 2) / 2 <= t) ++ti;
-    while (ti * (ti + 1) / 2 > t) --ti;
-    const int tl = t - ti * (ti + 1) / 2;
-    const int base = j0 + nb;
-    const int i0 = base + 64 * ti, l0 = base + 64 * tl;
-    const int tid = threadIdx.x;
-    for (int idx = tid; idx < 64 * kNB; idx += 256) {
-        const int r = idx / kNB, c = idx - r * kNB;
-        Pi[r][c] = (i0 + r <= L.n && c < nb) ? L.A[(size_t)(i0 + r) * L.ld + j0 + c] : 0.0;
-        Pl[r][c] = (l0 + r < L.n && c < nb) ? L.A[(size_t)(l0 + r) * L.ld + j0 + c] : 0.0;
-    }
-    __syncthreads();
-    const int tr = tid / 16, tc = tid % 16; // 16 x 16 threads, 4 x 4 each
-    double acc[4][4] = {};
-#pragma unroll 8
-    for (int k = 0; k < kNB; ++k) {
-        double a[4], b[4];
-#pragma unroll
-        for (int i = 0; i < 4; ++i) a[i] = Pi[tr + 16 * i][k];
-#pragma unroll
-        for (int i = 0; i < 4; ++i) b[i] = Pl[tc + 16 * i][k];
-#pragma unroll
-        for (int i = 0; i < 4; ++i)
-#pragma unroll
-            for (int j = 0; j < 4; ++j) acc[i][j] += a[i] * b[j];
-    }
-#pragma unroll
-    for (int i = 0; i < 4; ++i)
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const int r = i0 + tr + 16 * i, c = l0 + tc + 16 * j;
-            if (r <= L.n && c < L.n && c <= r) L.A[(size_t)r * L.ld + c] -= acc[i][j];
-        }
-}
-
-// L^T x = y with one CTA: y (row n) is staged in shared memory, rows of L are read contiguously
-__global__ void __launch_bounds__(1024) k_back_substitute(LargeSolve L)
-{
-    extern __shared__ double y[];
-    __shared__ double xb[kNB];
-    const int tid = threadIdx.x;
-    const int n = L.n;
-    if (*L.fail) return;
-    for (int i = tid; i < n; i += blockDim.x) y[i] = L.A[(size_t)n * L.ld + i];
-    __syncthreads();
-    for (int jb = ((n - 1) / kNB) * kNB; jb >= 0; jb -= kNB) {
-        const int nb = min(kNB, n - jb);
-        if (tid < 32) { // solve the nb x nb diagonal block with one warp
-            const double* dd = L.Dd + (size_t)(jb / kNB) * kNB * kNB;
-            for (int j = nb - 1; j >= 0; --j) {
-                const double xj = y[jb + j] / dd[j * kNB + j];
-                __syncwarp();
-                if (tid == 0) xb[j] = xj, y[jb + j] = xj;
-                if (tid < j) y[jb + tid] -= dd[j * kNB + tid] * xj;
-                __syncwarp();
-            }
-        }
-        __syncthreads();
-        for (int i = tid; i < jb; i += blockDim.x) {
-            double s = 0.0;
-            for (int j = 0; j < nb; ++j) s += L.A[(size_t)(jb + j) * L.ld + i] * xb[j];
-            y[i] -= s;
-        }
-        __syncthreads();
-    }
-    for (int i = tid; i < n; i += blockDim.x) L.x[i] = y[i];
-}
-
-__global__ void __launch_bounds__(256) k_large_finish(DevProblem P, LargeSolve L)
-{
-    __shared__ double sh[256];
-    LmState& st = P.lm[0];
-    if (!st.active) return;
-    const int fail = *L.fail;
-    const int cur = st.cur, cand = cur ^ 1;
-    const int tid = threadIdx.x;
-    for (int c = tid; c < P.n_cams; c += blockDim.x) {
-        const int f = P.cam_free[c];
-        double d[6];
-        for (int r = 0; r < 6; ++r) d[r] = (f >= 0 && !fail) ? L.x[6 * f + r] : 0.0;
-        for (int r = 0; r < 6; ++r) P.dp[6 * (size_t)c + r] = d[r];
-        const double* pc = P.pose[cur] + 7 * (size_t)c;
-        double* pn = P.pose[cand] + 7 * (size_t)c;
-        if (f >= 0 && !fail) pose_oplus(d, pc, pn);
-        else
-            for (int r = 0; r < 7; ++r) pn[r] = pc[r];
-        write_cam_rt(pn, P.cam_rt[cand] + 12 * (size_t)c);
-    }
-    double ss = 0.0;
-    if (!fail)
-        for (int i = tid; i < L.n; i += blockDim.x) ss += L.x[i] * L.x[i];
-    sh[tid] = ss;
-    __syncthreads();
-    for (int s = 128; s > 0; s >>= 1) {
-        if (tid < s) sh[tid] += sh[tid + s];
-        __syncthreads();
-    }
-    if (tid == 0) {
-        st.dp_sq = sh[0];
-        st.ok2 = fail ? 0 : 1;
-    }
-}
+// K3 (large, one problem): ba_dense.cu
 
 // ------------------------------------------------------------------------------------------
 // K4 update: one thread per point.  Back substitution through the stored records,
@@ -897,35 +696,6 @@ int launch_solve_small(const DevProblem& P, int max_n, cudaStream_t st)
     }
     k_solve_small<<<P.n_problems, 256, smem, st>>>(P);
     return 1;
-}
-
-int launch_solve_large(const DevProblem& P, const LargeSolve& L, cudaStream_t st)
-{
-    int launches = 0;
-    const int nf = L.n / 6;
-    const long long warps = (long long)nf * (nf + 1) / 2 + P.n_cams;
-    k_dense_assemble<<<cdiv(warps * 32, 256), 256, 0, st>>>(P, L);
-    ++launches;
-    for (int j0 = 0; j0 < L.n; j0 += kNB) {
-        const int nb = L.n - j0 < kNB ? L.n - j0 : kNB;
-        const int rows_below = L.n + 1 - (j0 + nb); // includes the rhs row
-        k_chol_panel<<<rows_below > 0 ? cdiv(rows_below, 128) : 1, 128, 0, st>>>(L, j0);
-        ++launches;
-        if (rows_below > 0) {
-            const int tiles = cdiv(rows_below, 64);
-            k_chol_trail<<<tiles * (tiles + 1) / 2, 256, 0, st>>>(L, j0, nb);
-            ++launches;
-        }
-    }
-    static bool configured = false;
-    const size_t smem = sizeof(double) * (size_t)L.n;
-    if (!configured) {
-        cudaFuncSetAttribute(k_back_substitute, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-        configured = true;
-    }
-    k_back_substitute<<<1, 1024, smem, st>>>(L);
-    k_large_finish<<<1, 256, 0, st>>>(P, L);
-    return launches + 2;
 }
 
 int launch_update(const DevProblem& P, cudaStream_t st)

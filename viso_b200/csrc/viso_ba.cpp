@@ -1003,7 +1003,7 @@ void carve(Arena& A, DevPtrs& d, int64_t Nc, int64_t Np, int64_t Ne, int64_t B, 
     if (large) {
         const size_t n = (size_t)b.max_n;
         d.LA = A.take<double>((n + 1) * (size_t)ldL);
-        d.LDd = A.take<double>(((n + 31) / 32) * 32 * 32);
+        d.LDd = A.take<double>(large_solve_diag_doubles((int)n));
         d.Lx = A.take<double>(n);
         d.Lfail = A.take<int32_t>(1);
     } else {
@@ -1121,6 +1121,10 @@ extern "C" int32_t viso_ba_upload(viso_ba* h)
         h->use_large = b.max_n > kSmallMaxN;
         if (h->use_large && B > 1) {
             rc = fail(h, VISO_BA_ERR_UNSUPPORTED, "batched problems need <= %d free poses each (got a reduced system of %d)", kSmallMaxN / 6, b.max_n);
+            break;
+        }
+        if (h->use_large && b.max_n > large_solve_max_n()) {
+            rc = fail(h, VISO_BA_ERR_UNSUPPORTED, "the dense reduced-system solver takes at most %d free poses (got %d)", large_solve_max_n() / 6, b.max_n / 6);
             break;
         }
         if (h->n_ranks > 1 && B > 1) {
