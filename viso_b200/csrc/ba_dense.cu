@@ -8,15 +8,19 @@
 // One PERSISTENT cooperative kernel (one CTA per SM, grid-wide barriers) replaces the former
 // chain of 2 launches per 32-column panel:
 //     for every 64-column block step
-//        P  every CTA factorises the 64x64 diagonal block redundantly in shared memory (same
-//           input, same order of operations -> same bits everywhere: no broadcast, no barrier),
+//        P  every CTA factorises the 64x64 diagonal block redundantly (same input, same order of
+//           operations -> same bits everywhere: no broadcast, no barrier): 32x32 quarters, the
+//           quarter on the diagonal by ONE warp in registers (shuffles, rsqrt on the pivot chain);
 //           then its warps solve their rows of the panel  X L_kk^T = A_panel  (one warp per row,
 //           the row lives in registers, L_kk^T is read from shared memory without conflicts)
 //        -- grid barrier --
 //        U  64x64 tiles of the trailing lower triangle:  A_il -= X_i X_l^T
 //        -- grid barrier --
-//     CTA 0: backward substitution L^T x = y (the rhs rides along as row n of A, so the forward
-//     substitution falls out of the factorisation).
+//     backward substitution L^T x = y (the rhs rides along as row n of A, so the forward
+//     substitution falls out of the factorisation): block b of x is owned by one CTA, which folds
+//     in every published x_b' (b' > b) and publishes x_b with a release flag; no grid barrier.
+// Measured on B200 (tools/chol_bench.cu, n = 1194): 786 us, of which 240 us are the pivot chain
+// (1194 columns x ~390 cycles of dependent FP64 latency) and 110 us the backward substitution.
 // Everything is fp64; nothing is atomic; the summation order is fixed by the tiling, so two runs
 // (and the ranks of a sharded solve, which all hold the same S) produce identical bits.
 #include "ba_math.cuh"
@@ -32,9 +36,43 @@ namespace {
 constexpr int kCB = 64;        // block size of the factorisation
 constexpr int kCT = 256;       // threads per CTA
 constexpr int kCS = kCB + 1;   // shared-memory row stride (doubles): odd -> column walks are conflict-free
-constexpr size_t kCholSmemFixed = sizeof(double) * (3 * (size_t)kCB * kCS + 2 * kCB);
+constexpr size_t kCholSmem = sizeof(double) * (3 * (size_t)kCB * kCS + 7 * kCB);
 
 __device__ __forceinline__ double shfl_d(double v, int src) { return __shfl_sync(0xffffffffu, v, src); }
+
+#ifdef VISO_CHOL_PROFILE // tools/chol_bench.cu: time stamps of CTA 0 at the phase boundaries
+__device__ unsigned long long g_chol_prof[16 * 512];
+__device__ __forceinline__ void prof_mark(int step, int k)
+{
+    if (blockIdx.x == 0 && threadIdx.x == 0 && step < 512) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        g_chol_prof[16 * step + k] = t;
+    }
+}
+#define PROF(step, k) prof_mark(step, k)
+#else
+#define PROF(step, k)
+#endif
+
+// Cholesky of a 32x32 block by one warp: lane i holds row i (lower part meaningful).  Column j:
+// the pivot travels by shuffle, 1/sqrt replaces sqrt + division on the serial chain, and column j
+// of L is handed to the lanes below by shuffles as well.  Returns true on a non-positive pivot.
+__device__ __forceinline__ bool warp_chol32(double (&r)[32], int lane)
+{
+    bool bad = false;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+        const double d = shfl_d(r[j], j);
+        bad |= !(d > 0.0) || !(d < 1.7e308);
+        const double inv = rsqrt(d);
+        const double l = r[j] * inv; // lane j: L_jj = d / sqrt(d)
+        r[j] = l;
+#pragma unroll
+        for (int k = j + 1; k < 32; ++k) r[k] = fma(-l, shfl_d(l, k), r[k]);
+    }
+    return bad;
+}
 
 // one warp per S block: scatter the packed 6x6 blocks (and the rhs as row n) into the dense matrix
 __global__ void __launch_bounds__(256) k_dense_assemble(DevProblem P, LargeSolve L)
@@ -64,12 +102,12 @@ __global__ void __launch_bounds__(kCT, 1) k_chol_coop(LargeSolve L)
 {
     cg::grid_group grid = cg::this_grid();
     extern __shared__ __align__(16) double smd[];
-    double* const D = smd;                   // [kCB][kCS]  diagonal block while it is factorised
+    double* const D = smd;                   // [kCB][kCS]  tile buffer (trailing update, backward substitution)
     double* const LT = D + kCB * kCS;        // [kCB][kCS]  LT[c][r] = L_kk[r][c]
     double* const T2 = LT + kCB * kCS;       // [kCB][kCS]  second tile of the trailing update
     double* const rinv = T2 + kCB * kCS;     // [kCB]       1 / L_kk[c][c]
-    double* const xb = rinv + kCB;           // [kCB]
-    double* const ysm = xb + kCB;            // [n]         CTA 0, backward substitution
+    double* const colb = rinv + kCB;         // [2][kCB]    y_b of the backward substitution
+    double* const red = colb + 2 * kCB;      // [4][kCB]    partial sums of the backward substitution
     __shared__ int s_fail;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -77,43 +115,96 @@ __global__ void __launch_bounds__(kCT, 1) k_chol_coop(LargeSolve L)
     const int G = gridDim.x;
     double* const A = L.A; // written and re-read across grid barriers: no __restrict__
     const int tx = tid & 15, ty = tid >> 4;
+    const int nblk = (n + kCB - 1) / kCB;
+    int* const flags = reinterpret_cast<int*>(L.Dd + (size_t)nblk * kCB * kCB); // [nblk] x_b published
     if (tid == 0) s_fail = 0;
+    if (blockIdx.x == 0)
+        for (int i = tid; i < nblk; i += kCT) flags[i] = 0; // visible to everybody after the first grid barrier
 
     for (int j0 = 0; j0 < n; j0 += kCB) {
         const int nb = min(kCB, n - j0);
+        PROF(j0 / kCB, 0);
         // ---------------- P: diagonal block, redundantly in every CTA ----------------
+        // 64x64 = [A11 .; A21 A22] in 32x32 quarters: warp 0 factorises A11 in registers (one row per
+        // lane, shuffles only: no block barrier inside the column chain), all warps solve
+        // L21 = A21 L11^-T and update A22 -= L21 L21^T, warp 0 factorises A22.
         for (int idx = tid; idx < kCB * kCB; idx += kCT) {
-            const int r = idx >> 6, c = idx & 63;
-            D[r * kCS + c] = (r < nb && c <= r) ? A[(size_t)(j0 + r) * ld + j0 + c] : 0.0;
+            const int rr = idx >> 6, c = idx & 63;
+            D[rr * kCS + c] = (rr < nb && c <= rr) ? A[(size_t)(j0 + rr) * ld + j0 + c] : (rr == c ? 1.0 : 0.0);
         }
         __syncthreads();
-        for (int j = 0; j < nb; ++j) {
-            const double d = D[j * kCS + j];
-            if (!(d > 0.0) || !isfinite(d)) { // every thread of every CTA sees the same d
-                s_fail = 1;
-                break;
-            }
-            const double l = sqrt(d);
-            const double inv = 1.0 / l;
-            // column j of L (into LT), rank-1 update of the rest of the lower triangle
-            for (int i = j + 1 + tid; i < nb; i += kCT) LT[j * kCS + i] = D[i * kCS + j] * inv;
-            if (tid == 0) LT[j * kCS + j] = l, rinv[j] = inv;
-            for (int i = j + 1 + ty; i < nb; i += 16) {
-                const double li = D[i * kCS + j] * inv;
-                for (int k = j + 1 + tx; k <= i; k += 16) D[i * kCS + k] -= li * (D[k * kCS + j] * inv);
+        PROF(j0 / kCB, 1);
+#pragma unroll 1
+        for (int h = 0; h < 2; ++h) {
+            const int o = 32 * h;
+            if (warp == 0) {
+                double r[32];
+#pragma unroll
+                for (int k = 0; k < 32; ++k) r[k] = D[(o + lane) * kCS + o + k];
+                const bool bad = warp_chol32(r, lane);
+                if (bad) s_fail = 1;
+#pragma unroll
+                for (int k = 0; k < 32; ++k) {
+                    if (k <= lane) LT[(o + k) * kCS + o + lane] = r[k];
+                    if (k == lane) rinv[o + k] = 1.0 / r[k];
+                }
             }
             __syncthreads();
+            if (h == 0) {
+                PROF(j0 / kCB, 2);
+                { // L21: rows 32..63, four per warp, the four chains interleaved
+                    double a4[4];
+#pragma unroll
+                    for (int t = 0; t < 4; ++t) a4[t] = D[(32 + 4 * warp + t) * kCS + lane];
+#pragma unroll 4
+                    for (int c = 0; c < 32; ++c) {
+                        const double ri = rinv[c], lc = LT[c * kCS + lane];
+#pragma unroll
+                        for (int t = 0; t < 4; ++t) {
+                            const double xc = shfl_d(a4[t], c) * ri;
+                            if (lane == c) a4[t] = xc;
+                            if (lane > c) a4[t] = fma(-xc, lc, a4[t]);
+                        }
+                    }
+#pragma unroll
+                    for (int t = 0; t < 4; ++t) {
+                        D[(32 + 4 * warp + t) * kCS + lane] = a4[t];
+                        LT[lane * kCS + 32 + 4 * warp + t] = a4[t];
+                    }
+                }
+                __syncthreads();
+                PROF(j0 / kCB, 3);
+                { // A22 -= L21 L21^T, 2 x 2 entries per thread
+                    double acc2[2][2] = {};
+#pragma unroll 8
+                    for (int k = 0; k < 32; ++k) {
+                        const double u0 = D[(32 + ty) * kCS + k], u1 = D[(48 + ty) * kCS + k];
+                        const double v0 = D[(32 + tx) * kCS + k], v1 = D[(48 + tx) * kCS + k];
+                        acc2[0][0] = fma(u0, v0, acc2[0][0]), acc2[0][1] = fma(u0, v1, acc2[0][1]);
+                        acc2[1][0] = fma(u1, v0, acc2[1][0]), acc2[1][1] = fma(u1, v1, acc2[1][1]);
+                    }
+#pragma unroll
+                    for (int a = 0; a < 2; ++a)
+#pragma unroll
+                        for (int bb = 0; bb < 2; ++bb) {
+                            const int rr = 32 + ty + 16 * a, c = 32 + tx + 16 * bb;
+                            if (c <= rr) D[rr * kCS + c] -= acc2[a][bb];
+                        }
+                }
+                __syncthreads();
+                PROF(j0 / kCB, 4);
+            }
         }
-        __syncthreads();
         if (s_fail) { // uniform over the whole grid: nobody reaches another barrier
             if (blockIdx.x == 0 && tid == 0) *L.fail = 1;
             return;
         }
+        PROF(j0 / kCB, 5);
         if (blockIdx.x == 0) { // the factor of the diagonal block, for the backward substitution
             double* dd = L.Dd + (size_t)(j0 / kCB) * kCB * kCB;
             for (int idx = tid; idx < kCB * kCB; idx += kCT) {
-                const int r = idx >> 6, c = idx & 63;
-                dd[idx] = (r < nb && c <= r) ? LT[c * kCS + r] : 0.0;
+                const int rr = idx >> 6, c = idx & 63;
+                dd[idx] = (rr < nb && c <= rr) ? LT[c * kCS + rr] : 0.0;
             }
         }
         // ---------------- P: panel rows, one warp per row (row n = rhs included) ----------------
@@ -140,7 +231,9 @@ __global__ void __launch_bounds__(kCT, 1) k_chol_coop(LargeSolve L)
             if (lane < nb) a[lane] = a0;
             if (lane + 32 < nb) a[lane + 32] = a1;
         }
+        PROF(j0 / kCB, 6);
         grid.sync();
+        PROF(j0 / kCB, 7);
         // ---------------- U: trailing update over 64x64 tiles of the lower triangle ----------------
         const int rows_below = n + 1 - base;
         if (rows_below > 0) {
@@ -183,51 +276,76 @@ __global__ void __launch_bounds__(kCT, 1) k_chol_coop(LargeSolve L)
                     }
             }
         }
+        PROF(j0 / kCB, 8);
         grid.sync();
+        PROF(j0 / kCB, 9);
     }
 
-    // ---------------- backward substitution  L^T x = y  (CTA 0; nobody syncs the grid any more) ----------------
-    if (blockIdx.x != 0) return;
-    for (int i = tid; i < n; i += kCT) ysm[i] = A[(size_t)n * ld + i];
-    __syncthreads();
-    for (int jb = ((n - 1) / kCB) * kCB; jb >= 0; jb -= kCB) {
-        const int nb = min(kCB, n - jb);
-        const double* dd = L.Dd + (size_t)(jb / kCB) * kCB * kCB;
-        for (int idx = tid; idx < kCB * kCB; idx += kCT) D[(idx >> 6) * kCS + (idx & 63)] = dd[idx]; // D[r][c] = L[r][c]
+    // ---------------- backward substitution  L^T x = y, pipelined over the CTAs with flags ----------------
+    // Block b of x belongs to CTA (nblk - 1 - b) mod G.  Its owner subtracts L[b', b]^T x_b' for every
+    // b' > b as soon as x_b' is published (the L tile is already in registers by then), solves the
+    // 64x64 triangle with one warp and publishes x_b.  Owners take their blocks top down and only
+    // ever wait for higher blocks, and all CTAs are co-resident (cooperative launch): no deadlock.
+    const int q = tid >> 6, cc = tid & 63;
+    for (int b = nblk - 1 - (int)blockIdx.x; b >= 0; b -= G) {
+        const int cb = b * kCB;
+        const int nbb = min(kCB, n - cb);
+        { // L_bb (row-major) and the reciprocals of its diagonal
+            const double* dd = L.Dd + (size_t)b * kCB * kCB;
+            for (int idx = tid; idx < kCB * kCB; idx += kCT) D[(idx >> 6) * kCS + (idx & 63)] = __ldcg(dd + idx);
+        }
+        double* const ysh = colb; // y_b (fetched before the waits)
+        if (tid < kCB) ysh[tid] = tid < nbb ? __ldcg(A + (size_t)n * ld + cb + tid) : 0.0;
+        double acc = 0.0;
+        for (int bp = nblk - 1; bp > b; --bp) {
+            const int rb = bp * kCB;
+            const int nrow = min(kCB, n - rb);
+            double t[16];
+#pragma unroll
+            for (int jj = 0; jj < 16; ++jj) {
+                const int j = q * 16 + jj;
+                t[jj] = j < nrow ? __ldcg(A + (size_t)(rb + j) * ld + cb + cc) : 0.0;
+            }
+            if (tid == 0) {
+                while (*reinterpret_cast<volatile int*>(flags + bp) == 0) {}
+                __threadfence();
+            }
+            __syncthreads();
+#pragma unroll
+            for (int jj = 0; jj < 16; ++jj) {
+                const int j = q * 16 + jj;
+                const double xj = j < nrow ? __ldcg(L.x + rb + j) : 0.0;
+                acc = fma(t[jj], xj, acc);
+            }
+        }
+        red[q * kCB + cc] = acc;
         __syncthreads();
         if (warp == 0) {
-            double y0 = lane < nb ? ysm[jb + lane] : 0.0;
-            double y1 = lane + 32 < nb ? ysm[jb + lane + 32] : 0.0;
-            for (int j = nb - 1; j >= 32; --j) {
-                const double xj = shfl_d(y1, j - 32) / D[j * kCS + j];
+            // reciprocals of the diagonal, one pair per lane: the serial chain below multiplies
+            const double ri0 = lane < nbb ? 1.0 / D[lane * kCS + lane] : 0.0;
+            const double ri1 = lane + 32 < nbb ? 1.0 / D[(lane + 32) * kCS + lane + 32] : 0.0;
+            double y0 = lane < nbb ? ysh[lane] - (red[lane] + red[kCB + lane] + red[2 * kCB + lane] + red[3 * kCB + lane]) : 0.0;
+            double y1 = lane + 32 < nbb ? ysh[lane + 32] - (red[lane + 32] + red[kCB + lane + 32] + red[2 * kCB + lane + 32] + red[3 * kCB + lane + 32]) : 0.0;
+            for (int j = nbb - 1; j >= 32; --j) {
+                const double xj = shfl_d(y1, j - 32) * shfl_d(ri1, j - 32);
                 if (lane + 32 == j) y1 = xj;
                 if (lane + 32 < j) y1 = fma(-xj, D[j * kCS + lane + 32], y1);
                 y0 = fma(-xj, D[j * kCS + lane], y0);
             }
-            for (int j = min(nb, 32) - 1; j >= 0; --j) {
-                const double xj = shfl_d(y0, j) / D[j * kCS + j];
+            for (int j = min(nbb, 32) - 1; j >= 0; --j) {
+                const double xj = shfl_d(y0, j) * shfl_d(ri0, j);
                 if (lane == j) y0 = xj;
                 if (lane < j) y0 = fma(-xj, D[j * kCS + lane], y0);
             }
-            xb[lane] = y0, xb[lane + 32] = y1;
-            if (lane < nb) ysm[jb + lane] = y0;
-            if (lane + 32 < nb) ysm[jb + lane + 32] = y1;
-        }
-        __syncthreads();
-        // y_above -= L[jb.., above]^T x_B : rows of L are contiguous in the column index
-        for (int c = tid; c < jb; c += kCT) {
-            double s0 = 0.0, s1 = 0.0;
-            int j = 0;
-            for (; j + 1 < nb; j += 2) {
-                s0 = fma(A[(size_t)(jb + j) * ld + c], xb[j], s0);
-                s1 = fma(A[(size_t)(jb + j + 1) * ld + c], xb[j + 1], s1);
-            }
-            if (j < nb) s0 = fma(A[(size_t)(jb + j) * ld + c], xb[j], s0);
-            ysm[c] -= s0 + s1;
+            if (lane < nbb) L.x[cb + lane] = y0;
+            if (lane + 32 < nbb) L.x[cb + lane + 32] = y1;
+            __threadfence();
+            __syncwarp();
+            if (lane == 0) *reinterpret_cast<volatile int*>(flags + b) = 1;
         }
         __syncthreads();
     }
-    for (int i = tid; i < n; i += kCT) L.x[i] = ysm[i];
+    PROF(nblk, 0);
 }
 
 __global__ void __launch_bounds__(256) k_large_finish(DevProblem P, LargeSolve L)
@@ -267,18 +385,21 @@ __global__ void __launch_bounds__(256) k_large_finish(DevProblem P, LargeSolve L
 
 } // namespace
 
-size_t large_solve_diag_doubles(int n) { return (size_t)((n + kCB - 1) / kCB) * kCB * kCB; }
-
-int large_solve_max_n()
-{ // the backward substitution keeps y in shared memory next to the three tiles
-    return (int)((227 * 1024 - 1024 - kCholSmemFixed) / sizeof(double));
+size_t large_solve_diag_doubles(int n)
+{ // the factorised diagonal blocks, followed by one int flag per block (backward substitution)
+    const size_t nblk = (size_t)((n + kCB - 1) / kCB);
+    return nblk * kCB * kCB + (nblk + 1) / 2;
 }
 
-int launch_solve_large(const DevProblem& P, const LargeSolve& L, cudaStream_t st)
+int large_solve_max_n() { return 6 * 5000; } // 7.2 GB of dense lower triangle; nothing else limits n
+
+// the factorisation + both substitutions alone (A assembled, x out); cooperative launch: the
+// runtime guarantees that all CTAs are co-resident, which the grid barriers need
+int launch_chol_coop(const LargeSolve& L, cudaStream_t st)
 {
     static int n_sm = 0;
     static size_t configured = 0;
-    const size_t smem = kCholSmemFixed + sizeof(double) * (size_t)L.n;
+    const size_t smem = kCholSmem;
     if (n_sm == 0) {
         int dev = 0;
         cudaGetDevice(&dev);
@@ -289,19 +410,23 @@ int launch_solve_large(const DevProblem& P, const LargeSolve& L, cudaStream_t st
         if (cudaFuncSetAttribute(k_chol_coop, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return 0;
         configured = smem;
     }
-    const int nf = L.n / 6;
-    const long long warps = (long long)nf * (nf + 1) / 2 + P.n_cams;
-    k_dense_assemble<<<(unsigned)((warps * 32 + 255) / 256), 256, 0, st>>>(P, L);
-    // cooperative launch: the runtime guarantees that all CTAs are co-resident (grid barriers)
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)n_sm), cfg.blockDim = dim3(kCT), cfg.dynamicSmemBytes = smem, cfg.stream = st;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeCooperative;
     attr[0].val.cooperative = 1;
     cfg.attrs = attr, cfg.numAttrs = 1;
-    cudaLaunchKernelEx(&cfg, k_chol_coop, L);
+    return cudaLaunchKernelEx(&cfg, k_chol_coop, L) == cudaSuccess ? 1 : 0;
+}
+
+int launch_solve_large(const DevProblem& P, const LargeSolve& L, cudaStream_t st)
+{
+    const int nf = L.n / 6;
+    const long long warps = (long long)nf * (nf + 1) / 2 + P.n_cams;
+    k_dense_assemble<<<(unsigned)((warps * 32 + 255) / 256), 256, 0, st>>>(P, L);
+    const int k = launch_chol_coop(L, st);
     k_large_finish<<<1, 256, 0, st>>>(P, L);
-    return 3;
+    return 2 + k;
 }
 
 } // namespace visoba
