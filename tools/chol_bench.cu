@@ -4,6 +4,7 @@
 //        tools/chol_bench.cu -o tools/_build/chol_bench && tools/_build/chol_bench 1194
 #include "../viso_b200/csrc/ba_dense.cu"
 
+#include <algorithm>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -15,6 +16,7 @@ int main(int argc, char** argv)
 {
     const int n = argc > 1 ? atoi(argv[1]) : 1194;
     const int reps = argc > 2 ? atoi(argv[2]) : 10;
+    const int band = argc > 3 ? atoi(argv[3]) : n; // half bandwidth in columns (entries with i - j > band are zero)
     const int ld = (n + 8) & ~7;
     std::vector<double> A((size_t)(n + 1) * ld, 0.0), M((size_t)n * 8);
     unsigned long long s = 88172645463325252ull;
@@ -24,6 +26,7 @@ int main(int argc, char** argv)
         for (int j = 0; j <= i; ++j) {
             double a = i == j ? 4.0 : 0.0;
             for (int k = 0; k < 8; ++k) a += M[(size_t)i * 8 + k] * M[(size_t)j * 8 + k];
+            if (i - j > band) a = 0.0; else if (i != j) a *= 0.1; // diagonally dominant: SPD with any band
             A[(size_t)i * ld + j] = a;
         }
     std::vector<double> xt(n), b(n, 0.0);
@@ -40,6 +43,19 @@ int main(int argc, char** argv)
     cudaMalloc(&L.Dd, large_solve_diag_doubles(n) * 8);
     cudaMalloc(&L.x, n * 8);
     cudaMalloc(&L.fail, 4);
+    const int nb64 = (n + 63) / 64;
+    std::vector<int> first(nb64), last(nb64);
+    for (int i = 0; i < nb64; ++i) first[i] = std::max(0, (64 * i - band) / 64);
+    for (int i = nb64 - 2; i >= 0; --i) first[i] = std::min(first[i], first[i + 1]);
+    for (int k = 0, i = 0; k < nb64; ++k) {
+        while (i + 1 < nb64 && first[i + 1] <= k) ++i;
+        last[k] = std::max(i, k);
+    }
+    int *dfirst, *dlast;
+    cudaMalloc(&dfirst, nb64 * 4), cudaMalloc(&dlast, nb64 * 4);
+    cudaMemcpy(dfirst, first.data(), nb64 * 4, cudaMemcpyHostToDevice);
+    cudaMemcpy(dlast, last.data(), nb64 * 4, cudaMemcpyHostToDevice);
+    L.first64 = dfirst, L.last64 = dlast;
     cudaMemset(L.fail, 0, 4);
     cudaMemcpy(dA0, A.data(), A.size() * 8, cudaMemcpyHostToDevice);
     cudaEvent_t e0, e1;

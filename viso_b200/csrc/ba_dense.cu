@@ -74,25 +74,30 @@ __device__ __forceinline__ bool warp_chol32(double (&r)[32], int lane)
     return bad;
 }
 
-// one warp per S block: scatter the packed 6x6 blocks (and the rhs as row n) into the dense matrix
+// zero the envelope of the dense matrix (row r: columns 64 * first64[r / 64] .. r); what lies left
+// of the envelope is never read or written by the solver
+__global__ void __launch_bounds__(256) k_dense_zero(LargeSolve L)
+{
+    const int r = blockIdx.x;
+    const int c0 = kCB * L.first64[r / kCB];
+    double* row = L.A + (size_t)r * L.ld;
+    for (int c = c0 + threadIdx.x; c <= r; c += blockDim.x) row[c] = 0.0;
+    if (r == 0 && threadIdx.x == 0) *L.fail = 0;
+}
+
+// one warp per stored S block: scatter the packed 6x6 blocks (and the rhs as row n) into the dense matrix
 __global__ void __launch_bounds__(256) k_dense_assemble(DevProblem P, LargeSolve L)
 {
     const int lane = threadIdx.x & 31;
     const int blk = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const int nf = P.prob_nfree[0];
-    const int nblk = nf * (nf + 1) / 2;
-    if (blk == 0 && lane == 0) *L.fail = 0;
-    if (blk < nblk) {
-        int I = (int)((sqrt(8.0 * (double)blk + 1.0) - 1.0) * 0.5);
-        while ((I + 1) * (I + 2) / 2 <= blk) ++I;
-        while (I * (I + 1) / 2 > blk) --I;
-        const int J = blk - I * (I + 1) / 2;
+    if (blk < P.n_blocks) {
+        const int2 ij = P.blk_ij[blk];
         for (int e = lane; e < 36; e += 32) {
             const int r = e / 6, c = e - 6 * r;
-            L.A[(size_t)(6 * I + r) * L.ld + 6 * J + c] = P.S_blk[36 * (size_t)blk + e];
+            L.A[(size_t)(6 * ij.x + r) * L.ld + 6 * ij.y + c] = P.S_blk[36 * (size_t)blk + e];
         }
-    } else if (blk < nblk + P.n_cams) {
-        const int c = blk - nblk;
+    } else if (blk < P.n_blocks + P.n_cams) {
+        const int c = blk - P.n_blocks;
         const int f = P.cam_free[c];
         if (f >= 0 && lane < 6) L.A[(size_t)L.n * L.ld + 6 * f + lane] = P.bs[6 * (size_t)c + lane];
     }
@@ -208,8 +213,13 @@ __global__ void __launch_bounds__(kCT, 1) k_chol_coop(LargeSolve L)
             }
         }
         // ---------------- P: panel rows, one warp per row (row n = rhs included) ----------------
+        // Only the rows inside the envelope take part: 64-row blocks up to last64[step]; below them the
+        // block column is structurally zero and stays zero (no fill outside a monotone envelope).
         const int base = j0 + nb;
-        for (int row = base + blockIdx.x * (kCT / 32) + warp; row <= n; row += G * (kCT / 32)) {
+        const int rend = min(n, (L.last64[j0 / kCB] + 1) * kCB);
+        const int nrow = max(rend - base, 0);
+        for (int qr = blockIdx.x * (kCT / 32) + warp; qr <= nrow; qr += G * (kCT / 32)) {
+            const int row = qr < nrow ? base + qr : n;
             double* a = A + (size_t)row * ld + j0;
             double a0 = lane < nb ? a[lane] : 0.0;
             double a1 = lane + 32 < nb ? a[lane + 32] : 0.0;
@@ -235,22 +245,27 @@ __global__ void __launch_bounds__(kCT, 1) k_chol_coop(LargeSolve L)
         grid.sync();
         PROF(j0 / kCB, 7);
         // ---------------- U: trailing update over 64x64 tiles of the lower triangle ----------------
-        const int rows_below = n + 1 - base;
-        if (rows_below > 0) {
-            const int nt = (rows_below + kCB - 1) / kCB;
-            const int ntile = nt * (nt + 1) / 2;
+        { // tiles (ti >= tl) of the active rows, then one tile per tl for the rhs row n
+            const int nt = (nrow + kCB - 1) / kCB;
+            const int ntri = nt * (nt + 1) / 2;
+            const int ntile = ntri + nt;
             double* const Pi = D;   // the diagonal-block buffers are free again
             double* const Pl = T2;
             for (int t = blockIdx.x; t < ntile; t += G) {
-                int ti = (int)((sqrt(8.0 * (double)t + 1.0) - 1.0) * 0.5);
-                while ((ti + 1) * (ti + 2) / 2 <= t) ++ti;
-                while (ti * (ti + 1) / 2 > t) --ti;
-                const int tl = t - ti * (ti + 1) / 2;
-                const int i0 = base + kCB * ti, l0 = base + kCB * tl;
+                const bool rhs = t >= ntri;
+                int ti = 0, tl = t - ntri;
+                if (!rhs) {
+                    ti = (int)((sqrt(8.0 * (double)t + 1.0) - 1.0) * 0.5);
+                    while ((ti + 1) * (ti + 2) / 2 <= t) ++ti;
+                    while (ti * (ti + 1) / 2 > t) --ti;
+                    tl = t - ti * (ti + 1) / 2;
+                }
+                const int i0 = rhs ? n : base + kCB * ti, l0 = base + kCB * tl;
+                const int ni = rhs ? 1 : min(kCB, n - i0); // valid rows of the tile
                 __syncthreads();
                 for (int idx = tid; idx < kCB * kCB; idx += kCT) {
                     const int r = idx >> 6, c = idx & 63;
-                    Pi[r * kCS + c] = (i0 + r <= n && c < nb) ? A[(size_t)(i0 + r) * ld + j0 + c] : 0.0;
+                    Pi[r * kCS + c] = (r < ni && c < nb) ? A[(size_t)(i0 + r) * ld + j0 + c] : 0.0;
                     Pl[r * kCS + c] = (l0 + r < n && c < nb) ? A[(size_t)(l0 + r) * ld + j0 + c] : 0.0;
                 }
                 __syncthreads();
@@ -272,7 +287,7 @@ __global__ void __launch_bounds__(kCT, 1) k_chol_coop(LargeSolve L)
 #pragma unroll
                     for (int j = 0; j < 4; ++j) {
                         const int r = i0 + ty + 16 * i, c = l0 + tx + 16 * j;
-                        if (r <= n && c < n && c <= r) A[(size_t)r * ld + c] -= acc[i][j];
+                        if (ty + 16 * i < ni && c < n && c <= r) A[(size_t)r * ld + c] -= acc[i][j];
                     }
             }
         }
@@ -297,7 +312,7 @@ __global__ void __launch_bounds__(kCT, 1) k_chol_coop(LargeSolve L)
         double* const ysh = colb; // y_b (fetched before the waits)
         if (tid < kCB) ysh[tid] = tid < nbb ? __ldcg(A + (size_t)n * ld + cb + tid) : 0.0;
         double acc = 0.0;
-        for (int bp = nblk - 1; bp > b; --bp) {
+        for (int bp = min(nblk - 1, L.last64[b]); bp > b; --bp) { // blocks below the envelope are zero
             const int rb = bp * kCB;
             const int nrow = min(kCB, n - rb);
             double t[16];
@@ -421,12 +436,12 @@ int launch_chol_coop(const LargeSolve& L, cudaStream_t st)
 
 int launch_solve_large(const DevProblem& P, const LargeSolve& L, cudaStream_t st)
 {
-    const int nf = L.n / 6;
-    const long long warps = (long long)nf * (nf + 1) / 2 + P.n_cams;
+    const long long warps = (long long)P.n_blocks + P.n_cams;
+    k_dense_zero<<<L.n, 256, 0, st>>>(L);
     k_dense_assemble<<<(unsigned)((warps * 32 + 255) / 256), 256, 0, st>>>(P, L);
     const int k = launch_chol_coop(L, st);
     k_large_finish<<<1, 256, 0, st>>>(P, L);
-    return 2 + k;
+    return 3 + k;
 }
 
 } // namespace visoba

@@ -88,6 +88,9 @@ struct DevProblem {
     const int32_t* diag_items; // indices of the items of diagonal blocks
     const int32_t* block_item_ptr; // [n_blocks+1]
     const int32_t* block_cam;  // [n_blocks] global cam of the block row if diagonal else -1
+    const int32_t* diag_blk;   // [n_cams] S block of the pose's diagonal, -1 for fixed poses
+    const int2* blk_ij;        // [n_blocks] (I, J) when only co-visible pairs are stored (large solver), else null:
+                               // the blocks of a problem are then its dense lower triangle, block = tri0 + I (I + 1) / 2 + J
     const int4* chunks;        // {problem, pt_begin, pt_end, 0}
     const int32_t* prob_chunk_ptr; // [B+1]
     // window fast path: tiles, visibility masks, per-observation meta word
@@ -134,6 +137,8 @@ struct LargeSolve { // dense path for one problem with n > kSmallMaxN
     double* Dd;     // factorised diagonal blocks, [ceil(n/64)][64][64] (A's own are stale)
     double* x;      // [n]
     int32_t* fail;  // [1]
+    const int32_t* first64; // [ceil(n/64)] envelope: first 64-column block of every 64-row block (monotone)
+    const int32_t* last64;  // [ceil(n/64)] last 64-row block with first64 <= k: the rows step k touches
 };
 
 // launchers (all asynchronous on `st`); each returns the number of kernels it launched

@@ -381,10 +381,10 @@ __global__ void k_lm_init(DevProblem P, double tau, double lambda_init)
     if (b >= P.n_problems) return;
     LmState& s = P.lm[b];
     double m = __longlong_as_double((long long)P.maxdiag_bits[b]);
-    const int tri0 = P.prob_tri0[b];
-    const int nf = P.prob_nfree[b];
-    for (int I = 0; I < nf; ++I) {
-        const double* blk = P.S_blk + 36 * (size_t)(tri0 + I * (I + 1) / 2 + I);
+    for (int c = P.prob_cam0[b]; c < P.prob_cam0[b + 1]; ++c) {
+        const int k = P.diag_blk[c];
+        if (k < 0) continue;
+        const double* blk = P.S_blk + 36 * (size_t)k;
         for (int r = 0; r < 6; ++r) m = fmax(m, fabs(blk[7 * r]));
     }
     s.chi = P.prob_sums[2 * (size_t)b];

@@ -138,6 +138,7 @@ struct viso_ba {
     DevProblem P;
     LargeSolve L;
     bool use_large = false;
+    std::vector<int32_t> blk_ij_host; // (I, J) of every stored S block when the storage is compact, else empty
     bool window = false; // tile fast path (ba_window.cu) instead of the pair-list kernels
     int max_n = 0; // largest reduced system over the problems
     double *d_pose_init = nullptr, *d_pts_init = nullptr, *d_pose_out = nullptr, *d_pts_out = nullptr;
@@ -697,6 +698,10 @@ struct Built {
     std::vector<int32_t> pairs;      // 2 per pair
     std::vector<int32_t> items;      // 4 per item
     std::vector<int32_t> diag_items, block_item_ptr, block_cam;
+    std::vector<int32_t> diag_blk;   // [Nc] S block of the pose's diagonal, -1 for fixed poses
+    std::vector<int32_t> blk_ij;     // 2 per S block: (I, J) free indices (compact storage, large solver only)
+    std::vector<int32_t> first64, last64; // envelope of the dense matrix in 64-row blocks (large solver only)
+    bool compact = false;            // S blocks stored for co-visible pose pairs only
     std::vector<int32_t> chunks;     // 4 per chunk
     std::vector<int32_t> prob_chunk_ptr;
     // window fast path: the structure is built on the device; the host only bounds its size
@@ -761,10 +766,14 @@ int32_t build_tables(viso_ba* h, Built& b)
     b.n_blocks = (int32_t)tri;
 
     b.block_cam.assign((size_t)b.n_blocks, -1);
+    b.diag_blk.assign((size_t)Nc, -1);
     for (int64_t p = 0; p < B; ++p)
         for (int32_t c = b.prob_cam0[(size_t)p]; c < b.prob_cam0[(size_t)p + 1]; ++c) {
             const int32_t f = b.cam_free[(size_t)c];
-            if (f >= 0) b.block_cam[(size_t)(b.prob_tri0[(size_t)p] + f * (f + 1) / 2 + f)] = c;
+            if (f >= 0) {
+                b.diag_blk[(size_t)c] = b.prob_tri0[(size_t)p] + f * (f + 1) / 2 + f;
+                b.block_cam[(size_t)b.diag_blk[(size_t)c]] = c;
+            }
         }
     // ---- window fast path? (every problem <= 32 keyframes and <= 27 free poses, one GPU) ----
     std::vector<int64_t> cam_off((size_t)B + 1);
@@ -792,7 +801,6 @@ int32_t build_general(viso_ba* h, Built& b)
     const int64_t Ne = (int64_t)h->e_pose.size();
     const int64_t B = h->n_problems;
     const std::vector<int64_t>& pt0 = b.pt0;
-    (void)Nc;
     b.pt_prob.assign((size_t)Np, 0);
     for (int64_t p = 0; p < B; ++p)
         for (int64_t q = pt0[(size_t)p]; q < pt0[(size_t)p + 1]; ++q) b.pt_prob[(size_t)q] = (int32_t)p;
@@ -837,9 +845,65 @@ int32_t build_general(viso_ba* h, Built& b)
     }
     const int32_t pt_begin = h->shard_pt[(size_t)h->rank], pt_end = h->shard_pt[(size_t)h->rank + 1];
 
+    // ---- large single problem: keep S blocks for co-visible pose pairs only (the structure is
+    // global: every rank of a sharded solve derives it from ALL points), and the envelope of the
+    // dense matrix the solver works in.  Small / batched problems keep the dense triangle. ----
+    std::vector<int32_t> remap;
+    b.compact = B == 1 && b.max_n > kSmallMaxN;
+    if (b.compact) {
+        const int32_t nf = b.prob_nfree[0];
+        std::vector<uint8_t> present((size_t)b.n_blocks, 0);
+        for (int32_t f = 0; f < nf; ++f) present[(size_t)f * (f + 1) / 2 + f] = 1;
+        for (int64_t p = 0; p < Np; ++p) {
+            const int32_t s0 = b.pt_ptr[(size_t)p], s1 = b.pt_ptr[(size_t)p + 1];
+            for (int32_t a = s0; a < s1; ++a) {
+                const int32_t fa = b.cam_free[(size_t)b.obs_cam[(size_t)a]];
+                if (fa < 0) continue;
+                const size_t row = (size_t)fa * (fa + 1) / 2;
+                for (int32_t c = s0; c < a; ++c) {
+                    const int32_t fc = b.cam_free[(size_t)b.obs_cam[(size_t)c]];
+                    if (fc >= 0) present[row + (size_t)fc] = 1;
+                }
+            }
+        }
+        remap.assign((size_t)b.n_blocks, -1);
+        const int nb64 = (b.max_n + 63) / 64;
+        b.first64.resize((size_t)nb64);
+        for (int i = 0; i < nb64; ++i) b.first64[(size_t)i] = i;
+        int32_t k = 0;
+        for (int32_t I = 0; I < nf; ++I)
+            for (int32_t J = 0; J <= I; ++J)
+                if (present[(size_t)I * (I + 1) / 2 + J]) {
+                    remap[(size_t)I * (I + 1) / 2 + J] = k++;
+                    b.blk_ij.push_back(I);
+                    b.blk_ij.push_back(J);
+                    const int cb = 6 * J / 64;
+                    for (int rb = 6 * I / 64; rb <= (6 * I + 5) / 64; ++rb) b.first64[(size_t)rb] = std::min(b.first64[(size_t)rb], cb);
+                }
+        // monotone envelope: a row block may not start right of the blocks below it, so that the
+        // active rows of every elimination step are one contiguous range
+        for (int i = nb64 - 2; i >= 0; --i) b.first64[(size_t)i] = std::min(b.first64[(size_t)i], b.first64[(size_t)i + 1]);
+        b.last64.resize((size_t)nb64);
+        for (int kk = 0, i = 0; kk < nb64; ++kk) {
+            while (i + 1 < nb64 && b.first64[(size_t)i + 1] <= kk) ++i;
+            b.last64[(size_t)kk] = std::max(i, kk);
+        }
+        b.n_blocks = k;
+        b.prob_tri0[1] = k;
+        b.block_cam.assign((size_t)k, -1);
+        for (int64_t c = 0; c < Nc; ++c) {
+            const int32_t f = b.cam_free[(size_t)c];
+            if (f >= 0) {
+                b.diag_blk[(size_t)c] = remap[(size_t)f * (f + 1) / 2 + f];
+                b.block_cam[(size_t)b.diag_blk[(size_t)c]] = (int32_t)c;
+            }
+        }
+    }
+
     // ---- pair list sorted by S block (two passes: count, fill) ----
     std::vector<int64_t> blk_ptr((size_t)b.n_blocks + 1, 0);
-    auto for_pairs = [&](auto&& emit) {
+    auto for_pairs = [&](auto&& emit0) {
+        auto emit = [&](int32_t blk, int32_t a, int32_t c) { emit0(b.compact ? remap[(size_t)blk] : blk, a, c); };
         for (int32_t p = pt_begin; p < pt_end; ++p) {
             const int32_t tri0 = b.prob_tri0[(size_t)b.pt_prob[(size_t)p]];
             const int32_t s0 = b.pt_ptr[(size_t)p], s1 = b.pt_ptr[(size_t)p + 1];
@@ -921,6 +985,8 @@ namespace {
 struct DevPtrs { // everything carved out of the arena, in one place so that the dry run and the
                  // real pass cannot diverge
     int32_t *pt_ptr, *pt_prob, *obs_cam, *cam_free, *cam_prob, *prob_cam0, *prob_tri0, *prob_nfree;
+    int32_t *diag_blk, *first64, *last64;
+    int2* blk_ij;
     float2* obs_uv;
     int2* pairs;
     int4 *items, *chunks;
@@ -962,6 +1028,10 @@ void carve(Arena& A, DevPtrs& d, int64_t Nc, int64_t Np, int64_t Ne, int64_t B, 
     d.diag_items = A.take<int32_t>(b.diag_items.size());
     d.block_item_ptr = A.take<int32_t>((size_t)b.n_blocks + 1);
     d.block_cam = A.take<int32_t>((size_t)b.n_blocks);
+    d.diag_blk = A.take<int32_t>((size_t)Nc);
+    d.blk_ij = A.take<int2>(b.blk_ij.size() / 2);
+    d.first64 = A.take<int32_t>(b.first64.size());
+    d.last64 = A.take<int32_t>(b.last64.size());
     d.chunks = A.take<int4>(b.chunks.size() / 4);
     d.prob_chunk_ptr = A.take<int32_t>((size_t)B + 1);
     d.tiles = A.take<WinTile>((size_t)b.tiles_max);
@@ -1157,6 +1227,10 @@ extern "C" int32_t viso_ba_upload(viso_ba* h)
         if ((rc = h2d(h, d.prob_tri0, b.prob_tri0))) break;
         if ((rc = h2d(h, d.prob_nfree, b.prob_nfree))) break;
         if ((rc = h2d(h, d.block_cam, b.block_cam))) break;
+        if ((rc = h2d(h, d.diag_blk, b.diag_blk))) break;
+        if ((rc = h2d(h, reinterpret_cast<int32_t*>(d.blk_ij), b.blk_ij))) break;
+        if ((rc = h2d(h, d.first64, b.first64))) break;
+        if ((rc = h2d(h, d.last64, b.last64))) break;
         if (b.window) {
             bool fallback = false;
             if ((rc = build_window_on_device(h, b, d, &fallback))) break;
@@ -1204,6 +1278,7 @@ extern "C" int32_t viso_ba_upload(viso_ba* h)
         P.cam_free = d.cam_free, P.cam_prob = d.cam_prob, P.prob_cam0 = d.prob_cam0, P.prob_tri0 = d.prob_tri0;
         P.prob_nfree = d.prob_nfree, P.pairs = d.pairs, P.items = d.items, P.diag_items = d.diag_items;
         P.block_item_ptr = d.block_item_ptr, P.block_cam = d.block_cam, P.chunks = d.chunks, P.prob_chunk_ptr = d.prob_chunk_ptr;
+        P.diag_blk = d.diag_blk, P.blk_ij = b.compact ? d.blk_ij : nullptr;
         for (int k = 0; k < 2; ++k) P.pts[k] = d.pts[k], P.pose[k] = d.pose[k], P.cam_rt[k] = d.cam_rt[k];
         P.lm = d.lm, P.iter_stats = (B == 1) ? d.iter_stats : nullptr;
         P.rec = d.rec, P.ptinfo = d.ptinfo, P.cost_pt = d.cost_pt, P.cost_new_pt = d.cost_new_pt, P.scale_pt = d.scale_pt;
@@ -1220,7 +1295,9 @@ extern "C" int32_t viso_ba_upload(viso_ba* h)
         std::memset(&h->L, 0, sizeof(h->L));
         if (h->use_large) {
             h->L.n = b.max_n, h->L.ld = ldL, h->L.A = d.LA, h->L.Dd = d.LDd, h->L.x = d.Lx, h->L.fail = d.Lfail;
+            h->L.first64 = d.first64, h->L.last64 = d.last64;
         }
+        h->blk_ij_host = b.compact ? b.blk_ij : std::vector<int32_t>();
         CU(cudaMemsetAsync(d.S_blk, 0, sizeof(double) * (h->allreduce_count + (size_t)B * 2), h->stream));
         CU(cudaMemsetAsync(d.bs, 0, sizeof(double) * (size_t)Nc * 6, h->stream));
         CU(cudaMemsetAsync(d.dp, 0, sizeof(double) * (size_t)Nc * 6, h->stream));
@@ -1555,16 +1632,22 @@ extern "C" int32_t viso_ba_debug_reduced_system(viso_ba* h, double lambda, int32
     CU(cudaStreamSynchronize(st));
     CU(cudaGetLastError());
     resolve_timing(h);
-    if (S)
-        for (int I = 0; I < nf; ++I)
-            for (int J = 0; J <= I; ++J) {
-                const double* x = &blk[36 * (size_t)(I * (I + 1) / 2 + J)];
-                for (int r = 0; r < 6; ++r)
-                    for (int c = 0; c < 6; ++c) {
-                        S[(size_t)(6 * I + r) * n + 6 * J + c] = x[6 * r + c];
-                        S[(size_t)(6 * J + c) * n + 6 * I + r] = x[6 * r + c];
-                    }
-            }
+    if (S) {
+        const bool compact = !h->blk_ij_host.empty();
+        if (compact) std::fill(S, S + (size_t)n * n, 0.0);
+        const int64_t nblk = compact ? (int64_t)h->blk_ij_host.size() / 2 : (int64_t)nf * (nf + 1) / 2;
+        int I = 0, J = -1;
+        for (int64_t k = 0; k < nblk; ++k) {
+            if (compact) I = h->blk_ij_host[2 * (size_t)k], J = h->blk_ij_host[2 * (size_t)k + 1];
+            else if (++J > I) ++I, J = 0;
+            const double* x = &blk[36 * (size_t)k];
+            for (int r = 0; r < 6; ++r)
+                for (int c = 0; c < 6; ++c) {
+                    S[(size_t)(6 * I + r) * n + 6 * J + c] = x[6 * r + c];
+                    S[(size_t)(6 * J + c) * n + 6 * I + r] = x[6 * r + c];
+                }
+        }
+    }
     if (bs)
         for (int c = 0; c < P.n_cams; ++c)
             if (cam_free[(size_t)c] >= 0)
