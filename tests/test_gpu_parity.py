@@ -93,6 +93,48 @@ def test_mid_size_reduced_system_uses_large_solver(vb, oracle):
     _check_against_oracle(vb, oracle, p, 6)
 
 
+def test_banded_reduced_system_envelope_solver_matches_oracle(vb, oracle):
+    """BASELINE configs[3] shape (cameras on a long trajectory, co-visibility span ~20 cameras) at a
+    size the oracle's dense Cholesky finishes in seconds: n = 894, 14 column blocks of 64, of which
+    every elimination step touches only the two or three inside the envelope; S is stored for
+    co-visible pose pairs only"""
+    p = vb.synth_config(4, n_poses=150, n_points=15000, target_edges=150000)
+    ba, _ = _check_against_oracle(vb, oracle, p, 5)
+    lam = 3.0
+    S, bs = ba.reduced_system(lam)
+    nf = len(p["poses_init"]) - 1
+    blocks = np.abs(S.reshape(nf, 6, nf, 6)).max(axis=(1, 3)) > 0
+    assert blocks.sum() < 0.5 * nf * nf  # genuinely block-sparse ...
+    assert blocks[np.arange(nf), np.arange(nf)].all()  # ... with every diagonal block present
+    rows, cols = np.nonzero(blocks)
+    assert np.abs(rows - cols).max() <= 24  # co-visibility span of this layout
+
+
+def test_c4_full_size_properties(vb):
+    """BASELINE configs[3] at full size (2k cameras, 1M points, 10M observations; n = 11994): the
+    oracle's dense solve would take minutes per iteration, so size-independent properties instead:
+    the cost the LM loop reports is the cost of the state it returns, it never increases, the run
+    reproduces bit for bit, and noise-free measurements are fitted to float32 rounding"""
+    p = vb.synth_config(4)
+    ba = _adjuster(vb, p)
+    s, stats = ba.Optimize(4, with_stats=True)
+    costs = [stats[0].cost_before] + [x.cost_after for x in stats]
+    assert all(b <= a for a, b in zip(costs, costs[1:]))
+    assert s.final_cost < 2.5 * len(p["edge_pose"])  # 1 px noise: about one unit of cost per observation
+    assert ba.eval_cost() == pytest.approx(s.final_cost, rel=1e-12)
+    poses, points = ba.poses().copy(), ba.points().copy()
+    ba2 = _adjuster(vb, p)
+    s2 = ba2.Optimize(4)
+    assert s2.final_cost == s.final_cost
+    assert np.array_equal(ba2.poses(), poses) and np.array_equal(ba2.points(), points)
+    del ba, ba2
+    q = vb.synth_config(4, noise_px=0.0)
+    bq = _adjuster(vb, q)
+    sq = bq.Optimize(15)
+    assert sq.initial_cost > 1e8
+    assert sq.final_cost < 5e-2, sq.final_cost  # float32 rounding of 2e7 pixel coordinates: ~2e-3
+
+
 @pytest.mark.parametrize("kpath", [1, 2], ids=["window", "general"])
 @pytest.mark.parametrize("path", GOLDEN, ids=[os.path.basename(x)[:-4] for x in GOLDEN])
 def test_golden_vectors(vb, path, kpath):

@@ -26,6 +26,7 @@ def main():
     ap.add_argument("--points", type=int, default=20000)
     ap.add_argument("--poses", type=int, default=60)
     ap.add_argument("--iters", type=int, default=6)
+    ap.add_argument("--config", type=int, default=3, help="synthetic layout: 3 = grid (dense-ish S), 4 = trajectory (banded S)")
     args = ap.parse_args()
     import torch
     import torch.distributed as dist
@@ -34,7 +35,7 @@ def main():
     rank, world, local = (int(os.environ.get(k, d)) for k, d in (("RANK", "0"), ("WORLD_SIZE", "1"), ("LOCAL_RANK", "0")))
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    p = vb.synth_config(3, n_poses=args.poses, n_points=args.points, target_edges=10 * args.points)
+    p = vb.synth_config(args.config, n_poses=args.poses, n_points=args.points, target_edges=10 * args.points)
     a = (p["poses_init"], p["points_init"], p["edge_pose"], p["edge_point"], p["edge_uv"])
     ba = vb.BundleAdjuster(len(a[1]), len(a[0]), len(a[2]), huber_delta=p["huber_delta"], device=local)
     ident = [vb.nccl_unique_id() if rank == 0 else None]
