@@ -247,6 +247,22 @@ PASS_OF = {"linearize": "L", "schur_blocks": "L", "block_finalize": "L", "win_li
            "update": "BC", "win_update": "BC", "solve_small": None, "solve_large": None, "reduce": None, "decide": None}
 
 
+# FP64-pipe slots (DFMA / DMUL / DADD, one slot each) per observation of one launch, from the ncu
+# capture profiles/r1b_win_kernels_full.csv: sm__pipe_fp64_cycles_active x cycles / 2 cycles per
+# warp instruction x 32 lanes / observations of the captured launch (296 windows).  The path is
+# bound by the FP64 pipe, not by HBM, so this second roof is reported beside the first.
+FP64_SLOTS_PER_OBS = {"win_linearize_schur": 662.0, "win_update": 141.0}
+
+
+def fp64_peak():
+    """measured FP64 FMA issue rate (profiles/r1_fma_peaks.json, tools/peaks.cu): T slots/s"""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r1_fma_peaks.json")) as fh:
+            return float(json.load(fh)["fp64_fma_tflops"]) / 2.0, "measured (profiles/r1_fma_peaks.json)"
+    except Exception:
+        return 148 * 64 * 1.965e9 / 1e12, "nominal 64 DFMA/clk/SM x 148 SMs x 1.965 GHz"
+
+
 def measured_peak():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as fh:
@@ -255,7 +271,7 @@ def measured_peak():
         return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
-def roofline(ktimes, trials_per_problem, sizes):
+def roofline(ktimes, trials_per_problem, sizes, nprob=1):
     """ktimes: name -> (launches, total ms) of ONE optimize call timed kernel by kernel."""
     No, Np, Nc, Nblocks = sizes
     A = algorithmic_bytes(No, Np, Nc, Nblocks)
@@ -271,14 +287,25 @@ def roofline(ktimes, trials_per_problem, sizes):
     # one launch of every member per trial (plus the init linearisation): time per launch of the pass
     t_us = sum(per_kernel[k]["avg_us"] for k in members)
     achieved = A[ps] / (t_us * 1e-6) / 1e9
+    # measured DRAM traffic of the same kernels (ncu --set full, one launch over `windows` windows of the
+    # same shape): scaled to this run's window count, per launch like `achieved`
     traffic = None
     try:
-        with open(os.path.join(ROOT, "profiles", "traffic.json")) as fh:
+        with open(os.path.join(ROOT, "profiles", "traffic_296win.json")) as fh:
             tr = json.load(fh)
-        traffic = sum(tr[k] for k in members)
+        if all(k in tr for k in members) and nprob > 1:
+            traffic = sum(tr[k] for k in members) * nprob / 296.0
     except Exception:
         pass
+    fp64 = None
+    if top in FP64_SLOTS_PER_OBS:
+        pk, src = fp64_peak()
+        ach = FP64_SLOTS_PER_OBS[top] * No / (per_kernel[top]["avg_us"] * 1e-6) / 1e12
+        fp64 = {"kernel": top, "slots_per_observation": FP64_SLOTS_PER_OBS[top], "achieved": ach, "peak": pk,
+                "unit": "T FP64 instructions/s (an FMA is one)", "frac": ach / pk, "peak_source": src,
+                "note": "the binding roof of this kernel: HBM traffic is ~7% of peak because the pair products are FP64-issue-bound"}
     return {
+        "fp64": fp64,
         "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
         "kernel": top, "pass": ps, "pass_kernels": members, "pass_us_per_launch": t_us,
         "algorithmic_bytes_per_launch": A[ps], "algorithmic_bytes_per_lm_iteration": A_iter,
@@ -393,7 +420,7 @@ def run_b200(args):
     ktimes = ba.kernel_times()
     ba.set_kernel_timing(False)
     ktimes = {k: v for k, v in ktimes.items() if k not in ("state_init", "cam_rt", "lm_init", "gather_current")}
-    roof = roofline(ktimes, trials_step / nprob, (No, Np, Nc, Nblocks))
+    roof = roofline(ktimes, trials_step / nprob, (No, Np, Nc, Nblocks), nprob)
     A_iter = roof["algorithmic_bytes_per_lm_iteration"]
     roof["iteration"] = {"achieved": A_iter * (trials_step / nprob) / (ms_per_step * 1e-3) / 1e9,
                          "frac": A_iter * (trials_step / nprob) / (ms_per_step * 1e-3) / 1e9 / roof["peak"],

@@ -55,21 +55,40 @@ __device__ __forceinline__ void prof_mark(int step, int k)
 #define PROF(step, k)
 #endif
 
-// Cholesky of a 32x32 block by one warp: lane i holds row i (lower part meaningful).  Column j:
-// the pivot travels by shuffle, 1/sqrt replaces sqrt + division on the serial chain, and column j
-// of L is handed to the lanes below by shuffles as well.  Returns true on a non-positive pivot.
-__device__ __forceinline__ bool warp_chol32(double (&r)[32], int lane)
+// Cholesky of a 32x32 block by one warp: lane i holds row i (lower part meaningful).  The serial
+// chain of the whole factorisation runs through here (B200: DFMA 8.5, SHFL of a double 30, rsqrt 66
+// cycles, tools/lat.cu).  Per column
+//     l = r[j] * inv  ->  lane j+1 forms ITS next pivot locally (r[j+1] - l^2)  ->  one shuffle
+//     broadcasts it  ->  rsqrt  (1/sqrt replaces sqrt + division),
+// while column j of L reaches the other lanes through shared memory: one 16-byte broadcast load
+// hands two entries to all 32 lanes, where shuffles cost two instructions per entry and made the
+// warp shuffle-issue-bound.  `buf` = 2 x 32 doubles of shared memory owned by the calling warp.
+// Returns true on a non-positive or non-finite pivot.
+__device__ __forceinline__ bool warp_chol32(double (&r)[32], int lane, double* buf)
 {
-    bool bad = false;
+    double d = shfl_d(r[0], 0);
+    bool bad = !(d > 0.0) || !(d < 1.7e308);
+    double inv = rsqrt(d);
 #pragma unroll
     for (int j = 0; j < 32; ++j) {
-        const double d = shfl_d(r[j], j);
-        bad |= !(d > 0.0) || !(d < 1.7e308);
-        const double inv = rsqrt(d);
         const double l = r[j] * inv; // lane j: L_jj = d / sqrt(d)
         r[j] = l;
+        double* const col = buf + 32 * (j & 1);
+        col[lane] = l;
+        __syncwarp();
+        double inv_next = 0.0;
+        if (j + 1 < 32) {
+            d = shfl_d(fma(-l, l, r[j + 1]), j + 1); // on lane j+1 this is exactly its updated diagonal
+            bad |= !(d > 0.0) || !(d < 1.7e308);
+            inv_next = rsqrt(d);
+        }
 #pragma unroll
-        for (int k = j + 1; k < 32; ++k) r[k] = fma(-l, shfl_d(l, k), r[k]);
+        for (int k0 = (j + 1) & ~1; k0 < 32; k0 += 2) {
+            const double2 lk = *reinterpret_cast<const double2*>(col + k0);
+            if (k0 > j) r[k0] = fma(-l, lk.x, r[k0]);
+            r[k0 + 1] = fma(-l, lk.y, r[k0 + 1]);
+        }
+        inv = inv_next;
     }
     return bad;
 }
@@ -111,7 +130,7 @@ __global__ void __launch_bounds__(kCT, 1) k_chol_coop(LargeSolve L)
     double* const LT = D + kCB * kCS;        // [kCB][kCS]  LT[c][r] = L_kk[r][c]
     double* const T2 = LT + kCB * kCS;       // [kCB][kCS]  second tile of the trailing update
     double* const rinv = T2 + kCB * kCS;     // [kCB]       1 / L_kk[c][c]
-    double* const colb = rinv + kCB;         // [2][kCB]    y_b of the backward substitution
+    double* const colb = rinv + kCB;         // [2][kCB]    column exchange of warp_chol32; y_b of the backward substitution
     double* const red = colb + 2 * kCB;      // [4][kCB]    partial sums of the backward substitution
     __shared__ int s_fail;
 
@@ -146,7 +165,7 @@ __global__ void __launch_bounds__(kCT, 1) k_chol_coop(LargeSolve L)
                 double r[32];
 #pragma unroll
                 for (int k = 0; k < 32; ++k) r[k] = D[(o + lane) * kCS + o + k];
-                const bool bad = warp_chol32(r, lane);
+                const bool bad = warp_chol32(r, lane, colb);
                 if (bad) s_fail = 1;
 #pragma unroll
                 for (int k = 0; k < 32; ++k) {

@@ -22,6 +22,7 @@
 #include <map>
 #include <new>
 #include <string>
+#include <thread>
 #include <vector>
 
 using namespace visoba;
@@ -100,6 +101,74 @@ struct DevBuf { // grow-only device buffer
     size_t cap = 0;
 };
 
+// std::vector<double>-like host array whose storage is page-locked when a CUDA device is usable:
+// the refined points then travel device -> this array in one DMA, without a bounce buffer
+struct PinVec {
+    double* p = nullptr;
+    size_t n = 0, cap = 0;
+    bool pinned = false;
+    PinVec() = default;
+    PinVec(const PinVec&) = delete;
+    PinVec& operator=(const PinVec&) = delete;
+    ~PinVec() { release(); }
+    size_t size() const { return n; }
+    double* data() { return p; }
+    const double* data() const { return p; }
+    void clear() { n = 0; }
+    void release()
+    {
+        if (p) pinned ? (void)cudaFreeHost(p) : std::free(p);
+        p = nullptr, cap = 0, n = 0;
+    }
+    bool reserve(size_t m, bool try_pinned)
+    {
+        if (m <= cap) return true;
+        const size_t c = std::max(m, cap + cap / 2);
+        double* q = nullptr;
+        bool pin = false;
+        if (try_pinned && c * sizeof(double) >= (1u << 16) && cudaHostAlloc(reinterpret_cast<void**>(&q), c * sizeof(double), cudaHostAllocDefault) == cudaSuccess) pin = true;
+        else {
+            if (try_pinned) (void)cudaGetLastError();
+            q = static_cast<double*>(std::malloc(c * sizeof(double)));
+        }
+        if (!q) return false;
+        if (n) std::memcpy(q, p, n * sizeof(double));
+        const size_t keep = n;
+        release();
+        p = q, cap = c, n = keep, pinned = pin;
+        return true;
+    }
+    bool append(const double* a, size_t k, bool try_pinned)
+    {
+        if (!reserve(n + k, try_pinned)) return false;
+        std::memcpy(p + n, a, k * sizeof(double));
+        n += k;
+        return true;
+    }
+};
+
+// dst <- src (n doubles) on up to 8 threads; returns the index of a non-finite entry or n
+size_t copy_and_check(double* dst, const double* src, size_t n)
+{
+    auto work = [&](size_t a, size_t b, size_t* bad) {
+        std::memcpy(dst + a, src + a, (b - a) * sizeof(double));
+        for (size_t i = a; i < b; ++i)
+            if (!std::isfinite(src[i])) {
+                *bad = i;
+                return;
+            }
+    };
+    const size_t nt = n >= (1u << 20) ? std::min<size_t>(8, std::max(1u, std::thread::hardware_concurrency())) : 1;
+    std::vector<size_t> bad(nt, n);
+    if (nt == 1) work(0, n, &bad[0]);
+    else {
+        std::vector<std::thread> th;
+        for (size_t t = 0; t < nt; ++t) th.emplace_back(work, n * t / nt, n * (t + 1) / nt, &bad[t]);
+        for (auto& t : th) t.join();
+    }
+    return *std::min_element(bad.begin(), bad.end());
+}
+
 struct KernelAcc {
     int64_t launches = 0;
     double ms = 0.0;
@@ -123,7 +192,8 @@ struct viso_ba {
     viso_ba_config cfg;
     std::string err;
     // ---- host staging (what AddPoint / AddPose / AddEdge append to) ----
-    std::vector<double> poses, points;
+    std::vector<double> poses;
+    PinVec points;
     std::vector<int32_t> e_pose, e_point;
     std::vector<float> e_uv;
     std::vector<int8_t> fixed; // -1 default policy, 0 free, 1 fixed
@@ -155,7 +225,9 @@ struct viso_ba {
     bool edges_local = false;     // raw indices are local to the edge's problem
     int64_t n_edges_dev = 0;
     std::vector<int64_t> edge_off_all; // B+1 (also for B == 1)
-    DevBuf raw, scratch, pairbuf;
+    DevBuf raw, scratch, pairbuf, pts_stage;
+    bool pts_staged = false;            // pts_stage holds the points exactly as `points` does (bulk set_problem)
+    std::vector<int32_t> stage_c0, stage_p0; // source of an H2D copy that may still be in flight
     // ---- sharding ----
     int rank = 0, n_ranks = 1;
     void* comm = nullptr;
@@ -350,7 +422,7 @@ extern "C" void viso_ba_destroy(viso_ba* h)
         resolve_timing(h);
         if (h->comm && nccl_api()) nccl_api()->CommDestroy(h->comm);
         if (h->arena.base) cudaFree(h->arena.base);
-        for (DevBuf* b : { &h->raw, &h->scratch, &h->pairbuf })
+        for (DevBuf* b : { &h->raw, &h->scratch, &h->pairbuf, &h->pts_stage })
             if (b->p) cudaFree(b->p);
         if (h->pin) cudaFreeHost(h->pin);
         if (h->ev0) cudaEventDestroy(h->ev0);
@@ -369,6 +441,7 @@ extern "C" int32_t viso_ba_clear(viso_ba* h)
     h->fixed.clear();
     h->pose_off.clear(), h->point_off.clear(), h->edge_off.clear(), h->edge_off_all.clear();
     h->edges_on_device = false, h->edges_local = false, h->n_edges_dev = 0, h->no_window = false;
+    h->pts_staged = false;
     h->n_problems = 1;
     h->uploaded = false;
     drop_graph(h);
@@ -383,7 +456,8 @@ extern "C" int64_t viso_ba_add_point(viso_ba* h, const double xyz[3])
     if (n >= h->cfg.max_points) return -(int64_t)fail(h, VISO_BA_ERR_CAPACITY, "point pool full (%lld)", (long long)h->cfg.max_points);
     for (int i = 0; i < 3; ++i)
         if (!std::isfinite(xyz[i])) return -(int64_t)fail(h, VISO_BA_ERR_NONFINITE, "point %lld is not finite", (long long)n);
-    h->points.insert(h->points.end(), xyz, xyz + 3);
+    if (!h->points.append(xyz, 3, false)) return -(int64_t)fail(h, VISO_BA_ERR_CAPACITY, "out of host memory");
+    h->pts_staged = false;
     h->uploaded = false;
     return n;
 }
@@ -522,8 +596,13 @@ bool window_shape_ok(const viso_ba* h, int64_t B, const int64_t* pose_off, int64
 }
 
 // H2D of the caller's edge arrays + validation kernel.  `local`: indices are local to the problem.
+int32_t stage_finish(viso_ba* h);
+
+// `defer`: return with the copies and the validation kernel still in flight; the caller overlaps its
+// host work with them and calls stage_finish before it returns to ITS caller
 int32_t stage_edges_on_device(viso_ba* h, int64_t B, const int64_t* pose_off, const int64_t* point_off, const int64_t* edge_off,
-    const int32_t* edge_pose, const int32_t* edge_point, const float* edge_uv, bool local, SetupIn* in_out, SetupWork* w_out)
+    const int32_t* edge_pose, const int32_t* edge_point, const float* edge_uv, bool local, SetupIn* in_out, SetupWork* w_out,
+    bool defer = false)
 {
     const int64_t Ne = edge_off[B];
     int32_t rc;
@@ -540,7 +619,8 @@ int32_t stage_edges_on_device(viso_ba* h, int64_t B, const int64_t* pose_off, co
         CU(cudaMemcpyAsync(r.e_point, edge_point, sizeof(int32_t) * (size_t)Ne, cudaMemcpyHostToDevice, st));
         CU(cudaMemcpyAsync(r.e_uv, edge_uv, sizeof(float) * 2 * (size_t)Ne, cudaMemcpyHostToDevice, st));
     }
-    std::vector<int32_t> c0((size_t)B + 1), p0((size_t)B + 1);
+    std::vector<int32_t>&c0 = h->stage_c0, &p0 = h->stage_p0;
+    c0.resize((size_t)B + 1), p0.resize((size_t)B + 1);
     for (int64_t b = 0; b <= B; ++b) c0[(size_t)b] = (int32_t)pose_off[b], p0[(size_t)b] = (int32_t)point_off[b];
     CU(cudaMemcpyAsync(r.edge_off, edge_off, sizeof(int64_t) * (size_t)(B + 1), cudaMemcpyHostToDevice, st));
     CU(cudaMemcpyAsync(r.prob_cam0, c0.data(), sizeof(int32_t) * (size_t)(B + 1), cudaMemcpyHostToDevice, st));
@@ -554,7 +634,14 @@ int32_t stage_edges_on_device(viso_ba* h, int64_t B, const int64_t* pose_off, co
     run_k(h, "setup", [&] { return setup_stage0(in, w, st); });
     if ((rc = pin_reserve(h, 64))) return rc;
     CU(cudaMemcpyAsync(h->pin, w.err, 4 * sizeof(int), cudaMemcpyDeviceToHost, st));
-    CU(cudaStreamSynchronize(st)); // the caller's arrays (and c0 / p0) are free again
+    if (in_out) *in_out = in;
+    if (w_out) *w_out = w;
+    return defer ? VISO_BA_OK : stage_finish(h);
+}
+
+int32_t stage_finish(viso_ba* h)
+{
+    CU(cudaStreamSynchronize(h->stream)); // the caller's arrays are free again
     CU(cudaGetLastError());
     const int* err = static_cast<const int*>(h->pin);
     if (err[0]) {
@@ -562,8 +649,6 @@ int32_t stage_edges_on_device(viso_ba* h, int64_t B, const int64_t* pose_off, co
         std::memcpy(&e, err + 2, sizeof(e));
         return fail(h, err[0], err[0] == VISO_BA_ERR_INDEX ? "edge %lld refers to a point or pose outside its problem" : "edge_uv of edge %lld is not finite", e);
     }
-    if (in_out) *in_out = in;
-    if (w_out) *w_out = w;
     return VISO_BA_OK;
 }
 
@@ -586,7 +671,6 @@ extern "C" int32_t viso_ba_set_problem_batched(viso_ba* h, int64_t B, const int6
             return fail(h, VISO_BA_ERR_ARG, "offsets of problem %lld decrease", (long long)b);
     int32_t rc;
     if ((rc = check_finite(h, poses7, (size_t)Nc * 7, "poses"))) return rc;
-    if ((rc = check_finite(h, points3, (size_t)Np * 3, "points"))) return rc;
     for (int64_t c = 0; c < Nc; ++c) {
         const double* q = poses7 + 7 * c;
         if (!(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3] > 1e-12)) return fail(h, VISO_BA_ERR_ARG, "pose %lld has a zero quaternion", (long long)c);
@@ -607,8 +691,36 @@ extern "C" int32_t viso_ba_set_problem_batched(viso_ba* h, int64_t B, const int6
     }
     viso_ba_clear(h);
     if (direct) {
-        if ((rc = stage_edges_on_device(h, B, pose_off, point_off, edge_off, edge_pose, edge_point, edge_uv, true, nullptr, nullptr))) return rc;
+        // edges and points leave for the device first (asynchronously when the caller's arrays are
+        // page-locked); the host-side copy and checks of the points below run while the DMA does
+        if ((rc = stage_edges_on_device(h, B, pose_off, point_off, edge_off, edge_pose, edge_point, edge_uv, true, nullptr, nullptr, true))) return rc;
+        if ((rc = devbuf_reserve(h, h->pts_stage, sizeof(double) * 3 * (size_t)Np))) {
+            cudaStreamSynchronize(h->stream);
+            return rc;
+        }
+        if (cudaMemcpyAsync(h->pts_stage.p, points3, sizeof(double) * 3 * (size_t)Np, cudaMemcpyHostToDevice, h->stream) != cudaSuccess) {
+            cudaStreamSynchronize(h->stream);
+            return fail(h, VISO_BA_ERR_CUDA, "H2D of the points failed");
+        }
+    }
+    { // host copy of the points (+ finiteness) — what GetPoint returns before Optimize
+        size_t bad = 3 * (size_t)Np;
+        const bool ok = h->points.reserve(3 * (size_t)Np, h->cuda_ok);
+        if (ok) bad = copy_and_check(h->points.data(), points3, 3 * (size_t)Np), h->points.n = 3 * (size_t)Np;
+        if (direct) {
+            rc = stage_finish(h);
+            if (!ok || bad < 3 * (size_t)Np || rc) h->points.clear();
+            if (rc) return rc;
+        }
+        if (!ok) return fail(h, VISO_BA_ERR_CAPACITY, "out of host memory");
+        if (bad < 3 * (size_t)Np) {
+            h->points.clear();
+            return fail(h, VISO_BA_ERR_NONFINITE, "points[%zu] is not finite", bad);
+        }
+    }
+    if (direct) {
         h->edges_on_device = true, h->edges_local = true, h->n_edges_dev = Ne;
+        h->pts_staged = true;
     } else {
         h->e_uv.assign(edge_uv, edge_uv + 2 * Ne);
         h->e_pose.resize((size_t)Ne);
@@ -620,7 +732,6 @@ extern "C" int32_t viso_ba_set_problem_batched(viso_ba* h, int64_t B, const int6
             }
     }
     h->poses.assign(poses7, poses7 + 7 * Nc);
-    h->points.assign(points3, points3 + 3 * Np);
     h->fixed.assign((size_t)Nc, -1);
     h->n_problems = B;
     h->edge_off_all.assign(edge_off, edge_off + B + 1);
@@ -1263,7 +1374,11 @@ extern "C" int32_t viso_ba_upload(viso_ba* h)
             for (int i = 0; i < 4; ++i) q[i] *= n;
         }
         if ((rc = h2d(h, d.pose_init, poses))) break;
-        if ((rc = h2d(h, d.pts_init, h->points))) break;
+        if (h->pts_staged) { // the points went to the device when the problem was set
+            CU(cudaMemcpyAsync(d.pts_init, h->pts_stage.p, sizeof(double) * 3 * (size_t)Np, cudaMemcpyDeviceToDevice, h->stream));
+        } else if (Np) {
+            CU(cudaMemcpyAsync(d.pts_init, h->points.data(), sizeof(double) * 3 * (size_t)Np, cudaMemcpyHostToDevice, h->stream));
+        }
         CU(cudaStreamSynchronize(h->stream)); // `poses` and `b` die at the end of this scope
 
         P.n_cams = (int32_t)Nc, P.n_points = (int32_t)Np, P.n_problems = (int32_t)B;
@@ -1507,10 +1622,12 @@ int32_t read_back(viso_ba* h)
     if (rc) return rc;
     char* pin = static_cast<char*>(h->pin);
     CU(cudaMemcpyAsync(pin, h->d_pose_out, nb_pose, cudaMemcpyDeviceToHost, h->stream));
-    CU(cudaMemcpyAsync(pin + nb_pose, h->d_pts_out, nb_pts, cudaMemcpyDeviceToHost, h->stream));
+    const bool direct = h->points.pinned; // page-locked storage: the DMA lands in place
+    CU(cudaMemcpyAsync(direct ? reinterpret_cast<char*>(h->points.data()) : pin + nb_pose, h->d_pts_out, nb_pts, cudaMemcpyDeviceToHost, h->stream));
     CU(cudaStreamSynchronize(h->stream));
     std::memcpy(h->poses.data(), pin, nb_pose);
-    std::memcpy(h->points.data(), pin + nb_pose, nb_pts);
+    if (!direct) std::memcpy(h->points.data(), pin + nb_pose, nb_pts);
+    h->pts_staged = false; // `points` now holds the refined state, the staging buffer the initial one
     return VISO_BA_OK;
 }
 
