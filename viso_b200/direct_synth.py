@@ -1,0 +1,90 @@
+"""Synthetic input for the direct pose estimator (numpy; input generation only, not a compute path).
+
+Scene: a textured plane at depth 1 in the last frame's camera (viso normalises the mean scene depth
+to 1, reference src/viso.cpp:622-637), texture = an analytic sum of sinusoids, so the current frame
+is rendered exactly (no resampling): every current pixel's ray is intersected with the plane and the
+texture evaluated at its projection into the last frame.  Intrinsics and image size are the
+reference's (src/main.cpp:14-17, :73).  Pyramids follow Keyframe's constructor (include/keyframe.h:
+29-45): cv::pyrDown to half size, 4 levels; if cv2 is missing a 2x2 box filter stands in.
+"""
+import numpy as np
+
+FX, FY, CX, CY = 517.3, 516.5, 325.1, 249.7
+W, H = 640, 480
+
+
+def quat_to_R(q):
+    x, y, z, w = q
+    return np.array([[1 - 2 * (y * y + z * z), 2 * (x * y - z * w), 2 * (x * z + y * w)],
+                     [2 * (x * y + z * w), 1 - 2 * (x * x + z * z), 2 * (y * z - x * w)],
+                     [2 * (x * z - y * w), 2 * (y * z + x * w), 1 - 2 * (x * x + y * y)]])
+
+
+def pose_from_rotvec(rv, t):
+    rv = np.asarray(rv, dtype=np.float64)
+    th = np.linalg.norm(rv)
+    if th < 1e-12:
+        q = np.array([0.5 * rv[0], 0.5 * rv[1], 0.5 * rv[2], 1.0])
+    else:
+        q = np.concatenate([np.sin(0.5 * th) * rv / th, [np.cos(0.5 * th)]])
+    q /= np.linalg.norm(q)
+    return np.concatenate([q, np.asarray(t, dtype=np.float64)])
+
+
+def _texture(rng, n_waves=24):
+    freq = rng.uniform(0.02, 0.35, size=(n_waves, 2)) * rng.choice([-1.0, 1.0], size=(n_waves, 2))
+    phase = rng.uniform(0, 2 * np.pi, size=n_waves)
+    amp = rng.uniform(6.0, 22.0, size=n_waves)
+
+    def T(u, v):
+        s = np.full(np.shape(u), 128.0)
+        for (a, b), p, m in zip(freq, phase, amp):
+            s = s + m * np.sin(a * u + b * v + p)
+        return s
+    return T
+
+
+def pyramid(img, levels=4):
+    pyr = [np.ascontiguousarray(img)]
+    try:
+        import cv2
+        for _ in range(1, levels):
+            prev = pyr[-1]
+            pyr.append(np.ascontiguousarray(cv2.pyrDown(prev, dstsize=(prev.shape[1] // 2, prev.shape[0] // 2))))
+    except ImportError:
+        for _ in range(1, levels):
+            p = pyr[-1].astype(np.float64)
+            h, w = (p.shape[0] // 2) * 2, (p.shape[1] // 2) * 2
+            q = 0.25 * (p[0:h:2, 0:w:2] + p[1:h:2, 0:w:2] + p[0:h:2, 1:w:2] + p[1:h:2, 1:w:2])
+            pyr.append(np.ascontiguousarray(np.clip(np.rint(q), 0, 255).astype(np.uint8)))
+    return pyr
+
+
+def synth_scene(seed=1, n_points=2000, rotvec=(0.004, -0.006, 0.003), trans=(0.012, -0.008, 0.01),
+                init_noise=0.0, width=W, height=H):
+    """Returns dict: ref_pyr, cur_pyr (lists of 4 uint8 images), points [n][3] (world = last frame's
+    camera frame), ref_pose [7] (identity), true_pose [7] (current frame), init_pose [7]."""
+    rng = np.random.default_rng(seed)
+    T = _texture(rng)
+    uu, vv = np.meshgrid(np.arange(width, dtype=np.float64), np.arange(height, dtype=np.float64))
+    ref = np.clip(np.rint(T(uu, vv)), 0, 255).astype(np.uint8)
+    true_pose = pose_from_rotvec(rotvec, trans)
+    R, t = quat_to_R(true_pose[:4]), true_pose[4:]
+    # current pixel -> ray -> plane z_ref = 1 -> last frame's pixel
+    d = np.stack([(uu - CX) / FX, (vv - CY) / FY, np.ones_like(uu)], axis=-1)
+    Rt_d = d @ R  # rows: R^T d
+    Rt_t = R.T @ t
+    s = (1.0 + Rt_t[2]) / Rt_d[..., 2]
+    Xr = Rt_d * s[..., None] - Rt_t
+    ur, vr = FX * Xr[..., 0] / Xr[..., 2] + CX, FY * Xr[..., 1] / Xr[..., 2] + CY
+    cur = np.clip(np.rint(T(ur, vr)), 0, 255).astype(np.uint8)
+    # map points on the plane, spread over the image with a margin
+    pu = rng.uniform(30, width - 30, size=n_points)
+    pv = rng.uniform(30, height - 30, size=n_points)
+    pts = np.stack([(pu - CX) / FX, (pv - CY) / FY, np.ones(n_points)], axis=-1)
+    init = true_pose.copy() if init_noise == 0.0 else None
+    if init is None:
+        init = pose_from_rotvec(np.asarray(rotvec) + rng.normal(0, init_noise, 3), np.asarray(trans) + rng.normal(0, init_noise, 3))
+    return {"ref_pyr": pyramid(ref), "cur_pyr": pyramid(cur), "points": pts,
+            "ref_pose": np.array([0, 0, 0, 1.0, 0, 0, 0]), "true_pose": true_pose, "init_pose": init,
+            "identity": np.array([0, 0, 0, 1.0, 0, 0, 0])}
