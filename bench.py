@@ -500,7 +500,54 @@ def others(vb, args, device):
             ba.close()
         except Exception as e:  # context only: never fail the headline because of it
             out[name] = {"error": str(e)}
+    try:
+        out["direct_pose"] = direct_leg(device, cpu=not args.no_cpu)
+    except Exception as e:
+        out["direct_pose"] = {"error": str(e)}
     return out
+
+
+def direct_leg(device, cpu=True, n_points=2000, batch=128):
+    """the tracker's direct pose estimation, reference src/viso.cpp:661-774, on a
+    synthetic 640x480 frame pair with 2000 map points.  Unit: Gauss-Newton iterations/s (one iteration =
+    one pass over all points x 64 patch pixels + the 6x6 solve); kernel time by CUDA events inside the
+    C ABI call.  `reference_loop` is the loop as the reference writes it (one step per level), `repaired`
+    iterates to convergence; `batched` runs `batch` independent frames in one launch."""
+    from viso_b200 import direct
+    from viso_b200.direct_synth import synth_scene
+    sc = synth_scene(seed=11, n_points=n_points)
+    res = {"points": n_points, "patch_pixels": 64, "image": "640x480, 4 levels", "unit": "GN iterations/s"}
+
+    def run(frames, ref_term, reps=20):
+        est = direct.DirectPoseEstimator(max_points=n_points, frames=frames, device=device, reference_termination=ref_term)
+        for f in range(frames):
+            est.set_pyramid(0, sc["ref_pyr"], frame=f)
+            est.set_pyramid(1, sc["cur_pyr"], frame=f)
+        est.set_points(sc["points"])
+        init = np.tile(sc["identity"], (frames, 1))
+        ms = []
+        for i in range(reps + 3):
+            pose, st, m = est.DirectPoseEstimationMultiLayer(init)
+            if i >= 3:
+                ms.append(m)
+        its = sum(s.iterations for fr in st for s in fr)
+        m = float(np.median(ms))
+        est.close()
+        return {"frames": frames, "gn_iterations": its, "kernel_ms": m, "value": its / (m * 1e-3),
+                "us_per_iteration_per_frame": 1e3 * m * frames / its, "frames_per_sec": frames / (m * 1e-3),
+                "pose_error": float(np.abs(np.reshape(pose, (-1, 7))[0] - sc["true_pose"]).max())}
+    res["reference_loop"] = run(1, 1)
+    res["repaired"] = run(1, 0)
+    res["batched"] = run(batch, 0, reps=5)
+    if cpu:
+        import direct_oracle_lib as dorc
+        t0 = time.perf_counter()
+        _, st = dorc.multi_layer(dorc.cfg(reference_termination=0), sc["ref_pyr"], sc["cur_pyr"], sc["ref_pose"], sc["identity"], sc["points"])
+        dt = time.perf_counter() - t0
+        its = sum(s.iterations for s in st)
+        res["cpu_baseline"] = {"value": its / dt, "unit": "GN iterations/s", "cores": 1, "kind": "port",
+                               "sample": "one frame, repaired loop, %d iterations, oracle/direct_oracle.c single-threaded like the reference" % its}
+    return res
 
 
 def emit(line):

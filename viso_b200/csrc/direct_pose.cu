@@ -9,7 +9,7 @@
 //   Keyframe::IsInside / Project           include/keyframe.h:76-89
 //
 // B200 design: the whole multi-level Gauss-Newton loop of one frame is ONE kernel launch by ONE
-// thread-block cluster (8 CTAs x 512 threads).  A warp owns a point at a time and its 32 lanes own
+// thread-block cluster (16 CTAs x 512 threads; 8 CTAs when many frames are batched).  A warp owns a point at a time and its 32 lanes own
 // two pixels of the 8x8 patch each; every lane keeps the 21 + 6 + 1 sums (upper triangle of H, b,
 // cost) in registers over all points of its warp.  The sums are folded with a fixed butterfly
 // inside the warp, in warp order inside the CTA, and in rank order across the cluster through
@@ -36,8 +36,9 @@ namespace cg = cooperative_groups;
 
 namespace visodirect {
 
-constexpr int kCluster = 8;    // CTAs per frame (portable cluster size)
-constexpr int kThreads = 256;  // threads per CTA
+constexpr int kClusterMax = 16;  // CTAs per frame when few frames run: the largest (non-portable) cluster a B200 schedules
+constexpr int kClusterBatch = 8; // ... and when many frames run: the portable size packs the GPCs better
+constexpr int kThreads = 512;  // threads per CTA
 constexpr int kWarps = kThreads / 32;
 constexpr int kSums = 28;      // 21 (upper triangle of H) + 6 (b) + 1 (cost)
 constexpr int kLevels = VISO_DIRECT_MAX_LEVELS;
@@ -123,35 +124,78 @@ __device__ void inverse_times(const double* H, const double* b, double* x)
     }
 }
 
+// Gauss-Newton state of one frame on one level: lives in rank 0's shared memory, touched by its thread 0
+struct GnState {
+    double T21[7], best[7];
+    double cost, lastCost;
+    int applied, reason, nGood, pad;
+};
+
+// viso.cpp:735-757: solve, update, and the reference's termination decisions.  Returns 1 when the
+// level is finished.  Kept out of line so that its 6x12 elimination tableau does not cost the
+// accumulation loop its registers.
+__device__ __noinline__ int gn_decide(GnState& st, const double* tot, const DevParams& K, int iter)
+{
+    double H[36], b[6], update[6];
+    int e = 0;
+    for (int r = 0; r < 6; ++r)
+        for (int q = r; q < 6; ++q) H[6 * r + q] = H[6 * q + r] = tot[e++];
+    for (int q = 0; q < 6; ++q) b[q] = tot[21 + q];
+    st.nGood = (int)tot[kSums];
+    st.cost = (K.reference_termination ? st.cost : 0.0) + tot[27]; // never reset in the reference (viso.cpp:673, :725)
+    inverse_times(H, b, update);                  // viso.cpp:735
+    double next[7];
+    visoba::pose_oplus(update, st.T21, next);     // viso.cpp:737
+    for (int k = 0; k < 7; ++k) st.T21[k] = next[k];
+    ++st.applied;
+    st.cost /= st.nGood;                          // viso.cpp:739
+    if (isnan(update[0])) {                       // viso.cpp:741-744
+        for (int k = 0; k < 7; ++k) st.T21[k] = st.best[k];
+        st.reason = 1;
+        return 1;
+    }
+    if (iter > 0 && st.cost > st.lastCost) {      // viso.cpp:746-749
+        for (int k = 0; k < 7; ++k) st.T21[k] = st.best[k];
+        st.reason = 2;
+        return 1;
+    }
+    if ((K.reference_termination || iter > 0) && (1 - st.cost / st.lastCost) < K.delta_thresh) {
+        st.reason = 3;                            // viso.cpp:751-753
+        return 1;
+    }
+    for (int k = 0; k < 7; ++k) st.best[k] = st.T21[k]; // viso.cpp:755-756
+    st.lastCost = st.cost;
+    return 0;
+}
+
 // ------------------------------------------------------------------------------------------
 // One cluster per frame: Gauss-Newton over the levels level_hi .. level_lo (viso.cpp:661-774),
 // or (linearize_only) the sums of one linearisation at the given pose.
 // ------------------------------------------------------------------------------------------
-__global__ void __cluster_dims__(kCluster, 1, 1) __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kThreads, 1)
 k_direct(const DevFrame* __restrict__ frames, const DevParams K, double* __restrict__ poses,
     viso_direct_level_stats* __restrict__ stats, int level_hi, int level_lo, int linearize_only,
     double* __restrict__ lin_out)
 {
     cg::cluster_group cluster = cg::this_cluster();
-    const int rank = (int)cluster.block_rank();
-    const int f = blockIdx.x / kCluster;
+    const int rank = (int)cluster.block_rank(), n_ranks = (int)cluster.num_blocks();
+    const int f = blockIdx.x / n_ranks;
     const DevFrame& F = frames[f];
 
     __shared__ double s_warp[kWarps][kSums + 1]; // [.][kSums] = good points (exact in a double)
     __shared__ double s_part[kSums + 1];         // this CTA's sums; read by rank 0 through DSMEM
     __shared__ double s_tot[kSums + 1];
-    __shared__ double s_pose[8];                 // rank 0: the pose every CTA linearises at
+    __shared__ GnState s_gn;                     // rank 0: s_gn.T21 is the pose every CTA linearises at
     __shared__ int s_flag;                       // rank 0: 1 = the level is finished
     __shared__ double s_rt[12], s_ref_rt[12];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int gw = rank * kWarps + warp, nw = kCluster * kWarps;
+    const int gw = rank * kWarps + warp, nw = n_ranks * kWarps;
     const int side = 2 * K.hp, npix = side * side;
     const double hp = (double)K.hp;
 
-    double T21[7], best[7]; // live in thread 0 of rank 0 only
     if (rank == 0 && tid == 0) {
-        for (int k = 0; k < 7; ++k) T21[k] = poses[7 * (size_t)f + k], s_pose[k] = T21[k];
+        for (int k = 0; k < 7; ++k) s_gn.T21[k] = poses[7 * (size_t)f + k];
         s_flag = 0;
     }
     if (tid == 0) visoba::write_cam_rt(F.ref_pose, s_ref_rt);
@@ -160,14 +204,15 @@ k_direct(const DevFrame* __restrict__ frames, const DevParams K, double* __restr
     for (int level = level_hi; level >= level_lo; --level) {
         const double scale = 1.0 / (double)(1 << level); // 1, 0.5, 0.25, 0.125 (viso.cpp:666)
         const DevImage ref = F.ref[level], cur = F.cur[level];
-        double cost = 0, lastCost = 0; // viso.cpp:673
-        int applied = 0, reason = 0, nGood = 0;
-        if (rank == 0 && tid == 0)
-            for (int k = 0; k < 7; ++k) best[k] = T21[k]; // viso.cpp:676
+        if (rank == 0 && tid == 0) {
+            s_gn.cost = 0, s_gn.lastCost = 0; // viso.cpp:673
+            s_gn.applied = 0, s_gn.reason = 0, s_gn.nGood = 0;
+            for (int k = 0; k < 7; ++k) s_gn.best[k] = s_gn.T21[k]; // viso.cpp:676
+        }
 
         for (int iter = 0; iter < K.max_iterations; ++iter) {
             { // the pose published by rank 0 (current_frame->SetR / SetT, viso.cpp:682-683)
-                const double* rp = cluster.map_shared_rank(s_pose, 0);
+                const double* rp = cluster.map_shared_rank(s_gn.T21, 0);
                 if (tid == 0) {
                     double p[7];
                     for (int k = 0; k < 7; ++k) p[k] = rp[k];
@@ -236,48 +281,22 @@ k_direct(const DevFrame* __restrict__ frames, const DevParams K, double* __restr
             if (rank == 0) {
                 if (tid <= kSums) {
                     double s = 0.0;
-                    for (int r = 0; r < kCluster; ++r) s += cluster.map_shared_rank(s_part, r)[tid];
+                    for (int r = 0; r < n_ranks; ++r) s += cluster.map_shared_rank(s_part, r)[tid];
                     s_tot[tid] = s;
                 }
                 __syncthreads();
                 if (tid == 0) {
-                    double H[36], b[6], update[6];
-                    int e = 0;
-                    for (int r = 0; r < 6; ++r)
-                        for (int q = r; q < 6; ++q) H[6 * r + q] = H[6 * q + r] = s_tot[e++];
-                    for (int q = 0; q < 6; ++q) b[q] = s_tot[21 + q];
-                    nGood = (int)s_tot[kSums];
-                    int flag;
                     if (linearize_only) {
                         double* o = lin_out + 44 * (size_t)f;
-                        for (int q = 0; q < 36; ++q) o[q] = H[q];
-                        for (int q = 0; q < 6; ++q) o[36 + q] = b[q];
-                        o[42] = s_tot[27], o[43] = (double)nGood;
-                        flag = 1;
+                        int e = 0;
+                        for (int r = 0; r < 6; ++r)
+                            for (int q = r; q < 6; ++q) o[6 * r + q] = o[6 * q + r] = s_tot[e++];
+                        for (int q = 0; q < 6; ++q) o[36 + q] = s_tot[21 + q];
+                        o[42] = s_tot[27], o[43] = s_tot[kSums];
+                        s_flag = 1;
                     } else {
-                        cost = (K.reference_termination ? cost : 0.0) + s_tot[27]; // never reset in the reference
-                        inverse_times(H, b, update);            // viso.cpp:735
-                        double next[7];
-                        visoba::pose_oplus(update, T21, next);  // viso.cpp:737
-                        for (int k = 0; k < 7; ++k) T21[k] = next[k];
-                        ++applied;
-                        cost /= nGood;                           // viso.cpp:739
-                        if (isnan(update[0])) {                  // viso.cpp:741-744
-                            for (int k = 0; k < 7; ++k) T21[k] = best[k];
-                            reason = 1, flag = 1;
-                        } else if (iter > 0 && cost > lastCost) { // viso.cpp:746-749
-                            for (int k = 0; k < 7; ++k) T21[k] = best[k];
-                            reason = 2, flag = 1;
-                        } else if ((K.reference_termination || iter > 0) && (1 - cost / lastCost) < K.delta_thresh) {
-                            reason = 3, flag = 1;                // viso.cpp:751-753
-                        } else {
-                            for (int k = 0; k < 7; ++k) best[k] = T21[k]; // viso.cpp:755-756
-                            lastCost = cost;
-                            flag = 0;
-                        }
+                        s_flag = gn_decide(s_gn, s_tot, K, iter);
                     }
-                    for (int k = 0; k < 7; ++k) s_pose[k] = T21[k];
-                    s_flag = flag;
                 }
             }
             cluster.sync();
@@ -285,13 +304,13 @@ k_direct(const DevFrame* __restrict__ frames, const DevParams K, double* __restr
         }
         if (rank == 0 && tid == 0 && stats && !linearize_only) {
             viso_direct_level_stats& st = stats[kLevels * (size_t)f + level];
-            st.iterations = applied, st.n_good = nGood, st.stop_reason = reason, st.reserved = 0;
-            st.cost = cost, st.last_cost = lastCost;
+            st.iterations = s_gn.applied, st.n_good = s_gn.nGood, st.stop_reason = s_gn.reason, st.reserved = 0;
+            st.cost = s_gn.cost, st.last_cost = s_gn.lastCost;
         }
         if (linearize_only) break;
     }
     if (rank == 0 && tid == 0 && !linearize_only)
-        for (int k = 0; k < 7; ++k) poses[7 * (size_t)f + k] = T21[k];
+        for (int k = 0; k < 7; ++k) poses[7 * (size_t)f + k] = s_gn.T21[k];
     cluster.sync(); // nobody leaves while its shared memory may still be read by a peer
 }
 
@@ -542,6 +561,30 @@ int32_t viso_direct_set_reference_pose(viso_direct* h, int32_t frame, const doub
     return VISO_DIRECT_OK;
 }
 
+// cluster launch: 16 CTAs per cluster is beyond the portable size of 8 and has to be allowed explicitly
+static cudaError_t launch_direct(viso_direct* h, int32_t n_frames, double* d_poses, viso_direct_level_stats* d_stats,
+                                 int level_hi, int level_lo, int linearize_only, double* d_lin)
+{
+    static bool allowed = false;
+    if (!allowed) {
+        cudaError_t e = cudaFuncSetAttribute(k_direct, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+        if (e != cudaSuccess) return e;
+        allowed = true;
+    }
+    const int csize = n_frames >= 2 * kClusterBatch ? kClusterBatch : kClusterMax;
+    cudaLaunchConfig_t lc = {};
+    lc.gridDim = dim3(csize * n_frames), lc.blockDim = dim3(kThreads), lc.dynamicSmemBytes = 0, lc.stream = h->stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = csize, at[0].val.clusterDim.y = 1, at[0].val.clusterDim.z = 1;
+    lc.attrs = at, lc.numAttrs = 1;
+    cudaError_t e = cudaLaunchKernelEx(&lc, k_direct, (const DevFrame*)h->d_frames.p, params_of(h->cfg), d_poses, d_stats,
+        level_hi, level_lo, linearize_only, d_lin);
+    if (e != cudaSuccess) return e;
+    ++h->launches;
+    return cudaGetLastError();
+}
+
 static int32_t run(viso_direct* h, int32_t level_hi, int32_t level_lo, int32_t n_frames, double* poses,
                    viso_direct_level_stats* stats, float* device_ms)
 {
@@ -556,10 +599,7 @@ static int32_t run(viso_direct* h, int32_t level_hi, int32_t level_lo, int32_t n
     DCU(cudaMemsetAsync(h->d_stats.p, 0, sizeof(viso_direct_level_stats) * kLevels * (size_t)n_frames, h->stream));
     DCU(cudaMemcpyAsync(h->d_poses.p, poses, sizeof(double) * 7 * (size_t)n_frames, cudaMemcpyHostToDevice, h->stream));
     DCU(cudaEventRecord(h->ev0, h->stream));
-    k_direct<<<kCluster * n_frames, kThreads, 0, h->stream>>>((const DevFrame*)h->d_frames.p, params_of(h->cfg), (double*)h->d_poses.p,
-        (viso_direct_level_stats*)h->d_stats.p, level_hi, level_lo, 0, nullptr);
-    DCU(cudaGetLastError());
-    ++h->launches;
+    DCU(launch_direct(h, n_frames, (double*)h->d_poses.p, (viso_direct_level_stats*)h->d_stats.p, level_hi, level_lo, 0, nullptr));
     DCU(cudaEventRecord(h->ev1, h->stream));
     DCU(cudaMemcpyAsync(poses, h->d_poses.p, sizeof(double) * 7 * (size_t)n_frames, cudaMemcpyDeviceToHost, h->stream));
     std::vector<viso_direct_level_stats> st;
@@ -601,10 +641,7 @@ int32_t viso_direct_linearize(viso_direct* h, int32_t level, int32_t n_frames, c
     if ((s = reserve(h, h->d_poses, sizeof(double) * 7 * (size_t)h->cfg.max_frames))) return s;
     if ((s = reserve(h, h->d_lin, sizeof(double) * 44 * (size_t)h->cfg.max_frames))) return s;
     DCU(cudaMemcpyAsync(h->d_poses.p, poses, sizeof(double) * 7 * (size_t)n_frames, cudaMemcpyHostToDevice, h->stream));
-    k_direct<<<kCluster * n_frames, kThreads, 0, h->stream>>>((const DevFrame*)h->d_frames.p, params_of(h->cfg), (double*)h->d_poses.p,
-        nullptr, level, level, 1, (double*)h->d_lin.p);
-    DCU(cudaGetLastError());
-    ++h->launches;
+    DCU(launch_direct(h, n_frames, (double*)h->d_poses.p, nullptr, level, level, 1, (double*)h->d_lin.p));
     std::vector<double> out(44 * (size_t)n_frames);
     DCU(cudaMemcpyAsync(out.data(), h->d_lin.p, sizeof(double) * out.size(), cudaMemcpyDeviceToHost, h->stream));
     DCU(cudaStreamSynchronize(h->stream));
