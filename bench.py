@@ -508,7 +508,7 @@ def others(vb, args, device):
 
 
 def direct_leg(device, cpu=True, n_points=2000, batch=128):
-    """the tracker's direct pose estimation, reference src/viso.cpp:661-774, on a
+    """the tracker's direct pose estimation, reference src/viso.cpp:661-766, on a
     synthetic 640x480 frame pair with 2000 map points.  Unit: Gauss-Newton iterations/s (one iteration =
     one pass over all points x 64 patch pixels + the 6x6 solve); kernel time by CUDA events inside the
     C ABI call.  `reference_loop` is the loop as the reference writes it (one step per level), `repaired`

@@ -2,8 +2,8 @@
  * viso_direct.h — C ABI of the B200-native direct (photometric) pose estimator of viso's tracker.
  *
  * the tracker's hot loop next to the bundle adjuster.  It replaces
- *   Viso::DirectPoseEstimationSingleLayer   reference src/viso.cpp:661-766
- *   Viso::DirectPoseEstimationMultiLayer    reference src/viso.cpp:768-774
+ *   Viso::DirectPoseEstimationSingleLayer   reference src/viso.cpp:661-758
+ *   Viso::DirectPoseEstimationMultiLayer    reference src/viso.cpp:760-766
  * and uses, with the reference's exact arithmetic,
  *   Keyframe::Project(point, level)         reference include/keyframe.h:82-89
  *   Keyframe::IsInside(u, v, level)         reference include/keyframe.h:76-79
@@ -57,7 +57,7 @@ typedef struct {
     int32_t max_iterations;  /* 100 (viso.cpp:671)                                               */
     double delta_thresh;     /* 0.005 (viso.cpp:668)                                             */
     int32_t reference_termination;
-                             /* 1 (default): the reference's loop exactly as written, viso.cpp:673-765 —
+                             /* 1 (default): the reference's loop exactly as written, viso.cpp:673-757 —
                                 `cost` is never reset between iterations and `lastCost` starts at 0, so
                                 (1 - cost/lastCost) is -inf after the first iteration and every level
                                 stops after ONE Gauss-Newton step.
@@ -66,12 +66,12 @@ typedef struct {
     int32_t reserved;
 } viso_direct_config;
 
-/* what one level did (viso.cpp:673-765), per frame */
+/* what one level did (viso.cpp:673-757), per frame */
 typedef struct {
     int32_t iterations;  /* Gauss-Newton updates applied to T21 on this level (before a restore) */
-    int32_t n_good;      /* nGood of the last evaluated iteration (viso.cpp:709)                 */
-    int32_t stop_reason; /* 0 = ran out of iterations, 1 = NaN update -> best restored (:744-747),
-                            2 = cost went up -> best restored (:749-752), 3 = converged (:754-756) */
+    int32_t n_good;      /* nGood of the last evaluated iteration (viso.cpp:717)                 */
+    int32_t stop_reason; /* 0 = ran out of iterations, 1 = NaN update -> best restored (:741-744),
+                            2 = cost went up -> best restored (:746-749), 3 = converged (:751-753) */
     int32_t reserved;
     double cost;         /* the value of `cost` when the loop ended                             */
     double last_cost;
@@ -96,7 +96,7 @@ int32_t viso_direct_set_image(viso_direct* h, int32_t frame, int32_t which, int3
  * of the handle when frame < 0, else the points of that frame's problem. */
 int32_t viso_direct_set_points(viso_direct* h, int32_t frame, const double* xyz, int32_t n);
 
-/* last_frame's pose (Keyframe::GetR/GetT), used by frame->Project(P1, level) at viso.cpp:690-692 */
+/* last_frame's pose (Keyframe::GetR/GetT), used by frame->Project(P1, level) at viso.cpp:693-695 */
 int32_t viso_direct_set_reference_pose(viso_direct* h, int32_t frame, const double pose[7]);
 
 /*
@@ -107,7 +107,7 @@ int32_t viso_direct_estimate_level(viso_direct* h, int32_t level, int32_t n_fram
                                    viso_direct_level_stats* stats);
 
 /*
- * Viso::DirectPoseEstimationMultiLayer: levels 3, 2, 1, 0 (viso.cpp:770-773).
+ * Viso::DirectPoseEstimationMultiLayer: levels 3, 2, 1, 0 (viso.cpp:763-765).
  * stats (optional): [n_frames][VISO_DIRECT_MAX_LEVELS], indexed by level.
  * device_ms (optional): CUDA-event time of the kernels.
  */
@@ -116,7 +116,7 @@ int32_t viso_direct_estimate(viso_direct* h, int32_t n_frames, double* poses,
 
 /*
  * The normal equations of ONE linearisation at the given poses (no update): H 6x6 row-major,
- * b 6, cost = sum of squared errors, n_good.  This is the loop body viso.cpp:689-733; exposed so
+ * b 6, cost = sum of squared errors, n_good.  This is the loop body viso.cpp:688-733; exposed so
  * that parity tests can compare the accumulation itself with the oracle.
  */
 int32_t viso_direct_linearize(viso_direct* h, int32_t level, int32_t n_frames, const double* poses,

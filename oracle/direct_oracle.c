@@ -79,8 +79,8 @@ void direct_dpixel_dxi(const direct_cfg* c, const double R[9], const double T[3]
     J[6] = 0, J[7] = fy / z, J[8] = -fy * y / zz, J[9] = -fy - fy * y * y / zz, J[10] = fy * xy / zz, J[11] = fy * x / z;
 }
 
-/* src/viso.cpp:689-733: the loop over the map points.  `cost` is ADDED to (the caller decides
- * whether it starts from zero); H, b and n_good start from zero (viso.cpp:675-680). */
+/* src/viso.cpp:688-733: the loop over the map points.  `cost` is ADDED to (the caller decides
+ * whether it starts from zero); H, b and n_good start from zero (viso.cpp:678-683). */
 static void accumulate(const direct_cfg* c, int32_t level, const direct_image* ref, const direct_image* cur,
                        const double ref_pose[7], const double T21[7], const double* points, int32_t n_points,
                        double H[36], double b[6], double* cost, int32_t* n_good)
@@ -89,21 +89,21 @@ static void accumulate(const direct_cfg* c, int32_t level, const direct_image* r
     const double scale = scales[level];
     const double hp = (double)c->half_patch_size;
     double R[9];
-    oracle_quat_to_R(T21, R); /* current_frame->SetR(T21.rotationMatrix()), viso.cpp:682-683 */
+    oracle_quat_to_R(T21, R); /* current_frame->SetR(T21.rotationMatrix()), viso.cpp:685-686 */
     memset(H, 0, 36 * sizeof(double));
     memset(b, 0, 6 * sizeof(double));
     *n_good = 0;
     for (int32_t i = 0; i < n_points; ++i) {
         const double* P1 = points + 3 * (size_t)i;
         double uv_ref[2], uv_cur[2];
-        direct_project(c, ref_pose, P1, scale, uv_ref); /* viso.cpp:690-692 */
-        direct_project(c, T21, P1, scale, uv_cur);      /* viso.cpp:694-696 */
+        direct_project(c, ref_pose, P1, scale, uv_ref); /* viso.cpp:693-695 */
+        direct_project(c, T21, P1, scale, uv_cur);      /* viso.cpp:697-699 */
         const int good = is_inside(ref, uv_ref[0] - hp, uv_ref[1] - hp) && is_inside(ref, uv_ref[0] + hp, uv_ref[1] + hp)
             && is_inside(cur, uv_cur[0] - hp, uv_cur[1] - hp) && is_inside(cur, uv_cur[0] + hp, uv_cur[1] + hp);
-        if (!good) continue; /* viso.cpp:701-711 (NaN projections fail every comparison) */
+        if (!good) continue; /* viso.cpp:704-715 (NaN projections fail every comparison) */
         ++*n_good;
         double Jx[12];
-        direct_dpixel_dxi(c, R, T21 + 4, P1, scale, Jx); /* viso.cpp:715-716 */
+        direct_dpixel_dxi(c, R, T21 + 4, P1, scale, Jx); /* viso.cpp:719-720 */
         for (int x = -c->half_patch_size; x < c->half_patch_size; ++x) {
             for (int y = -c->half_patch_size; y < c->half_patch_size; ++y) {
                 const double error = direct_pixel_value(ref, uv_ref[0] + x, uv_ref[1] + y)
@@ -111,11 +111,11 @@ static void accumulate(const direct_cfg* c, int32_t level, const direct_image* r
                 double g[2];
                 direct_gradient(cur, uv_cur[0] + x, uv_cur[1] + y, g);
                 double J[6];
-                for (int k = 0; k < 6; ++k) J[k] = -(g[0] * Jx[k] + g[1] * Jx[6 + k]); /* viso.cpp:722 */
+                for (int k = 0; k < 6; ++k) J[k] = -(g[0] * Jx[k] + g[1] * Jx[6 + k]); /* viso.cpp:726 */
                 for (int r = 0; r < 6; ++r)
-                    for (int q = 0; q < 6; ++q) H[6 * r + q] += J[r] * J[q]; /* viso.cpp:723 */
-                for (int k = 0; k < 6; ++k) b[k] += -error * J[k];            /* viso.cpp:724 */
-                *cost += error * error;                                       /* viso.cpp:725 */
+                    for (int q = 0; q < 6; ++q) H[6 * r + q] += J[r] * J[q]; /* viso.cpp:727 */
+                for (int k = 0; k < 6; ++k) b[k] += -error * J[k];            /* viso.cpp:728 */
+                *cost += error * error;                                       /* viso.cpp:729 */
             }
         }
     }
@@ -160,7 +160,7 @@ static void inverse_times(const double H[36], const double b[6], double x[6])
     }
 }
 
-/* src/viso.cpp:661-766 */
+/* src/viso.cpp:661-758 */
 void direct_single_layer(const direct_cfg* c, int32_t level, const direct_image* ref, const direct_image* cur,
                          const double ref_pose[7], double T21[7], const double* points, int32_t n_points,
                          direct_level_stats* stats)
@@ -207,7 +207,7 @@ void direct_single_layer(const direct_cfg* c, int32_t level, const direct_image*
     }
 }
 
-/* src/viso.cpp:768-774 */
+/* src/viso.cpp:760-766 */
 void direct_multi_layer(const direct_cfg* c, const direct_image* ref, const direct_image* cur,
                         const double ref_pose[7], double T21[7], const double* points, int32_t n_points,
                         direct_level_stats* stats)

@@ -3,8 +3,8 @@
  *
  * Only tests/, __graft_entry__.smoke() and bench.py's CPU legs may load this.  It follows the
  * reference statement by statement (file:line cited at every function in direct_oracle.c):
- *   src/viso.cpp:661-766   Viso::DirectPoseEstimationSingleLayer
- *   src/viso.cpp:768-774   Viso::DirectPoseEstimationMultiLayer
+ *   src/viso.cpp:661-758   Viso::DirectPoseEstimationSingleLayer
+ *   src/viso.cpp:760-766   Viso::DirectPoseEstimationMultiLayer
  *   src/viso.cpp:640-658   dPixeldXi
  *   include/keyframe.h:50-64, :76-89   GetPixelValue, GetGradient, IsInside, Project
  * Parity unpinned: the reference has no tests or fixtures for this function and cannot be built
@@ -47,17 +47,17 @@ void direct_project(const direct_cfg* c, const double pose[7], const double Pw[3
 void direct_dpixel_dxi(const direct_cfg* c, const double R[9], const double T[3], const double P[3],
                        double scale, double J[12]);
 
-/* loop body viso.cpp:689-733: H (6x6 row-major), b (6), sum of squared errors, nGood */
+/* loop body viso.cpp:688-733: H (6x6 row-major), b (6), sum of squared errors, nGood */
 void direct_linearize(const direct_cfg* c, int32_t level, const direct_image* ref, const direct_image* cur,
                       const double ref_pose[7], const double T21[7], const double* points, int32_t n_points,
                       double H[36], double b[6], double* cost, int32_t* n_good);
 
-/* viso.cpp:661-766 */
+/* viso.cpp:661-758 */
 void direct_single_layer(const direct_cfg* c, int32_t level, const direct_image* ref, const direct_image* cur,
                          const double ref_pose[7], double T21[7], const double* points, int32_t n_points,
                          direct_level_stats* stats);
 
-/* viso.cpp:768-774; ref / cur: arrays of 4 levels; stats (optional): [4] indexed by level */
+/* viso.cpp:760-766; ref / cur: arrays of 4 levels; stats (optional): [4] indexed by level */
 void direct_multi_layer(const direct_cfg* c, const direct_image* ref, const direct_image* cur,
                         const double ref_pose[7], double T21[7], const double* points, int32_t n_points,
                         direct_level_stats* stats);

@@ -1,5 +1,5 @@
 """Independent numpy statement of one linearisation of viso's direct pose estimation
-(reference src/viso.cpp:689-733), vectorised over points and patch pixels.  Written from the
+(reference src/viso.cpp:688-733), vectorised over points and patch pixels.  Written from the
 reference text, not from oracle/direct_oracle.c, so that a shared misreading shows up as a
 disagreement."""
 import numpy as np

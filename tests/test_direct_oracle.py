@@ -1,5 +1,5 @@
 """CPU tests of the direct-pose oracle (oracle/direct_oracle.c) — what pins it, given that the
-reference has no tests for src/viso.cpp:661-774: known answers of the bilinear sampler and the
+reference has no tests for src/viso.cpp:661-766: known answers of the bilinear sampler and the
 gradient, dPixeldXi entry by entry against the formula in the reference text and against finite
 differences of Project(exp(eps) T, P), an independent numpy statement of the normal equations,
 the reference's termination quirk, and recovery of a known camera motion."""
@@ -86,7 +86,7 @@ def test_points_outside_the_image_are_skipped(scene):
     _, _, _, ng50 = dorc.linearize(*args, pts[:50])
     _, _, _, ng52 = dorc.linearize(*args, pts[:52])
     _, _, _, ng53 = dorc.linearize(*args, pts)
-    assert ng52 == ng50  # viso.cpp:701-711: a patch that leaves either image is skipped
+    assert ng52 == ng50  # viso.cpp:704-715: a patch that leaves either image is skipped
     assert ng53 == ng50 + 1  # ... but a point BEHIND the camera projects to (cx, cy) and is kept: no depth test there
 
 

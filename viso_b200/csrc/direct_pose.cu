@@ -2,8 +2,8 @@
 // (SURVEY.md section 8 row f3).  C ABI: include/viso_direct.h.
 //
 // Reference semantics (citations relative to /root/reference):
-//   Viso::DirectPoseEstimationSingleLayer  src/viso.cpp:661-766   Gauss-Newton on one pyramid level
-//   Viso::DirectPoseEstimationMultiLayer   src/viso.cpp:768-774   levels 3, 2, 1, 0
+//   Viso::DirectPoseEstimationSingleLayer  src/viso.cpp:661-758   Gauss-Newton on one pyramid level
+//   Viso::DirectPoseEstimationMultiLayer   src/viso.cpp:760-766   levels 3, 2, 1, 0
 //   dPixeldXi                              src/viso.cpp:640-658   2x6, columns (v, w)
 //   Keyframe::GetPixelValue / GetGradient  include/keyframe.h:50-64
 //   Keyframe::IsInside / Project           include/keyframe.h:76-89
@@ -142,7 +142,7 @@ __device__ __noinline__ int gn_decide(GnState& st, const double* tot, const DevP
         for (int q = r; q < 6; ++q) H[6 * r + q] = H[6 * q + r] = tot[e++];
     for (int q = 0; q < 6; ++q) b[q] = tot[21 + q];
     st.nGood = (int)tot[kSums];
-    st.cost = (K.reference_termination ? st.cost : 0.0) + tot[27]; // never reset in the reference (viso.cpp:673, :725)
+    st.cost = (K.reference_termination ? st.cost : 0.0) + tot[27]; // never reset in the reference (viso.cpp:673, :729)
     inverse_times(H, b, update);                  // viso.cpp:735
     double next[7];
     visoba::pose_oplus(update, st.T21, next);     // viso.cpp:737
@@ -169,7 +169,7 @@ __device__ __noinline__ int gn_decide(GnState& st, const double* tot, const DevP
 }
 
 // ------------------------------------------------------------------------------------------
-// One cluster per frame: Gauss-Newton over the levels level_hi .. level_lo (viso.cpp:661-774),
+// One cluster per frame: Gauss-Newton over the levels level_hi .. level_lo (viso.cpp:661-766),
 // or (linearize_only) the sums of one linearisation at the given pose.
 // ------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kThreads, 1)
@@ -211,7 +211,7 @@ k_direct(const DevFrame* __restrict__ frames, const DevParams K, double* __restr
         }
 
         for (int iter = 0; iter < K.max_iterations; ++iter) {
-            { // the pose published by rank 0 (current_frame->SetR / SetT, viso.cpp:682-683)
+            { // the pose published by rank 0 (current_frame->SetR / SetT, viso.cpp:685-686)
                 const double* rp = cluster.map_shared_rank(s_gn.T21, 0);
                 if (tid == 0) {
                     double p[7];
@@ -225,22 +225,22 @@ k_direct(const DevFrame* __restrict__ frames, const DevParams K, double* __restr
 #pragma unroll
             for (int k = 0; k < kSums; ++k) acc[k] = 0.0;
             int good_cnt = 0;
-            for (int i = gw; i < F.n_points; i += nw) { // viso.cpp:685
+            for (int i = gw; i < F.n_points; i += nw) { // viso.cpp:688
                 const double X = __ldg(F.points + 3 * (size_t)i), Y = __ldg(F.points + 3 * (size_t)i + 1);
                 const double Z = __ldg(F.points + 3 * (size_t)i + 2);
                 double u_ref, v_ref, u_cur, v_cur, x, y, z, xr, yr, zr;
-                project(K, s_ref_rt, X, Y, Z, scale, u_ref, v_ref, xr, yr, zr); // viso.cpp:690-692
-                project(K, s_rt, X, Y, Z, scale, u_cur, v_cur, x, y, z);         // viso.cpp:694-696
+                project(K, s_ref_rt, X, Y, Z, scale, u_ref, v_ref, xr, yr, zr); // viso.cpp:693-695
+                project(K, s_rt, X, Y, Z, scale, u_cur, v_cur, x, y, z);         // viso.cpp:697-699
                 const bool good = is_inside(ref, u_ref - hp, v_ref - hp) && is_inside(ref, u_ref + hp, v_ref + hp)
                     && is_inside(cur, u_cur - hp, v_cur - hp) && is_inside(cur, u_cur + hp, v_cur + hp);
-                if (!good) continue; // viso.cpp:701-711, uniform over the warp
+                if (!good) continue; // viso.cpp:704-715, uniform over the warp
                 ++good_cnt;
                 // dPixeldXi (viso.cpp:640-658)
                 const double fx = K.fx * scale, fy = K.fy * scale, zz = z * z, xy = x * y;
                 double J0[6], J1[6];
                 J0[0] = fx / z, J0[1] = 0, J0[2] = -fx * x / zz, J0[3] = -fx * xy / zz, J0[4] = fx + fx * x * x / zz, J0[5] = -fx * y / z;
                 J1[0] = 0, J1[1] = fy / z, J1[2] = -fy * y / zz, J1[3] = -fy - fy * y * y / zz, J1[4] = fy * xy / zz, J1[5] = fy * x / z;
-                for (int k = lane; k < npix; k += 32) { // viso.cpp:718-719: x outer, y inner
+                for (int k = lane; k < npix; k += 32) { // viso.cpp:722-723: x outer, y inner
                     const double px = (double)(k / side - K.hp), py = (double)(k % side - K.hp);
                     const double uc = u_cur + px, vc = v_cur + py;
                     const double error = pixel_value(ref, u_ref + px, v_ref + py) - pixel_value(cur, uc, vc);
@@ -249,15 +249,15 @@ k_direct(const DevFrame* __restrict__ frames, const DevParams K, double* __restr
                     const double g1 = 0.5 * (pixel_value(cur, uc, vc + 1) - pixel_value(cur, uc, vc - 1));
                     double J[6];
 #pragma unroll
-                    for (int q = 0; q < 6; ++q) J[q] = -(g0 * J0[q] + g1 * J1[q]); // viso.cpp:722
+                    for (int q = 0; q < 6; ++q) J[q] = -(g0 * J0[q] + g1 * J1[q]); // viso.cpp:726
                     int e = 0;
 #pragma unroll
                     for (int r = 0; r < 6; ++r)
 #pragma unroll
-                        for (int q = r; q < 6; ++q) acc[e++] += J[r] * J[q];   // viso.cpp:723 (upper triangle)
+                        for (int q = r; q < 6; ++q) acc[e++] += J[r] * J[q];   // viso.cpp:727 (upper triangle)
 #pragma unroll
-                    for (int q = 0; q < 6; ++q) acc[21 + q] += -error * J[q];  // viso.cpp:724
-                    acc[27] += error * error;                                  // viso.cpp:725
+                    for (int q = 0; q < 6; ++q) acc[21 + q] += -error * J[q];  // viso.cpp:728
+                    acc[27] += error * error;                                  // viso.cpp:729
                 }
             }
 

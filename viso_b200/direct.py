@@ -1,6 +1,6 @@
 """Python mirror of the direct pose estimator's C ABI (include/viso_direct.h) — SURVEY.md 8 row f3.
 
-Mirrors Viso::DirectPoseEstimationSingleLayer / MultiLayer (reference src/viso.cpp:661-774): same
+Mirrors Viso::DirectPoseEstimationSingleLayer / MultiLayer (reference src/viso.cpp:661-766): same
 argument meaning (level, current frame's pyramid, T21 in/out), last_frame and the map points set on
 the handle the way Viso holds them as members.  ctypes over libviso_ba.so; no CPU fallback.
 """
@@ -122,14 +122,14 @@ class DirectPoseEstimator:
         self._check(_load().viso_direct_set_reference_pose(self._h, frame, pose.ctypes.data_as(_D)))
 
     def DirectPoseEstimationSingleLayer(self, level, T21):
-        """reference src/viso.cpp:661-766.  T21: [7] or [frames][7]; returns (refined, [LevelStats per frame])."""
+        """reference src/viso.cpp:661-758.  T21: [7] or [frames][7]; returns (refined, [LevelStats per frame])."""
         poses = np.array(T21, dtype=np.float64).reshape(-1, 7).copy()
         st = (LevelStats * len(poses))()
         self._check(_load().viso_direct_estimate_level(self._h, level, len(poses), poses.ctypes.data_as(_D), st))
         return poses.reshape(np.shape(T21)), list(st)
 
     def DirectPoseEstimationMultiLayer(self, T21):
-        """reference src/viso.cpp:768-774.  Returns (refined, stats[frame][level], device_ms)."""
+        """reference src/viso.cpp:760-766.  Returns (refined, stats[frame][level], device_ms)."""
         poses = np.array(T21, dtype=np.float64).reshape(-1, 7).copy()
         st = (LevelStats * (LEVELS * len(poses)))()
         ms = C.c_float(0)
@@ -138,7 +138,7 @@ class DirectPoseEstimator:
         return poses.reshape(np.shape(T21)), stats, float(ms.value)
 
     def linearize(self, level, T21):
-        """H [frames][6][6], b [frames][6], cost [frames], n_good [frames] of one linearisation (viso.cpp:689-733)."""
+        """H [frames][6][6], b [frames][6], cost [frames], n_good [frames] of one linearisation (viso.cpp:688-733)."""
         poses = np.array(T21, dtype=np.float64).reshape(-1, 7).copy()
         n = len(poses)
         H, b, cost = np.zeros((n, 6, 6)), np.zeros((n, 6)), np.zeros(n)
