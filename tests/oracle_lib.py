@@ -30,7 +30,7 @@ _lib = None
 
 
 def build_oracle(force=False):
-    src = [os.path.join(ORACLE_DIR, f) for f in ("ba_oracle.c", "ba_oracle.h", "Makefile")]
+    src = [os.path.join(ORACLE_DIR, f) for f in os.listdir(ORACLE_DIR) if f.endswith((".c", ".h")) or f == "Makefile"]
     if (not force and os.path.exists(ORACLE_LIB)
             and all(os.path.getmtime(ORACLE_LIB) >= os.path.getmtime(s) for s in src)):
         return ORACLE_LIB

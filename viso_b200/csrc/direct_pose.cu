@@ -19,6 +19,7 @@
 // batched frames are independent clusters of the same launch.  Images are read through the
 // read-only path (__ldg): level 0 of a 640x480 frame is 300 kB and stays in L1/L2.
 #include "ba_math.cuh"
+#include "image_math.cuh"
 #include "../../include/viso_direct.h"
 
 #include <cooperative_groups.h>
@@ -36,17 +37,16 @@ namespace cg = cooperative_groups;
 
 namespace visodirect {
 
+using visoimg::DevImage;
+using visoimg::is_inside;
+using visoimg::pixel_value;
+
 constexpr int kClusterMax = 16;  // CTAs per frame when few frames run: the largest (non-portable) cluster a B200 schedules
 constexpr int kClusterBatch = 8; // ... and when many frames run: the portable size packs the GPCs better
 constexpr int kThreads = 512;  // threads per CTA
 constexpr int kWarps = kThreads / 32;
 constexpr int kSums = 28;      // 21 (upper triangle of H) + 6 (b) + 1 (cost)
 constexpr int kLevels = VISO_DIRECT_MAX_LEVELS;
-
-struct DevImage {
-    const uint8_t* data;
-    int32_t cols, rows, step, pad;
-};
 
 struct DevFrame {
     DevImage ref[kLevels], cur[kLevels];
@@ -61,26 +61,6 @@ struct DevParams {
 };
 
 // ---- device arithmetic, statement by statement as the reference writes it ----
-
-// keyframe.h:50-57.  Reads that leave the cv::Mat buffer in the reference are clamped into it.
-__device__ __forceinline__ double pixel_value(const DevImage& im, double x, double y)
-{
-    const long long base = (long long)(int)y * im.step + (long long)(int)x;
-    const long long last = (long long)im.rows * im.step - 1;
-    const double xx = x - floor(x);
-    const double yy = y - floor(y);
-    const long long i0 = min(max(base, 0LL), last), i1 = min(max(base + 1, 0LL), last);
-    const long long i2 = min(max(base + im.step, 0LL), last), i3 = min(max(base + im.step + 1, 0LL), last);
-    const double d0 = (double)__ldg(im.data + i0), d1 = (double)__ldg(im.data + i1);
-    const double d2 = (double)__ldg(im.data + i2), d3 = (double)__ldg(im.data + i3);
-    return (1 - xx) * (1 - yy) * d0 + xx * (1 - yy) * d1 + (1 - xx) * yy * d2 + xx * yy * d3;
-}
-
-// keyframe.h:76-79
-__device__ __forceinline__ bool is_inside(const DevImage& im, double u, double v)
-{
-    return u >= 0 && u < im.cols && v >= 0 && v < im.rows;
-}
 
 // keyframe.h:82-89 with R|t already expanded (rt[0..8] = R row-major, rt[9..11] = t)
 __device__ __forceinline__ void project(const DevParams& K, const double* rt, double X, double Y, double Z,
