@@ -291,10 +291,16 @@ def roofline(ktimes, trials_per_problem, sizes, nprob=1):
     # same shape): scaled to this run's window count, per launch like `achieved`
     traffic = None
     try:
-        with open(os.path.join(ROOT, "profiles", "traffic_296win.json")) as fh:
+        exact = os.path.join(ROOT, "profiles", "traffic_%dwin.json" % nprob)
+        base = 296.0
+        if os.path.exists(exact):  # a capture of exactly this launch
+            base = float(nprob)
+        else:
+            exact = os.path.join(ROOT, "profiles", "traffic_296win.json")
+        with open(exact) as fh:
             tr = json.load(fh)
         if all(k in tr for k in members) and nprob > 1:
-            traffic = sum(tr[k] for k in members) * nprob / 296.0
+            traffic = sum(tr[k] for k in members) * nprob / base
     except Exception:
         pass
     fp64 = None
@@ -504,7 +510,52 @@ def others(vb, args, device):
         out["direct_pose"] = direct_leg(device, cpu=not args.no_cpu)
     except Exception as e:
         out["direct_pose"] = {"error": str(e)}
+    try:
+        out["lk_align"] = lk_leg(device, cpu=not args.no_cpu)
+    except Exception as e:
+        out["lk_align"] = {"error": str(e)}
     return out
+
+
+def lk_leg(device, cpu=True, n_points=4000):
+    """Lucas-Kanade patch alignment, reference src/viso.cpp:845-925 (LKAlignmentSingle over
+    4 levels) and :259-391 (optical flow), on a synthetic 640x480 frame pair.  Unit: keypoints/s through all four
+    pyramid levels; kernel time by CUDA events inside the C ABI call; `e2e` adds the H2D/D2H of the keypoints."""
+    from viso_b200 import lk
+    from viso_b200.direct_synth import synth_scene, FX, FY, CX, CY
+    sc = synth_scene(seed=12, n_points=n_points)
+    P = sc["points"]
+    uv_ref = np.stack([FX * P[:, 0] / P[:, 2] + CX, FY * P[:, 1] / P[:, 2] + CY], axis=1)
+    a = lk.LKAligner(max_keypoints=n_points, slots=2, device=device)
+    a.set_pyramid(0, sc["ref_pyr"])
+    a.set_pyramid(1, sc["cur_pyr"])
+    res = {"keypoints": n_points, "patch_pixels": 64, "image": "640x480, 4 levels", "unit": "keypoints/s"}
+
+    def timed(fn, reps=20):
+        ms, wall = [], []
+        for i in range(reps + 3):
+            t0 = time.perf_counter()
+            out = fn()
+            dt = time.perf_counter() - t0
+            if i >= 3:
+                ms.append(out[2])
+                wall.append(dt)
+        m, w = float(np.median(ms)), float(np.median(wall))
+        return {"kernel_ms": m, "value": n_points / (m * 1e-3), "e2e_ms": 1e3 * w, "e2e_value": n_points / w,
+                "success_rate": float(np.mean(out[1]))}
+    res["lk_alignment"] = timed(lambda: a.LKAlignment(0, 1, uv_ref, uv_ref))
+    kp1 = uv_ref.astype(np.float32)
+    res["optical_flow_forward"] = timed(lambda: a.OpticalFlowMultiLevel(0, 1, kp1, None, inverse=False))
+    res["optical_flow_inverse"] = timed(lambda: a.OpticalFlowMultiLevel(0, 1, kp1, None, inverse=True))
+    a.close()
+    if cpu:
+        import lk_oracle_lib as lko
+        t0 = time.perf_counter()
+        lko.align(lko.cfg(), [sc["ref_pyr"]], 0, sc["cur_pyr"], uv_ref, uv_ref)
+        dt = time.perf_counter() - t0
+        res["cpu_baseline"] = {"value": n_points / dt, "unit": "keypoints/s", "cores": 1, "kind": "port",
+                               "sample": "LKAlignment of %d pairs, oracle/lk_oracle.c single-threaded like the reference" % n_points}
+    return res
 
 
 def direct_leg(device, cpu=True, n_points=2000, batch=128):
