@@ -92,6 +92,13 @@ int64_t viso_direct_kernel_launches(const viso_direct* h);
 int32_t viso_direct_set_image(viso_direct* h, int32_t frame, int32_t which, int32_t level,
                               const uint8_t* data, int32_t cols, int32_t rows, int32_t step);
 
+/*
+ * Keyframe's constructor (keyframe.h:29-45): `data` becomes level 0 and levels 1..3 are built on the device
+ * with cv::pyrDown's arithmetic (bit-exact against OpenCV; see viso_lk_set_frame).
+ */
+int32_t viso_direct_set_frame(viso_direct* h, int32_t frame, int32_t which, const uint8_t* data,
+                              int32_t cols, int32_t rows, int32_t step);
+
 /* Map points in world coordinates (MapPoint::GetWorldPos, map_point.h:21-31), shared by all frames
  * of the handle when frame < 0, else the points of that frame's problem. */
 int32_t viso_direct_set_points(viso_direct* h, int32_t frame, const double* xyz, int32_t n);

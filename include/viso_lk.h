@@ -60,6 +60,17 @@ int32_t viso_lk_set_image(viso_lk* h, int32_t slot, int32_t level, const uint8_t
                           int32_t cols, int32_t rows, int32_t step);
 
 /*
+ * Keyframe's constructor (keyframe.h:29-45): `data` becomes level 0 of `slot` and levels 1..3 are built on
+ * the device with cv::pyrDown's arithmetic (5-tap [1 4 6 4 1], BORDER_REFLECT_101, (sum + 128) >> 8,
+ * Size(cols * 0.5, rows * 0.5)), bit-exact against OpenCV.
+ */
+int32_t viso_lk_set_frame(viso_lk* h, int32_t slot, const uint8_t* data, int32_t cols, int32_t rows, int32_t step);
+
+/* Keyframe::Pyramids()[level] of `slot` back on the host, rows packed (stride = cols); capacity in bytes. */
+int32_t viso_lk_get_image(viso_lk* h, int32_t slot, int32_t level, uint8_t* out, int64_t capacity,
+                          int32_t* cols, int32_t* rows);
+
+/*
  * The level loop of Viso::LKAlignment (viso.cpp:828-830) over LKAlignmentSingle (viso.cpp:845-925).
  * Pair i = AlignmentPair{ref_frame = slot ref_slot[i], cur_frame = slot cur_slot, uv_ref, uv_cur}
  * (include/viso.h:116-121).  uv_ref [n][2] level-0 pixels; uv_cur [n][2] in = projection of the map

@@ -14,7 +14,7 @@ ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libviso_ba.so")
 STAMP = os.path.join(HERE, ".libviso_ba.stamp")
-SOURCES = ["ba_kernels.cu", "ba_window.cu", "ba_dense.cu", "ba_setup.cu", "direct_pose.cu", "lk_align.cu", "viso_ba.cpp", "synth.cpp"]
+SOURCES = ["ba_kernels.cu", "ba_window.cu", "ba_dense.cu", "ba_setup.cu", "direct_pose.cu", "lk_align.cu", "pyramid.cu", "viso_ba.cpp", "synth.cpp"]
 HEADERS = [os.path.join(CSRC, "ba_device.h"), os.path.join(CSRC, "ba_math.cuh"), os.path.join(CSRC, "ba_setup.h"), os.path.join(CSRC, "image_math.cuh"), os.path.join(ROOT, "include", "viso_ba.h"), os.path.join(ROOT, "include", "viso_direct.h"), os.path.join(ROOT, "include", "viso_lk.h")]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",

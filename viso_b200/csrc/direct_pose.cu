@@ -515,6 +515,26 @@ int32_t viso_direct_set_image(viso_direct* h, int32_t frame, int32_t which, int3
     return VISO_DIRECT_OK;
 }
 
+int32_t viso_direct_set_frame(viso_direct* h, int32_t frame, int32_t which, const uint8_t* data, int32_t cols, int32_t rows, int32_t step)
+{
+    int32_t s = viso_direct_set_image(h, frame, which, 0, data, cols, rows, step);
+    if (s) return s;
+    for (int l = 1; l < kLevels; ++l) { // keyframe.h:40-45
+        DevImage* pyr = which == 0 ? h->frames[frame].ref : h->frames[frame].cur;
+        const DevImage prev = pyr[l - 1];
+        const int dcols = (int)(prev.cols * 0.5), drows = (int)(prev.rows * 0.5);
+        if (dcols < 1 || drows < 1) return fail(h, VISO_DIRECT_ERR_ARG, "set_frame: %dx%d is too small for %d pyramid levels", cols, rows, kLevels);
+        DevBuf& b = h->images[((size_t)frame * 2 + which) * kLevels + l];
+        if ((s = reserve(h, b, (size_t)drows * dcols))) return s;
+        h->launches += visoimg::launch_pyr_down(prev.data, prev.cols, prev.rows, prev.step, (uint8_t*)b.p, dcols, drows, dcols, h->stream);
+        DCU(cudaGetLastError());
+        pyr[l].data = (const uint8_t*)b.p, pyr[l].cols = dcols, pyr[l].rows = drows, pyr[l].step = dcols, pyr[l].pad = 0;
+    }
+    h->frames_dirty = true;
+    DCU(cudaStreamSynchronize(h->stream));
+    return VISO_DIRECT_OK;
+}
+
 int32_t viso_direct_set_points(viso_direct* h, int32_t frame, const double* xyz, int32_t n)
 {
     int32_t s = need_device(h);

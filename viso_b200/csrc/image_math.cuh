@@ -43,5 +43,8 @@ __device__ __forceinline__ bool is_inside(const DevImage& im, double u, double v
     return u >= 0 && u < im.cols && v >= 0 && v < im.rows;
 }
 
+// pyramid.cu: one cv::pyrDown step (CV_8UC1, Size(cols * 0.5, rows * 0.5)) on the device; returns the launches made
+int launch_pyr_down(const uint8_t* src, int cols, int rows, int step, uint8_t* dst, int dcols, int drows, int dstep, cudaStream_t st);
+
 } // namespace visoimg
 #endif

@@ -474,6 +474,40 @@ int32_t viso_lk_set_image(viso_lk* h, int32_t slot, int32_t level, const uint8_t
     return VISO_LK_OK;
 }
 
+int32_t viso_lk_set_frame(viso_lk* h, int32_t slot, const uint8_t* data, int32_t cols, int32_t rows, int32_t step)
+{
+    int32_t s = viso_lk_set_image(h, slot, 0, data, cols, rows, step);
+    if (s) return s;
+    for (int l = 1; l < kLevels; ++l) { // keyframe.h:40-45
+        const DevImage prev = h->slots[(size_t)slot * kLevels + l - 1];
+        const int dcols = (int)(prev.cols * 0.5), drows = (int)(prev.rows * 0.5);
+        if (dcols < 1 || drows < 1) return lk_fail(h, VISO_LK_ERR_ARG, "set_frame: %dx%d is too small for %d pyramid levels", cols, rows, kLevels);
+        LkBuf& b = h->images[(size_t)slot * kLevels + l];
+        if ((s = lk_reserve(h, b, (size_t)drows * dcols))) return s;
+        h->launches += visoimg::launch_pyr_down(prev.data, prev.cols, prev.rows, prev.step, (uint8_t*)b.p, dcols, drows, dcols, h->stream);
+        LCU(cudaGetLastError());
+        DevImage& im = h->slots[(size_t)slot * kLevels + l];
+        im.data = (const uint8_t*)b.p, im.cols = dcols, im.rows = drows, im.step = dcols, im.pad = 0;
+    }
+    h->slots_dirty = true;
+    LCU(cudaStreamSynchronize(h->stream));
+    return VISO_LK_OK;
+}
+
+int32_t viso_lk_get_image(viso_lk* h, int32_t slot, int32_t level, uint8_t* out, int64_t capacity, int32_t* cols, int32_t* rows)
+{
+    int32_t s = lk_need_device(h);
+    if (s) return s;
+    if (!out || !cols || !rows || level < 0 || level >= kLevels) return lk_fail(h, VISO_LK_ERR_ARG, "get_image: bad argument");
+    if ((s = lk_check_slot(h, slot, level, level))) return s;
+    const DevImage& im = h->slots[(size_t)slot * kLevels + level];
+    if (capacity < (int64_t)im.cols * im.rows) return lk_fail(h, VISO_LK_ERR_CAPACITY, "get_image: %dx%d does not fit %lld bytes", im.cols, im.rows, (long long)capacity);
+    LCU(cudaMemcpy2DAsync(out, im.cols, im.data, im.step, im.cols, im.rows, cudaMemcpyDeviceToHost, h->stream));
+    LCU(cudaStreamSynchronize(h->stream));
+    *cols = im.cols, *rows = im.rows;
+    return VISO_LK_OK;
+}
+
 int32_t viso_lk_align(viso_lk* h, int32_t n, const int32_t* ref_slot, int32_t cur_slot, const double* uv_ref, double* uv_cur,
                       uint8_t* success, float* device_ms)
 {

@@ -37,6 +37,7 @@ DIRECT_SYMBOLS = {
     "viso_direct_last_error": (C.c_char_p, [_P]),
     "viso_direct_kernel_launches": (C.c_int64, [_P]),
     "viso_direct_set_image": (C.c_int32, [_P, C.c_int32, C.c_int32, C.c_int32, _U8, C.c_int32, C.c_int32, C.c_int32]),
+    "viso_direct_set_frame": (C.c_int32, [_P, C.c_int32, C.c_int32, _U8, C.c_int32, C.c_int32, C.c_int32]),
     "viso_direct_set_points": (C.c_int32, [_P, C.c_int32, _D, C.c_int32]),
     "viso_direct_set_reference_pose": (C.c_int32, [_P, C.c_int32, _D]),
     "viso_direct_estimate_level": (C.c_int32, [_P, C.c_int32, C.c_int32, _D, C.POINTER(LevelStats)]),
@@ -112,6 +113,11 @@ class DirectPoseEstimator:
             im = np.ascontiguousarray(im, dtype=np.uint8)
             self._check(_load().viso_direct_set_image(self._h, frame, which, level, im.ctypes.data_as(_U8),
                                                       im.shape[1], im.shape[0], im.strides[0]))
+
+    def set_frame(self, which, image, frame=0):
+        """Keyframe(cv::Mat) (keyframe.h:29-45): level 0 = image, levels 1..3 by pyrDown on the device"""
+        im = np.ascontiguousarray(image, dtype=np.uint8)
+        self._check(_load().viso_direct_set_frame(self._h, frame, which, im.ctypes.data_as(_U8), im.shape[1], im.shape[0], im.strides[0]))
 
     def set_points(self, xyz, frame=-1):
         xyz = np.ascontiguousarray(xyz, dtype=np.float64).reshape(-1, 3)

@@ -32,6 +32,8 @@ LK_SYMBOLS = {
     "viso_lk_last_error": (C.c_char_p, [_P]),
     "viso_lk_kernel_launches": (C.c_int64, [_P]),
     "viso_lk_set_image": (C.c_int32, [_P, C.c_int32, C.c_int32, _U8, C.c_int32, C.c_int32, C.c_int32]),
+    "viso_lk_set_frame": (C.c_int32, [_P, C.c_int32, _U8, C.c_int32, C.c_int32, C.c_int32]),
+    "viso_lk_get_image": (C.c_int32, [_P, C.c_int32, C.c_int32, _U8, C.c_int64, _I32, _I32]),
     "viso_lk_align": (C.c_int32, [_P, C.c_int32, _I32, C.c_int32, _D, _D, _U8, _F]),
     "viso_lk_align_level": (C.c_int32, [_P, C.c_int32, C.c_int32, _I32, C.c_int32, _D, _D, _U8]),
     "viso_lk_optical_flow": (C.c_int32, [_P, C.c_int32, C.c_int32, C.c_int32, _F, _F, C.c_int32, C.c_int32, _U8, _F]),
@@ -102,6 +104,18 @@ class LKAligner:
         for level, im in enumerate(pyramid):
             im = np.ascontiguousarray(im, dtype=np.uint8)
             self._check(_load().viso_lk_set_image(self._h, slot, level, im.ctypes.data_as(_U8), im.shape[1], im.shape[0], im.strides[0]))
+
+    def set_frame(self, slot, image):
+        """Keyframe(cv::Mat) (keyframe.h:29-45): level 0 = image, levels 1..3 by pyrDown on the device"""
+        im = np.ascontiguousarray(image, dtype=np.uint8)
+        self._check(_load().viso_lk_set_frame(self._h, slot, im.ctypes.data_as(_U8), im.shape[1], im.shape[0], im.strides[0]))
+
+    def get_image(self, slot, level):
+        """Keyframe::Pyramids()[level] of the slot, read back from the device"""
+        out = np.zeros(self.cfg.max_width * self.cfg.max_height, dtype=np.uint8)
+        cols, rows = C.c_int32(0), C.c_int32(0)
+        self._check(_load().viso_lk_get_image(self._h, slot, level, out.ctypes.data_as(_U8), out.size, C.byref(cols), C.byref(rows)))
+        return out[:cols.value * rows.value].reshape(rows.value, cols.value).copy()
 
     def _pairs(self, ref_slot, uv_ref, uv_cur):
         uv_ref = np.ascontiguousarray(uv_ref, dtype=np.float64).reshape(-1, 2)
