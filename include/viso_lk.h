@@ -97,6 +97,21 @@ int32_t viso_lk_optical_flow_level(viso_lk* h, int32_t level, int32_t slot1, int
                                    const float* kp1, float* kp2, int32_t have_initial, int32_t inverse,
                                    uint8_t* success);
 
+/*
+ * EdgeDirectProjection::computeError (reference include/bundle_adjuster.h:70-101), the reference adjuster's
+ * only edge, for n edges at once: the 16-D photometric residual over the 4x4
+ * patch (i, j in [-2, 1]) between srcFrame (slot src_slot[e], projected with that keyframe's own pose
+ * frame_poses[src_slot[e]], :79) and targetFrame (slot tgt_slot[e], projected with the pose VERTEX
+ * vertex_poses[tgt_slot[e]] through K, :74-78), pixel coordinates cast to float as at :86-89.
+ * errors [n][16] in the reference's idx order (j outer, i inner, :83-99); level[e] = 1 when a sample
+ * fell outside an image — the edge disables itself with setLevel(1) and stops (:91-95); its remaining
+ * entries are then left at 0 here (the reference leaves stale values).  Poses [max_slots][7].
+ */
+int32_t viso_lk_edge_direct_projection(viso_lk* h, int32_t n, const double* points, const int32_t* src_slot,
+                                       const int32_t* tgt_slot, const double* frame_poses,
+                                       const double* vertex_poses, double fx, double fy, double cx, double cy,
+                                       double* errors, uint8_t* level, float* device_ms);
+
 #ifdef __cplusplus
 }
 #endif

@@ -4,6 +4,7 @@
  * holds cv::Point2f.  Citations are relative to /root/reference.
  */
 #include "lk_oracle.h"
+#include "ba_oracle.h" /* oracle_quat_to_R */
 
 #include <math.h>
 #include <stdlib.h>
@@ -151,4 +152,47 @@ void lk_flow_multi(const lk_cfg* c, const direct_image* pyr1, const direct_image
             for (int32_t j = 0; j < 2 * n; ++j) kp2[j] = (float)(kp2[j] / pyramid_scale); /* viso.cpp:384-389 */
     }
     free(kp1_);
+}
+
+/* include/bundle_adjuster.h:70-101  EdgeDirectProjection::computeError */
+void photo_edge_errors(const direct_image* images, int32_t n, const double* points, const int32_t* src_slot,
+                       const int32_t* tgt_slot, const double* frame_poses, const double* vertex_poses,
+                       const double K[4], double* errors, uint8_t* level)
+{
+    const double fx = K[0], fy = K[1], cx = K[2], cy = K[3];
+    for (int32_t e = 0; e < n; ++e) {
+        const direct_image* src = images + 4 * (size_t)src_slot[e];
+        const direct_image* tgt = images + 4 * (size_t)tgt_slot[e];
+        const double* p = points + 3 * (size_t)e;
+        const double* T = vertex_poses + 7 * (size_t)tgt_slot[e]; /* vertex(1), :73 */
+        double R[9];
+        oracle_quat_to_R(T, R); /* :74-75 */
+        const double x = R[0] * p[0] + R[1] * p[1] + R[2] * p[2] + T[4];
+        const double y = R[3] * p[0] + R[4] * p[1] + R[5] * p[2] + T[5];
+        const double z = R[6] * p[0] + R[7] * p[1] + R[8] * p[2] + T[6];
+        /* target_uv1 = K * (R p + t); target_uv1 /= z  (:77-78): K is the full 3x3 [fx 0 cx; 0 fy cy; 0 0 1] */
+        const double tu = (fx * x + 0.0 * y + cx * z) / z, tv = (0.0 * x + fy * y + cy * z) / z;
+        double suv[2];
+        direct_cfg c;
+        direct_default_cfg(&c);
+        c.fx = fx, c.fy = fy, c.cx = cx, c.cy = cy;
+        direct_project(&c, frame_poses + 7 * (size_t)src_slot[e], p, 1.0, suv); /* srcFrame->Project(p), :79 */
+        double* err = errors + 16 * (size_t)e;
+        for (int k = 0; k < 16; ++k) err[k] = 0.0;
+        level[e] = 0;
+        int idx = 0, abort_ = 0;
+        for (int j = -2; (j <= 1) && !abort_; ++j) {
+            for (int i = -2; i <= 1; ++i) {
+                const float u1 = (float)(tu + (double)i), v1 = (float)(tv + (double)j);         /* :86-87 */
+                const float u2 = (float)(suv[0] + (double)i), v2 = (float)(suv[1] + (double)j); /* :88-89 */
+                if (!is_inside(tgt, u1, v1) || !is_inside(src, u2, v2)) { /* :91-95 */
+                    level[e] = 1;
+                    abort_ = 1;
+                    break;
+                }
+                err[idx] = direct_pixel_value(src, u2, v2) - direct_pixel_value(tgt, u1, v1); /* :97 */
+                ++idx;
+            }
+        }
+    }
 }

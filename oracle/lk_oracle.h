@@ -41,4 +41,10 @@ void lk_flow_single(const lk_cfg* c, const direct_image* img1, const direct_imag
 void lk_flow_multi(const lk_cfg* c, const direct_image* pyr1, const direct_image* pyr2, int32_t n,
                    const float* kp1, float* kp2, int32_t have_initial, int32_t inverse, uint8_t* success);
 
+/* include/bundle_adjuster.h:70-101  EdgeDirectProjection::computeError for n edges.
+ * images: [n_slots][4] pyramids (level 0 is used); poses [n_slots][7]; K = (fx, fy, cx, cy). */
+void photo_edge_errors(const direct_image* images, int32_t n, const double* points, const int32_t* src_slot,
+                       const int32_t* tgt_slot, const double* frame_poses, const double* vertex_poses,
+                       const double K[4], double* errors, uint8_t* level);
+
 #endif

@@ -32,6 +32,7 @@ def lib():
         L.lk_align.argtypes = [C.POINTER(Cfg), _IM, _I32, _IM, C.c_int32, _D, _D, _U8]
         L.lk_flow_single.argtypes = [C.POINTER(Cfg), _IM, _IM, C.c_int32, _F, _F, C.c_int32, C.c_int32, _U8]
         L.lk_flow_multi.argtypes = [C.POINTER(Cfg), _IM, _IM, C.c_int32, _F, _F, C.c_int32, C.c_int32, _U8]
+        L.photo_edge_errors.argtypes = [_IM, C.c_int32, _D, _I32, _I32, _D, _D, _D, _D, _U8]
         _lib = L
     return _lib
 
@@ -78,3 +79,19 @@ def flow(c, pyr1, pyr2, kp1, kp2=None, inverse=False, level=None):
         lib().lk_flow_single(C.byref(c), C.byref(a), C.byref(b), len(kp1), kp1.ctypes.data_as(_F), kp2.ctypes.data_as(_F), int(have), int(inverse),
                              ok.ctypes.data_as(_U8))
     return kp2, ok.astype(bool)
+
+
+def photo_edge_errors(pyramids, points, src_slot, tgt_slot, frame_poses, vertex_poses, K=(517.3, 516.5, 325.1, 249.7)):
+    """include/bundle_adjuster.h:70-101 for n edges"""
+    pts = np.ascontiguousarray(points, dtype=np.float64).reshape(-1, 3)
+    n = len(pts)
+    ss = np.ascontiguousarray(np.broadcast_to(np.asarray(src_slot, dtype=np.int32), (n,)))
+    ts = np.ascontiguousarray(np.broadcast_to(np.asarray(tgt_slot, dtype=np.int32), (n,)))
+    fp = np.ascontiguousarray(frame_poses, dtype=np.float64)
+    vp = np.ascontiguousarray(vertex_poses, dtype=np.float64)
+    Kc = np.array(K, dtype=np.float64)
+    err, lvl = np.zeros((n, 16)), np.zeros(n, dtype=np.uint8)
+    imgs = _slots(pyramids)
+    lib().photo_edge_errors(imgs, n, pts.ctypes.data_as(_D), ss.ctypes.data_as(_I32), ts.ctypes.data_as(_I32), fp.ctypes.data_as(_D),
+                            vp.ctypes.data_as(_D), Kc.ctypes.data_as(_D), err.ctypes.data_as(_D), lvl.ctypes.data_as(_U8))
+    return err, lvl

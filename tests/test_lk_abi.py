@@ -19,7 +19,7 @@ def _declared_symbols():
 def test_library_exports_every_declared_symbol(vb):
     from viso_b200 import lk
     declared = _declared_symbols()
-    assert len(declared) == 12
+    assert len(declared) == 13
     lib = C.CDLL(vb.LIB_PATH)
     for name in declared:
         assert hasattr(lib, name), "libviso_ba.so does not export " + name

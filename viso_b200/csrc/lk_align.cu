@@ -15,6 +15,7 @@
 // gradient and H do not change between iterations (the reference recomputes the same values): they
 // are sampled once per level and kept in registers.  Pyramids stay resident in HBM/L2 and are read
 // through the read-only path.
+#include "ba_math.cuh"
 #include "image_math.cuh"
 #include "../../include/viso_lk.h"
 
@@ -203,6 +204,49 @@ __global__ void __launch_bounds__(kThreads) k_lk_flow(const DevImage* __restrict
     }
 }
 
+// ------------------------------------------------------------------------------------------
+// EdgeDirectProjection::computeError (include/bundle_adjuster.h:70-101): 16 lanes per edge, lane =
+// sample idx (j outer, i inner).  The reference stops at the first sample that leaves an image
+// (setLevel(1), :91-95): the lanes vote, samples before the first failure are kept, the rest are 0.
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads) k_edge_direct_projection(const DevImage* __restrict__ slots, int n,
+    const double* __restrict__ points, const int32_t* __restrict__ src_slot, const int32_t* __restrict__ tgt_slot,
+    const double* __restrict__ frame_poses, const double* __restrict__ vertex_poses, double fx, double fy, double cx, double cy,
+    double* __restrict__ errors, uint8_t* __restrict__ level)
+{
+    const int t = blockIdx.x * kThreads + threadIdx.x;
+    const int e = t >> 4, idx = t & 15;
+    const bool live = e < n;
+    const int ee = live ? e : n - 1;
+    const int ss = src_slot[ee], ts = tgt_slot[ee];
+    const DevImage src = slots[kLevels * ss], tgt = slots[kLevels * ts];
+    const double X = points[3 * (size_t)ee], Y = points[3 * (size_t)ee + 1], Z = points[3 * (size_t)ee + 2];
+    double rt[12];
+    visoba::write_cam_rt(vertex_poses + 7 * (size_t)ts, rt); // T->estimate(), :73-75
+    const double x = rt[0] * X + rt[1] * Y + rt[2] * Z + rt[9];
+    const double y = rt[3] * X + rt[4] * Y + rt[5] * Z + rt[10];
+    const double z = rt[6] * X + rt[7] * Y + rt[8] * Z + rt[11];
+    const double tu = (fx * x + 0.0 * y + cx * z) / z, tv = (0.0 * x + fy * y + cy * z) / z; // K * (R p + t), / z  (:77-78)
+    visoba::write_cam_rt(frame_poses + 7 * (size_t)ss, rt);  // srcFrame->Project(p), :79 (keyframe.h:82-89)
+    const double xs = rt[0] * X + rt[1] * Y + rt[2] * Z + rt[9];
+    const double ys = rt[3] * X + rt[4] * Y + rt[5] * Z + rt[10];
+    const double zs = rt[6] * X + rt[7] * Y + rt[8] * Z + rt[11];
+    const double su = 1.0 * ((xs / zs) * fx + cx), sv = 1.0 * ((ys / zs) * fy + cy);
+    const int i = (idx & 3) - 2, j = (idx >> 2) - 2; // :83-84
+    const float u1 = (float)(tu + (double)i), v1 = (float)(tv + (double)j); // :86-87
+    const float u2 = (float)(su + (double)i), v2 = (float)(sv + (double)j); // :88-89
+    const bool outside = !is_inside(tgt, u1, v1) || !is_inside(src, u2, v2);
+    const unsigned half = (threadIdx.x & 16) ? 0xffff0000u : 0x0000ffffu;
+    const unsigned fails = __ballot_sync(0xffffffffu, outside) & half;
+    const int first = fails ? (__ffs(fails) - 1) & 15 : 16; // the sample at which the reference aborts
+    double err = 0.0;
+    if (idx < first) err = pixel_value(src, u2, v2) - pixel_value(tgt, u1, v1); // :97
+    if (live) {
+        errors[16 * (size_t)e + idx] = err;
+        if (idx == 0) level[e] = first < 16 ? 1 : 0;
+    }
+}
+
 } // namespace visolk
 
 // ------------------------------------------------------------------------------------------
@@ -226,6 +270,7 @@ struct viso_lk {
     std::vector<LkBuf> images;
     bool slots_dirty = true;
     LkBuf d_slots, d_ref_slot, d_uv_ref, d_uv_cur, d_kp1, d_kp2, d_success;
+    LkBuf d_pts, d_src, d_tgt, d_fpose, d_vpose, d_err;
 };
 
 namespace {
@@ -446,6 +491,7 @@ void viso_lk_destroy(viso_lk* h)
         for (auto& b : h->images) cudaFree(b.p);
         cudaFree(h->d_slots.p), cudaFree(h->d_ref_slot.p), cudaFree(h->d_uv_ref.p), cudaFree(h->d_uv_cur.p);
         cudaFree(h->d_kp1.p), cudaFree(h->d_kp2.p), cudaFree(h->d_success.p);
+        cudaFree(h->d_pts.p), cudaFree(h->d_src.p), cudaFree(h->d_tgt.p), cudaFree(h->d_fpose.p), cudaFree(h->d_vpose.p), cudaFree(h->d_err.p);
         cudaEventDestroy(h->ev0), cudaEventDestroy(h->ev1);
         cudaStreamDestroy(h->stream);
     }
@@ -532,6 +578,48 @@ int32_t viso_lk_optical_flow_level(viso_lk* h, int32_t level, int32_t slot1, int
 {
     if (level < 0 || level >= kLevels) return lk_fail(h, VISO_LK_ERR_ARG, "optical_flow_level: level %d", level);
     return lk_flow_run(h, level, level, 0, slot1, slot2, n, kp1, kp2, have_initial, inverse, success, nullptr);
+}
+
+int32_t viso_lk_edge_direct_projection(viso_lk* h, int32_t n, const double* points, const int32_t* src_slot, const int32_t* tgt_slot,
+                                       const double* frame_poses, const double* vertex_poses, double fx, double fy, double cx, double cy,
+                                       double* errors, uint8_t* level, float* device_ms)
+{
+    int32_t s = lk_need_device(h);
+    if (s) return s;
+    if (n < 0 || (n > 0 && (!points || !src_slot || !tgt_slot || !frame_poses || !vertex_poses || !errors || !level)))
+        return lk_fail(h, VISO_LK_ERR_ARG, "edge_direct_projection: bad argument");
+    if (n > h->cfg.max_keypoints) return lk_fail(h, VISO_LK_ERR_CAPACITY, "edge_direct_projection: %d edges exceed the pool of %d", n, h->cfg.max_keypoints);
+    if (device_ms) *device_ms = 0.f;
+    if (n == 0) return VISO_LK_OK;
+    for (int32_t e = 0; e < n; ++e)
+        if ((s = lk_check_slot(h, src_slot[e], 0, 0)) || (s = lk_check_slot(h, tgt_slot[e], 0, 0))) return s;
+    const size_t ns = (size_t)h->cfg.max_slots, cap = (size_t)h->cfg.max_keypoints;
+    if (!lk_finite(points, 3 * (size_t)n) || !lk_finite(frame_poses, 7 * ns) || !lk_finite(vertex_poses, 7 * ns))
+        return lk_fail(h, VISO_LK_ERR_NONFINITE, "edge_direct_projection: NaN/Inf in the points or poses");
+    if ((s = lk_sync_slots(h))) return s;
+    if ((s = lk_reserve(h, h->d_pts, sizeof(double) * 3 * cap)) || (s = lk_reserve(h, h->d_src, sizeof(int32_t) * cap))
+        || (s = lk_reserve(h, h->d_tgt, sizeof(int32_t) * cap)) || (s = lk_reserve(h, h->d_fpose, sizeof(double) * 7 * ns))
+        || (s = lk_reserve(h, h->d_vpose, sizeof(double) * 7 * ns)) || (s = lk_reserve(h, h->d_err, sizeof(double) * 16 * cap))
+        || (s = lk_reserve(h, h->d_success, cap)))
+        return s;
+    LCU(cudaMemcpyAsync(h->d_pts.p, points, sizeof(double) * 3 * n, cudaMemcpyHostToDevice, h->stream));
+    LCU(cudaMemcpyAsync(h->d_src.p, src_slot, sizeof(int32_t) * n, cudaMemcpyHostToDevice, h->stream));
+    LCU(cudaMemcpyAsync(h->d_tgt.p, tgt_slot, sizeof(int32_t) * n, cudaMemcpyHostToDevice, h->stream));
+    LCU(cudaMemcpyAsync(h->d_fpose.p, frame_poses, sizeof(double) * 7 * ns, cudaMemcpyHostToDevice, h->stream));
+    LCU(cudaMemcpyAsync(h->d_vpose.p, vertex_poses, sizeof(double) * 7 * ns, cudaMemcpyHostToDevice, h->stream));
+    LCU(cudaEventRecord(h->ev0, h->stream));
+    const int grid = (int)(((size_t)n * 16 + kThreads - 1) / kThreads);
+    k_edge_direct_projection<<<grid, kThreads, 0, h->stream>>>((const DevImage*)h->d_slots.p, n, (const double*)h->d_pts.p,
+        (const int32_t*)h->d_src.p, (const int32_t*)h->d_tgt.p, (const double*)h->d_fpose.p, (const double*)h->d_vpose.p, fx, fy, cx, cy,
+        (double*)h->d_err.p, (uint8_t*)h->d_success.p);
+    LCU(cudaGetLastError());
+    ++h->launches;
+    LCU(cudaEventRecord(h->ev1, h->stream));
+    LCU(cudaMemcpyAsync(errors, h->d_err.p, sizeof(double) * 16 * n, cudaMemcpyDeviceToHost, h->stream));
+    LCU(cudaMemcpyAsync(level, h->d_success.p, n, cudaMemcpyDeviceToHost, h->stream));
+    LCU(cudaStreamSynchronize(h->stream));
+    if (device_ms) LCU(cudaEventElapsedTime(device_ms, h->ev0, h->ev1));
+    return VISO_LK_OK;
 }
 
 } // extern "C"

@@ -37,6 +37,8 @@ LK_SYMBOLS = {
     "viso_lk_align": (C.c_int32, [_P, C.c_int32, _I32, C.c_int32, _D, _D, _U8, _F]),
     "viso_lk_align_level": (C.c_int32, [_P, C.c_int32, C.c_int32, _I32, C.c_int32, _D, _D, _U8]),
     "viso_lk_optical_flow": (C.c_int32, [_P, C.c_int32, C.c_int32, C.c_int32, _F, _F, C.c_int32, C.c_int32, _U8, _F]),
+    "viso_lk_edge_direct_projection": (C.c_int32, [_P, C.c_int32, _D, _I32, _I32, _D, _D, C.c_double, C.c_double, C.c_double, C.c_double,
+                                                   _D, _U8, _F]),
     "viso_lk_optical_flow_level": (C.c_int32, [_P, C.c_int32, C.c_int32, C.c_int32, C.c_int32, _F, _F, C.c_int32, C.c_int32, _U8]),
 }
 
@@ -159,6 +161,23 @@ class LKAligner:
         self._check(_load().viso_lk_optical_flow_level(self._h, level, slot1, slot2, len(kp1), kp1.ctypes.data_as(_F),
                                                        kp2.ctypes.data_as(_F), have, int(inverse), ok.ctypes.data_as(_U8)))
         return kp2, ok.astype(bool)
+
+    def EdgeDirectProjection_computeError(self, points, src_slot, tgt_slot, frame_poses, vertex_poses, K=(517.3, 516.5, 325.1, 249.7)):
+        """reference include/bundle_adjuster.h:70-101 for n edges.  Returns (errors [n][16], level [n] uint8, device_ms)."""
+        pts = np.ascontiguousarray(points, dtype=np.float64).reshape(-1, 3)
+        n = len(pts)
+        ss = np.ascontiguousarray(np.broadcast_to(np.asarray(src_slot, dtype=np.int32), (n,)))
+        ts = np.ascontiguousarray(np.broadcast_to(np.asarray(tgt_slot, dtype=np.int32), (n,)))
+        fp = np.zeros((self.cfg.max_slots, 7))
+        vp = np.zeros((self.cfg.max_slots, 7))
+        fp[:, 3] = vp[:, 3] = 1.0
+        fp[:len(frame_poses)] = frame_poses
+        vp[:len(vertex_poses)] = vertex_poses
+        err, lvl, ms = np.zeros((n, 16)), np.zeros(n, dtype=np.uint8), C.c_float(0)
+        self._check(_load().viso_lk_edge_direct_projection(self._h, n, pts.ctypes.data_as(_D), ss.ctypes.data_as(_I32), ts.ctypes.data_as(_I32),
+                                                           fp.ctypes.data_as(_D), vp.ctypes.data_as(_D), K[0], K[1], K[2], K[3],
+                                                           err.ctypes.data_as(_D), lvl.ctypes.data_as(_U8), C.byref(ms)))
+        return err, lvl, float(ms.value)
 
     def kernel_launches(self):
         return int(_load().viso_lk_kernel_launches(self._h))
