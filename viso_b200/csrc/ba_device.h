@@ -25,8 +25,19 @@ constexpr int kChunkPoints = 1024;
 constexpr int kSmallMaxN = 162; // dense per-problem solve in shared memory up to 27 free poses
 // window fast path (ba_window.cu): one CTA per tile of consecutive points of one problem
 constexpr int kWinThreads = 128;
-constexpr int kWinObsCap = 640; // observations per tile (their records live in shared memory)
-constexpr int kWinPtCap = 88;   // points per tile
+// tile shape and residency of the linearise kernel: compile-time tuning knobs (tools/win_tune.sh sweeps them)
+#ifndef VISO_WIN_OBS_CAP
+#define VISO_WIN_OBS_CAP 640
+#endif
+#ifndef VISO_WIN_PT_CAP
+#define VISO_WIN_PT_CAP 88
+#endif
+#ifndef VISO_WIN_LS_CTAS
+#define VISO_WIN_LS_CTAS 3
+#endif
+constexpr int kWinObsCap = VISO_WIN_OBS_CAP; // observations per tile (their records live in shared memory)
+constexpr int kWinPtCap = VISO_WIN_PT_CAP;   // points per tile
+constexpr int kWinLsCtas = VISO_WIN_LS_CTAS; // CTAs of k_win_linearize_schur resident per SM (registers and shared memory)
 constexpr int kWinMaxCams = 32; // keyframes per problem (visibility mask is 32 bits)
 constexpr int kWinAutoMinTiles = 2 * 148; // "auto": fewer tiles than this cannot fill the GPU -> general path
 

@@ -96,7 +96,7 @@ __device__ __forceinline__ WinTile load_tile(const DevProblem& P)
 //   A3 (thread per observation)  G~ = F w Jl L^-T,  v~ = F (w r + G zb)
 //   B  (8 lanes per S block)     S_IJ -= Jp_a^T G_a G_b^T Jp_b, S_II += w Jp^T Jp, bs_I -= Jp^T v~
 // ------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kWinThreads, 3) k_win_linearize_schur(DevProblem P, int init_pass, double lambda_override)
+__global__ void __launch_bounds__(kWinThreads, kWinLsCtas) k_win_linearize_schur(DevProblem P, int init_pass, double lambda_override)
 {
     extern __shared__ __align__(16) unsigned char sm[];
     double2* const rec = reinterpret_cast<double2*>(sm + kLsRec);
@@ -600,7 +600,7 @@ int launch_win_prob_sums(const DevProblem& P, int even_if_inactive, cudaStream_t
     return 1;
 }
 
-static_assert(3 * (kLsBytes + 1024) <= 227 * 1024, "three linearize CTAs per SM must fit in shared memory");
+static_assert(kWinLsCtas * (kLsBytes + 1024) <= 227 * 1024, "the resident linearize CTAs of one SM must fit in shared memory");
 static_assert(kWinPtCap <= 255 && kWinObsCap <= 65535 && kWinMaxCams <= 32, "meta word packing");
 
 } // namespace visoba
