@@ -12,7 +12,7 @@ import pytest
 pytestmark = pytest.mark.gpu
 
 COST_RTOL, POSE_ATOL, POINT_ATOL = 1e-5, 1e-6, 1e-5  # BASELINE.json north_star
-GOLDEN = sorted(glob.glob(os.path.join(os.path.dirname(__file__), "golden", "*.npz")))
+GOLDEN = sorted(glob.glob(os.path.join(os.path.dirname(__file__), "golden", "tiny_*.npz")))  # the bundle-adjustment fixtures (tools/make_golden.py)
 # problems of <= 32 keyframes take the window fast path (tile kernels, ba_window.cu) unless told
 # otherwise; the tests that matter run both it and the general pair-list path
 BOTH_PATHS = pytest.mark.parametrize("path", [1, 2], ids=["window", "general"])

@@ -12,7 +12,7 @@ import pytest
 import numpy_ba
 
 K = (517.3, 516.5, 325.1, 249.7)  # reference src/main.cpp:14-17
-GOLDEN = sorted(glob.glob(os.path.join(os.path.dirname(__file__), "golden", "*.npz")))
+GOLDEN = sorted(glob.glob(os.path.join(os.path.dirname(__file__), "golden", "tiny_*.npz")))  # the bundle-adjustment fixtures (tools/make_golden.py)
 _D = C.POINTER(C.c_double)
 
 

@@ -99,7 +99,16 @@ __device__ __forceinline__ int cut_tiles(const int32_t* __restrict__ pt_ptr, int
     while (q < hi) {
         int e = q;
         const int o0 = pt_ptr[q];
-        while (e < hi && e - q < kWinPtCap && pt_ptr[e + 1] - o0 <= kWinObsCap) ++e;
+        { // the largest e <= min(hi, q + kWinPtCap) with pt_ptr[e] - o0 <= kWinObsCap: pt_ptr is monotone, so the
+          // greedy scan's end point is found by bisection (23 tiles x 7 probes instead of 2000 loads per window)
+            int lo = q, up = min(hi, q + kWinPtCap);
+            while (lo < up) {
+                const int mid = (lo + up + 1) >> 1;
+                if (pt_ptr[mid] - o0 <= kWinObsCap) lo = mid;
+                else up = mid - 1;
+            }
+            e = lo;
+        }
         if (e == q) ++e; // a point with more observations than a tile holds (only with duplicate edges,
                          // which send the handle to the general path anyway): keep the loop finite
         if (kFill) {
