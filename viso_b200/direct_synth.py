@@ -88,3 +88,34 @@ def synth_scene(seed=1, n_points=2000, rotvec=(0.004, -0.006, 0.003), trans=(0.0
     return {"ref_pyr": pyramid(ref), "cur_pyr": pyramid(cur), "points": pts,
             "ref_pose": np.array([0, 0, 0, 1.0, 0, 0, 0]), "true_pose": true_pose, "init_pose": init,
             "identity": np.array([0, 0, 0, 1.0, 0, 0, 0])}
+
+
+def render_plane(T, pose, width=W, height=H):
+    """The textured plane z = 1 of the world frame seen from `pose` (world -> camera), rendered exactly."""
+    uu, vv = np.meshgrid(np.arange(width, dtype=np.float64), np.arange(height, dtype=np.float64))
+    R, t = quat_to_R(pose[:4]), pose[4:]
+    d = np.stack([(uu - CX) / FX, (vv - CY) / FY, np.ones_like(uu)], axis=-1)
+    Rt_d = d @ R
+    Rt_t = R.T @ t
+    s = (1.0 + Rt_t[2]) / Rt_d[..., 2]
+    Xw = Rt_d * s[..., None] - Rt_t
+    return np.clip(np.rint(T(FX * Xw[..., 0] / Xw[..., 2] + CX, FY * Xw[..., 1] / Xw[..., 2] + CY)), 0, 255).astype(np.uint8)
+
+
+def project(pose, P):
+    """Keyframe::Project at level 0 for an array of points"""
+    Pc = P @ quat_to_R(pose[:4]).T + pose[4:]
+    return np.stack([FX * Pc[:, 0] / Pc[:, 2] + CX, FY * Pc[:, 1] / Pc[:, 2] + CY], axis=1)
+
+
+def synth_sequence(seed=1, n_frames=5, n_points=1500, step_rot=(0.003, -0.004, 0.002), step_trans=(0.010, -0.006, 0.008)):
+    """A short camera trajectory over the textured plane: frame 0 at the identity (viso keeps frame 0 there,
+    include/keyframe.h:34-35), frame k at k steps of a constant twist.  Returns images, true poses, map points."""
+    rng = np.random.default_rng(seed)
+    T = _texture(rng)
+    poses = [pose_from_rotvec(np.asarray(step_rot) * k, np.asarray(step_trans) * k) for k in range(n_frames)]
+    images = [render_plane(T, p) for p in poses]
+    pu = rng.uniform(60, W - 60, size=n_points)
+    pv = rng.uniform(60, H - 60, size=n_points)
+    pts = np.stack([(pu - CX) / FX, (pv - CY) / FY, np.ones(n_points)], axis=-1)
+    return {"images": images, "poses": np.stack(poses), "points": pts}
