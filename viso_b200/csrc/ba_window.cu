@@ -131,6 +131,12 @@ __global__ void __launch_bounds__(kWinThreads, kWinLsCtas) k_win_linearize_schur
         }
     }
     const int nblk_all = t.nf * (t.nf + 1) / 2;
+    { // the tile's pair lists are read once, in phase B, a few rounds ahead of their use: a round is shorter than an
+      // HBM miss (ncu: 12 % of the kernel's stall samples sat on that load), so start the lines towards L2 now
+        const unsigned int* lp = P.win_pairs + t.list_off;
+        const int words = (int)__ldg(P.win_blkptr + t.blkptr_off + (init_pass ? t.nf : nblk_all));
+        for (int w = tid * 32; w < words; w += kWinThreads * 32) asm volatile("prefetch.global.L2 [%0];" ::"l"(lp + w));
+    }
     {
         for (int o = tid; o < t.no; o += kWinThreads) s_slot[o] = __ldg(P.win_slot + t.o0 + o);
         for (int k = tid; k <= nblk_all; k += kWinThreads) s_bp[k] = __ldg(P.win_blkptr + t.blkptr_off + k);
