@@ -87,6 +87,18 @@ __device__ __forceinline__ WinTile load_tile(const DevProblem& P)
     return t;
 }
 
+// global -> shared without a register round trip (LDGSTS): a tile's inputs are many short strided copies, and a
+// load-then-store loop leaves one miss in flight per thread; these all go out back to back and are awaited once
+__device__ __forceinline__ void cp_async8(void* smem, const void* gmem)
+{
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((unsigned)__cvta_generic_to_shared(smem)), "l"(gmem));
+}
+__device__ __forceinline__ void cp_async4(void* smem, const void* gmem)
+{
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(smem)), "l"(gmem));
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
 } // namespace
 
 // ------------------------------------------------------------------------------------------
@@ -111,23 +123,21 @@ __global__ void __launch_bounds__(kWinThreads, kWinLsCtas) k_win_linearize_schur
 
     const int tid = threadIdx.x;
     const WinTile t = load_tile(P);
-    const LmState& st = P.lm[t.prob];
-    if (!st.active && lambda_override < 0.0) return;
-    const int cur = st.cur;
-    const double lambda = init_pass ? 0.0 : (lambda_override >= 0.0 ? lambda_override : st.lambda);
 
-    // ---- A0: everything the tile needs from HBM, issued at once.  Thread <-> slot: the
-    // observations of the tile in keyframe-major order, so that consecutive threads share the
-    // keyframe (R|t reads broadcast) and touch consecutive record slots (no bank conflicts) ----
+    // ---- A0: everything the tile needs from HBM, issued at once, and what does not depend on the LM state
+    // before the state is read.  Thread <-> slot: the observations of the tile in keyframe-major order, so that
+    // consecutive threads share the keyframe (R|t reads broadcast) and touch consecutive record slots ----
     unsigned int meta[kObsPerThread];
     float2 uv[kObsPerThread];
+    unsigned short slot_r[kObsPerThread];
 #pragma unroll
     for (int i = 0; i < kObsPerThread; ++i) {
         const int o = tid + i * kWinThreads;
-        meta[i] = 0u, uv[i] = make_float2(0.f, 0.f);
+        meta[i] = 0u, uv[i] = make_float2(0.f, 0.f), slot_r[i] = 0;
         if (o < t.no) {
             meta[i] = __ldg(P.win_meta + t.o0 + o);
             uv[i] = __ldg(P.win_uv + t.o0 + o);
+            slot_r[i] = __ldg(P.win_slot + t.o0 + o);
         }
     }
     const int nblk_all = t.nf * (t.nf + 1) / 2;
@@ -137,18 +147,31 @@ __global__ void __launch_bounds__(kWinThreads, kWinLsCtas) k_win_linearize_schur
         const int words = (int)__ldg(P.win_blkptr + t.blkptr_off + (init_pass ? t.nf : nblk_all));
         for (int w = tid * 32; w < words; w += kWinThreads * 32) asm volatile("prefetch.global.L2 [%0];" ::"l"(lp + w));
     }
+    for (int k = tid; k <= nblk_all; k += kWinThreads) cp_async4(s_bp + k, P.win_blkptr + t.blkptr_off + k);
+    const int obs0_r = tid <= t.np ? __ldg(P.pt_ptr + t.p0 + tid) - t.o0 : 0; // kWinPtCap < kWinThreads
+    const LmState& st = P.lm[t.prob];
+    if (!st.active && lambda_override < 0.0) {
+        cp_async_wait_all();
+        return;
+    }
+    const int cur = st.cur;
+    const double lambda = init_pass ? 0.0 : (lambda_override >= 0.0 ? lambda_override : st.lambda);
     {
-        for (int o = tid; o < t.no; o += kWinThreads) s_slot[o] = __ldg(P.win_slot + t.o0 + o);
-        for (int k = tid; k <= nblk_all; k += kWinThreads) s_bp[k] = __ldg(P.win_blkptr + t.blkptr_off + k);
         const double* __restrict__ gp = P.pts[cur] + 3 * (size_t)t.p0;
         for (int i = tid; i < 3 * t.np; i += kWinThreads) {
             const int p = i / 3, k = i - 3 * p;
-            s_pt[k * kPtStride + p] = gp[i];
+            cp_async8(s_pt + k * kPtStride + p, gp + i);
         }
         const double* __restrict__ grt = P.cam_rt[cur] + 12 * (size_t)t.cam0;
-        for (int i = tid; i < 12 * t.ncam; i += kWinThreads) s_rt[i] = grt[i];
-        for (int p = tid; p <= t.np; p += kWinThreads) s_obs0[p] = (unsigned short)(__ldg(P.pt_ptr + t.p0 + p) - t.o0);
+        for (int i = tid; i < 12 * t.ncam; i += kWinThreads) cp_async8(s_rt + i, grt + i);
+#pragma unroll
+        for (int i = 0; i < kObsPerThread; ++i) {
+            const int o = tid + i * kWinThreads;
+            if (o < t.no) s_slot[o] = slot_r[i];
+        }
+        if (tid <= t.np) s_obs0[tid] = (unsigned short)obs0_r;
     }
+    cp_async_wait_all();
     __syncthreads();
 
     // ---- A1 ----
@@ -421,41 +444,54 @@ __global__ void __launch_bounds__(kWinThreads, 5) k_win_update(DevProblem P)
 
     const int tid = threadIdx.x;
     const WinTile t = load_tile(P);
-    const LmState& st = P.lm[t.prob];
-    if (!st.active) return;
-    const int cur = st.cur, cand = cur ^ 1;
-    const double lambda = st.lambda;
-
+    // everything that does not depend on the LM state goes out before the state is read (one dependent miss less)
     unsigned int meta[kObsPerThread];
     float2 uv[kObsPerThread];
+    unsigned short slot_r[kObsPerThread];
 #pragma unroll
     for (int i = 0; i < kObsPerThread; ++i) {
         const int o = tid + i * kWinThreads;
-        meta[i] = 0u, uv[i] = make_float2(0.f, 0.f);
+        meta[i] = 0u, uv[i] = make_float2(0.f, 0.f), slot_r[i] = 0;
         if (o < t.no) {
             meta[i] = __ldg(P.win_meta + t.o0 + o);
             uv[i] = __ldg(P.win_uv + t.o0 + o);
+            slot_r[i] = __ldg(P.win_slot + t.o0 + o);
         }
     }
     {
-        for (int o = tid; o < t.no; o += kWinThreads) s_slot[o] = __ldg(P.win_slot + t.o0 + o);
-        const double* __restrict__ gp = P.pts[cur] + 3 * (size_t)t.p0;
-        for (int i = tid; i < 3 * t.np; i += kWinThreads) {
-            const int p = i / 3, k = i - 3 * p;
-            s_pt[k * kPtStride + p] = gp[i];
-        }
         const double* __restrict__ gi = P.ptinfo + kPtInfoDoubles * (size_t)t.p0;
         for (int i = tid; i < 9 * t.np; i += kWinThreads) {
             const int p = i / 9, k = i - 9 * p;
-            s_info[k * kPtStride + p] = gi[i];
+            cp_async8(s_info + k * kPtStride + p, gi + i);
+        }
+        const double* __restrict__ gd = P.dp + 6 * (size_t)t.cam0;
+        for (int i = tid; i < 6 * t.ncam; i += kWinThreads) cp_async8(s_dp + i, gd + i);
+    }
+    const int obs0_r = tid <= t.np ? __ldg(P.pt_ptr + t.p0 + tid) - t.o0 : 0; // kWinPtCap < kWinThreads
+    const LmState& st = P.lm[t.prob];
+    if (!st.active) {
+        cp_async_wait_all();
+        return;
+    }
+    const int cur = st.cur, cand = cur ^ 1;
+    const double lambda = st.lambda;
+    {
+        const double* __restrict__ gp = P.pts[cur] + 3 * (size_t)t.p0;
+        for (int i = tid; i < 3 * t.np; i += kWinThreads) {
+            const int p = i / 3, k = i - 3 * p;
+            cp_async8(s_pt + k * kPtStride + p, gp + i);
         }
         const double* __restrict__ g1 = P.cam_rt[cur] + 12 * (size_t)t.cam0;
         const double* __restrict__ g2 = P.cam_rt[cand] + 12 * (size_t)t.cam0;
-        for (int i = tid; i < 12 * t.ncam; i += kWinThreads) s_rt[i] = g1[i], s_rt2[i] = g2[i];
-        const double* __restrict__ gd = P.dp + 6 * (size_t)t.cam0;
-        for (int i = tid; i < 6 * t.ncam; i += kWinThreads) s_dp[i] = gd[i];
-        for (int p = tid; p <= t.np; p += kWinThreads) s_obs0[p] = (unsigned short)(__ldg(P.pt_ptr + t.p0 + p) - t.o0);
+        for (int i = tid; i < 12 * t.ncam; i += kWinThreads) cp_async8(s_rt + i, g1 + i), cp_async8(s_rt2 + i, g2 + i);
+#pragma unroll
+        for (int i = 0; i < kObsPerThread; ++i) {
+            const int o = tid + i * kWinThreads;
+            if (o < t.no) s_slot[o] = slot_r[i];
+        }
+        if (tid <= t.np) s_obs0[tid] = (unsigned short)obs0_r;
     }
+    cp_async_wait_all();
     __syncthreads();
 
     // ---- U1 ----
@@ -608,5 +644,6 @@ int launch_win_prob_sums(const DevProblem& P, int even_if_inactive, cudaStream_t
 
 static_assert(kWinLsCtas * (kLsBytes + 1024) <= 227 * 1024, "the resident linearize CTAs of one SM must fit in shared memory");
 static_assert(kWinPtCap <= 255 && kWinObsCap <= 65535 && kWinMaxCams <= 32, "meta word packing");
+static_assert(kWinPtCap < kWinThreads, "one thread per point-pointer entry at tile entry");
 
 } // namespace visoba
