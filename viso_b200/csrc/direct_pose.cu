@@ -205,21 +205,43 @@ k_direct(const DevFrame* __restrict__ frames, const DevParams K, double* __restr
 #pragma unroll
             for (int k = 0; k < kSums; ++k) acc[k] = 0.0;
             int good_cnt = 0;
-            for (int i = gw; i < F.n_points; i += nw) { // viso.cpp:688
-                const double X = __ldg(F.points + 3 * (size_t)i), Y = __ldg(F.points + 3 * (size_t)i + 1);
-                const double Z = __ldg(F.points + 3 * (size_t)i + 2);
-                double u_ref, v_ref, u_cur, v_cur, x, y, z, xr, yr, zr;
-                project(K, s_ref_rt, X, Y, Z, scale, u_ref, v_ref, xr, yr, zr); // viso.cpp:693-695
-                project(K, s_rt, X, Y, Z, scale, u_cur, v_cur, x, y, z);         // viso.cpp:697-699
-                const bool good = is_inside(ref, u_ref - hp, v_ref - hp) && is_inside(ref, u_ref + hp, v_ref + hp)
-                    && is_inside(cur, u_cur - hp, v_cur - hp) && is_inside(cur, u_cur + hp, v_cur + hp);
-                if (!good) continue; // viso.cpp:704-715, uniform over the warp
-                ++good_cnt;
-                // dPixeldXi (viso.cpp:640-658)
-                const double fx = K.fx * scale, fy = K.fy * scale, zz = z * z, xy = x * y;
-                double J0[6], J1[6];
-                J0[0] = fx / z, J0[1] = 0, J0[2] = -fx * x / zz, J0[3] = -fx * xy / zz, J0[4] = fx + fx * x * x / zz, J0[5] = -fx * y / z;
-                J1[0] = 0, J1[1] = fy / z, J1[2] = -fy * y / zz, J1[3] = -fy - fy * y * y / zz, J1[4] = fy * xy / zz, J1[5] = fy * x / z;
+            // The warp's points come in batches of 32: lane l prepares point gw + (batch * 32 + l) * nw (projections,
+            // the inside test, dPixeldXi: 14 fp64 divisions that would otherwise be repeated by all 32 lanes), then the
+            // good points are taken in order, their 14 values broadcast by shuffles, and the lanes split the patch.
+            for (int base = gw; base < F.n_points; base += 32 * nw) { // viso.cpp:688
+                const int i = base + lane * nw;
+                double q_ur = 0, q_vr = 0, q_uc = 0, q_vc = 0, q_j[10];
+#pragma unroll
+                for (int q = 0; q < 10; ++q) q_j[q] = 0.0;
+                bool good = false;
+                if (i < F.n_points) {
+                    const double X = __ldg(F.points + 3 * (size_t)i), Y = __ldg(F.points + 3 * (size_t)i + 1);
+                    const double Z = __ldg(F.points + 3 * (size_t)i + 2);
+                    double x, y, z, xr, yr, zr;
+                    project(K, s_ref_rt, X, Y, Z, scale, q_ur, q_vr, xr, yr, zr); // viso.cpp:693-695
+                    project(K, s_rt, X, Y, Z, scale, q_uc, q_vc, x, y, z);         // viso.cpp:697-699
+                    good = is_inside(ref, q_ur - hp, q_vr - hp) && is_inside(ref, q_ur + hp, q_vr + hp)
+                        && is_inside(cur, q_uc - hp, q_vc - hp) && is_inside(cur, q_uc + hp, q_vc + hp); // viso.cpp:704-715
+                    // dPixeldXi (viso.cpp:640-658); its two structural zeros are not carried
+                    const double fx = K.fx * scale, fy = K.fy * scale, zz = z * z, xy = x * y;
+                    q_j[0] = fx / z, q_j[1] = -fx * x / zz, q_j[2] = -fx * xy / zz, q_j[3] = fx + fx * x * x / zz, q_j[4] = -fx * y / z;
+                    q_j[5] = fy / z, q_j[6] = -fy * y / zz, q_j[7] = -fy - fy * y * y / zz, q_j[8] = fy * xy / zz, q_j[9] = fy * x / z;
+                }
+                unsigned todo = __ballot_sync(0xffffffffu, good);
+                good_cnt += __popc(todo);
+                while (todo) {
+                    const int src = __ffs(todo) - 1;
+                    todo &= todo - 1;
+                    const double u_ref = __shfl_sync(0xffffffffu, q_ur, src), v_ref = __shfl_sync(0xffffffffu, q_vr, src);
+                    const double u_cur = __shfl_sync(0xffffffffu, q_uc, src), v_cur = __shfl_sync(0xffffffffu, q_vc, src);
+                    double J0[6], J1[6];
+                    J0[0] = __shfl_sync(0xffffffffu, q_j[0], src), J0[1] = 0;
+                    J1[0] = 0, J1[1] = __shfl_sync(0xffffffffu, q_j[5], src);
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        J0[2 + q] = __shfl_sync(0xffffffffu, q_j[1 + q], src);
+                        J1[2 + q] = __shfl_sync(0xffffffffu, q_j[6 + q], src);
+                    }
                 for (int k = lane; k < npix; k += 32) { // viso.cpp:722-723: x outer, y inner
                     const double px = (double)(k / side - K.hp), py = (double)(k % side - K.hp);
                     const double uc = u_cur + px, vc = v_cur + py;
@@ -238,6 +260,7 @@ k_direct(const DevFrame* __restrict__ frames, const DevParams K, double* __restr
 #pragma unroll
                     for (int q = 0; q < 6; ++q) acc[21 + q] += -error * J[q];  // viso.cpp:728
                     acc[27] += error * error;                                  // viso.cpp:729
+                }
                 }
             }
 
