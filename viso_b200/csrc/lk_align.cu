@@ -62,6 +62,7 @@ __device__ __forceinline__ void solve2(double h00, double h01, double h10, doubl
 // ------------------------------------------------------------------------------------------
 // LKAlignmentSingle over the levels level_hi .. level_lo, one warp per AlignmentPair
 // ------------------------------------------------------------------------------------------
+template <int kPL> // patch pixels per lane: 2 for the reference's 8x8 patch, kMaxPerLane for larger ones
 __global__ void __launch_bounds__(kThreads) k_lk_align(const DevImage* __restrict__ slots, const int32_t* __restrict__ ref_slot,
     int cur_slot, int n, const double* __restrict__ uv_ref, double* __restrict__ uv_cur, uint8_t* __restrict__ success,
     int level_hi, int level_lo, const LkParams P)
@@ -78,10 +79,10 @@ __global__ void __launch_bounds__(kThreads) k_lk_align(const DevImage* __restric
         const double s = 1.0 / (double)(1 << level); // scales[level], viso.cpp:850
         const DevImage ref = slots[kLevels * rs + level], cur = slots[kLevels * cur_slot + level];
         // inverse = true (viso.cpp:848): J = -grad(ref) and the reference patch do not depend on (dx, dy)
-        double J0[kMaxPerLane], J1[kMaxPerLane], rv[kMaxPerLane];
+        double J0[kPL], J1[kPL], rv[kPL];
         double h00 = 0, h01 = 0, h11 = 0;
 #pragma unroll
-        for (int q = 0; q < kMaxPerLane; ++q) {
+        for (int q = 0; q < kPL; ++q) {
             const int k = lane + 32 * q;
             J0[q] = J1[q] = rv[q] = 0.0;
             if (k < npix) {
@@ -104,7 +105,7 @@ __global__ void __launch_bounds__(kThreads) k_lk_align(const DevImage* __restric
             double b0 = 0, b1 = 0;
             cost = 0;
 #pragma unroll
-            for (int q = 0; q < kMaxPerLane; ++q) {
+            for (int q = 0; q < kPL; ++q) {
                 const int k = lane + 32 * q;
                 if (k < npix) {
                     const int x = k / side - P.hp, y = k % side - P.hp;
@@ -398,8 +399,12 @@ int32_t lk_align_run(viso_lk* h, int32_t level_hi, int32_t level_lo, int32_t n, 
     LCU(cudaMemcpyAsync(h->d_uv_cur.p, uv_cur, sizeof(double) * 2 * n, cudaMemcpyHostToDevice, h->stream));
     LCU(cudaEventRecord(h->ev0, h->stream));
     const int grid = (n * 32 + kThreads - 1) / kThreads;
-    k_lk_align<<<grid, kThreads, 0, h->stream>>>((const DevImage*)h->d_slots.p, (const int32_t*)h->d_ref_slot.p, cur_slot, n,
-        (const double*)h->d_uv_ref.p, (double*)h->d_uv_cur.p, (uint8_t*)h->d_success.p, level_hi, level_lo, lk_params(h->cfg));
+    if (4 * h->cfg.half_patch_size * h->cfg.half_patch_size <= 64)
+        k_lk_align<2><<<grid, kThreads, 0, h->stream>>>((const DevImage*)h->d_slots.p, (const int32_t*)h->d_ref_slot.p, cur_slot, n,
+            (const double*)h->d_uv_ref.p, (double*)h->d_uv_cur.p, (uint8_t*)h->d_success.p, level_hi, level_lo, lk_params(h->cfg));
+    else
+        k_lk_align<kMaxPerLane><<<grid, kThreads, 0, h->stream>>>((const DevImage*)h->d_slots.p, (const int32_t*)h->d_ref_slot.p, cur_slot, n,
+            (const double*)h->d_uv_ref.p, (double*)h->d_uv_cur.p, (uint8_t*)h->d_success.p, level_hi, level_lo, lk_params(h->cfg));
     LCU(cudaGetLastError());
     ++h->launches;
     LCU(cudaEventRecord(h->ev1, h->stream));
