@@ -114,3 +114,36 @@ def test_edge_cases(vb, scene):
     with pytest.raises(direct.DirectError) as e:
         fresh.DirectPoseEstimationMultiLayer(scene["identity"])
     assert e.value.code == 7  # images not set
+
+
+def test_moved_reference_frame_strided_images_and_small_patch(vb, scene):
+    """last_frame away from the origin (the map's world frame is not the last frame's), cv::Mat rows with padding
+    (step > cols), and a 4x4 patch"""
+    from viso_b200 import direct
+    from viso_b200.direct_synth import quat_to_R
+    ref_pose = pose_from_rotvec((0.01, -0.02, 0.015), (0.05, -0.03, 0.02))
+    R, t = quat_to_R(ref_pose[:4]), ref_pose[4:]
+    world_pts = (scene["points"] - t) @ R          # Pc = R Pw + t  ->  Pw = R^T (Pc - t)
+    # T21 maps the world to the current frame: (true motion) o (reference pose)
+    est = direct.DirectPoseEstimator(max_points=len(world_pts), reference_termination=0, half_patch_size=2, max_iterations=6)
+
+    def padded(img):
+        buf = np.zeros((img.shape[0], img.shape[1] + 24), dtype=np.uint8)
+        buf[:, :img.shape[1]] = img
+        return buf[:, :img.shape[1]]  # a view whose row stride is cols + 24
+    ref_p, cur_p = [padded(im) for im in scene["ref_pyr"]], [padded(im) for im in scene["cur_pyr"]]
+    assert ref_p[0].strides[0] == ref_p[0].shape[1] + 24
+    est.set_pyramid(0, ref_p)
+    est.set_pyramid(1, cur_p)
+    est.set_reference_pose(ref_pose)
+    est.set_points(world_pts)
+    pose, stats, _ = est.DirectPoseEstimationMultiLayer(ref_pose)  # X starts at last_frame's pose (viso.cpp:113)
+    c = dorc.cfg(reference_termination=0, half_patch_size=2, max_iterations=6)
+    po, so = dorc.multi_layer(c, ref_p, cur_p, ref_pose, ref_pose, world_pts)
+    assert [s.iterations for s in stats[0]] == [s.iterations for s in so]
+    assert [s.n_good for s in stats[0]] == [s.n_good for s in so]
+    assert np.abs(pose - po).max() < 1e-9
+    # the recovered pose composes the true motion with the reference pose
+    Rt, tt = quat_to_R(scene["true_pose"][:4]), scene["true_pose"][4:]
+    want_R, want_t = Rt @ R, Rt @ t + tt
+    assert np.abs(quat_to_R(pose[:4]) - want_R).max() < 3e-3 and np.abs(pose[4:] - want_t).max() < 3e-3

@@ -125,3 +125,29 @@ def test_runs_are_bit_identical(vb, scene):
     u1, o1, _ = a.LKAlignment(0, 1, scene["uv_ref"], scene["uv_ref"])
     u2, o2, _ = a.LKAlignment(0, 1, scene["uv_ref"], scene["uv_ref"])
     assert np.array_equal(u1, u2) and np.array_equal(o1, o2)
+
+
+@pytest.mark.parametrize("hp", [2, 6, 8])
+def test_other_patch_sizes_match_the_oracle(vb, scene, hp):
+    """half_patch_size is a constant of Viso (include/viso.h:25) but a parameter here: 4x4 patches use one pixel
+    per lane, 12x12 and 16x16 patches the general pixels-per-lane path of the kernels"""
+    a = _aligner(scene, half_patch_size=hp, align_iterations=5, flow_iterations=4)
+    n = 400
+    start = scene["uv_ref"][:n] + 0.6
+    uv, ok, _ = a.LKAlignment(0, 1, scene["uv_ref"][:n], start)
+    c = lko.cfg(half_patch_size=hp, align_iterations=5, flow_iterations=4)
+    uvo, oko = lko.align(c, [scene["ref_pyr"]], 0, scene["cur_pyr"], scene["uv_ref"][:n], start)
+    assert np.array_equal(ok, oko)
+    assert np.abs(uv - uvo).max() < 1e-7
+    kp1 = scene["uv_ref"][:n].astype(np.float32)
+    out, okf, _ = a.OpticalFlowMultiLevel(0, 1, kp1, None, inverse=False)
+    outo, okfo = lko.flow(c, scene["ref_pyr"], scene["cur_pyr"], kp1, None, inverse=False)
+    assert np.array_equal(okf, okfo)
+    assert np.abs(out - outo).max() < 1e-4
+
+
+def test_patch_size_beyond_the_kernel_limit_is_rejected(vb):
+    from viso_b200 import lk
+    with pytest.raises(lk.LkError) as e:
+        lk.LKAligner(half_patch_size=9)  # 18 x 18 = 324 pixels > 32 lanes x 8
+    assert e.value.code == 6
