@@ -202,6 +202,7 @@ __global__ void __launch_bounds__(kWinThreads, kWinLsCtas) k_win_linearize_schur
     __syncthreads();
 
     // ---- A2 ----
+    double maxdiag = 0.0; // init pass: this thread's share of max diag(H_ll)
     for (int p = tid; p < t.np; p += kWinThreads) {
         double h00 = 0, h10 = 0, h11 = 0, h20 = 0, h21 = 0, h22 = 0, b0 = 0, b1 = 0, b2 = 0;
         for (int o = s_obs0[p]; o < s_obs0[p + 1]; ++o) {
@@ -221,8 +222,7 @@ __global__ void __launch_bounds__(kWinThreads, kWinLsCtas) k_win_linearize_schur
         }
         double i00 = 0, i10 = 0, i11 = 0, i20 = 0, i21 = 0, i22 = 0, z0 = 0, z1 = 0, z2 = 0;
         if (init_pass) { // g2o computeLambdaInit: point part of max diag(H); max is order-free
-            const double m = fmax(h00, fmax(h11, h22));
-            if (m > 0.0) atomicMax(P.maxdiag_bits + t.prob, (unsigned long long)__double_as_longlong(m));
+            maxdiag = fmax(maxdiag, fmax(h00, fmax(h11, h22)));
         } else {
             h00 += lambda, h11 += lambda, h22 += lambda;
             const double l00 = sqrt(h00);
@@ -247,6 +247,11 @@ __global__ void __launch_bounds__(kWinThreads, kWinLsCtas) k_win_linearize_schur
             s_info[k * kPtStride + p] = v[k];
             gi[k] = v[k];
         }
+    }
+    if (init_pass) { // one atomic per warp instead of one per point (2000 per window on one address): max is order-free
+#pragma unroll
+        for (int off = 16; off >= 1; off >>= 1) maxdiag = fmax(maxdiag, __shfl_xor_sync(0xffffffffu, maxdiag, off));
+        if ((tid & 31) == 0 && maxdiag > 0.0) atomicMax(P.maxdiag_bits + t.prob, (unsigned long long)__double_as_longlong(maxdiag));
     }
     __syncthreads();
 
