@@ -114,8 +114,17 @@ __global__ void __launch_bounds__(128) k_linearize(DevProblem P, int init_pass, 
     double i00 = 0, i10 = 0, i11 = 0, i20 = 0, i21 = 0, i22 = 0, z0 = 0, z1 = 0, z2 = 0;
     if (init_pass) {
         // g2o computeLambdaInit: the point part of max diag(H); max is order-free -> deterministic
-        const double m = fmax(h00, fmax(h11, h22));
-        if (m > 0.0) atomicMax(P.maxdiag_bits + prob, (unsigned long long)__double_as_longlong(m));
+        double m = fmax(h00, fmax(h11, h22));
+        // a full warp of points of one problem (the rule: one large problem has 100k points on ONE address) folds
+        // its maximum first and sends one atomic; ragged warps keep one atomic per point
+        const unsigned act = __activemask();
+        const bool whole = act == 0xffffffffu && __match_any_sync(act, prob) == 0xffffffffu;
+        if (whole) {
+#pragma unroll
+            for (int off = 16; off >= 1; off >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, off));
+        }
+        if (m > 0.0 && (!whole || (threadIdx.x & 31) == 0))
+            atomicMax(P.maxdiag_bits + prob, (unsigned long long)__double_as_longlong(m));
     } else {
         h00 += lambda;
         h11 += lambda;
