@@ -273,6 +273,16 @@ def test_batched_windows_with_diverging_trial_counts(vb, oracle, path):
         assert sums[w].final_cost == pytest.approx(fc, rel=COST_RTOL)
         trials.append(sums[w].trials)
     assert len(set(trials)) > 1
+    # the straggler trials run on a compacted grid (only the tiles of the windows still active): a window
+    # solved alone, where nothing is compacted, must come out bit-identical
+    poses, pts = ba.poses(), ba.points()
+    for w, p in enumerate(probs):
+        alone = vb.BundleAdjuster(len(p["points_init"]), len(p["poses_init"]), len(p["edge_pose"]), lm_tau=1e-8, path=path)
+        alone.set_problem(p["poses_init"], p["points_init"], p["edge_pose"], p["edge_point"], p["edge_uv"])
+        sa = alone.Optimize(8)
+        assert sa.final_cost == sums[w].final_cost and sa.trials == sums[w].trials
+        assert np.array_equal(alone.poses(), poses[b["pose_off"][w]:b["pose_off"][w + 1]])
+        assert np.array_equal(alone.points(), pts[b["point_off"][w]:b["point_off"][w + 1]])
 
 
 def test_zero_noise_round_trip_full_size_batch(vb):

@@ -118,6 +118,9 @@ struct DevProblem {
     const int64_t* prob_part_off;  // [B+1] offset (doubles) of the problem's tile partials
     double* tile_part;             // per tile: [nblocks of its problem][kItemPart]
     double* tile_sums;             // [n_tiles][2]  {cost, scale} of the tile
+    // straggler trials: CTA b works on tile tile_map[b] (the tiles of the problems still active), null = identity
+    const int32_t* tile_map;
+    int32_t n_map_tiles;
     // state
     double* pts[2];
     double* pose[2];
@@ -175,6 +178,7 @@ int launch_win_linearize_schur(const DevProblem& P, int init_pass, double lambda
 int launch_win_finalize(const DevProblem& P, int init_pass, double lambda_override, cudaStream_t st);
 int launch_win_update(const DevProblem& P, cudaStream_t st);
 int launch_win_prob_sums(const DevProblem& P, int even_if_inactive, cudaStream_t st);
+int launch_win_active_tiles(const DevProblem& P, int32_t* map, cudaStream_t st);
 
 } // namespace visoba
 #endif

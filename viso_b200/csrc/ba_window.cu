@@ -73,9 +73,15 @@ __device__ __forceinline__ double cta_sum(double v, double* red, int tid)
     return s;
 }
 
-__device__ __forceinline__ WinTile load_tile(const DevProblem& P)
+// the tile of this CTA: blockIdx.x, or its entry in the compacted list of a straggler trial
+__device__ __forceinline__ int tile_index(const DevProblem& P)
 {
-    const int4* src = reinterpret_cast<const int4*>(P.tiles + blockIdx.x);
+    return P.tile_map ? __ldg(P.tile_map + blockIdx.x) : (int)blockIdx.x;
+}
+
+__device__ __forceinline__ WinTile load_tile(const DevProblem& P, int tile)
+{
+    const int4* src = reinterpret_cast<const int4*>(P.tiles + tile);
     const int4 a = __ldg(src), b = __ldg(src + 1), c = __ldg(src + 2), d = __ldg(src + 3);
     WinTile t;
     t.prob = a.x, t.p0 = a.y, t.np = a.z, t.o0 = a.w;
@@ -122,7 +128,8 @@ __global__ void __launch_bounds__(kWinThreads, kWinLsCtas) k_win_linearize_schur
 #define REC(c, o) rec[(c) * kWinObsCap + (o)]
 
     const int tid = threadIdx.x;
-    const WinTile t = load_tile(P);
+    const int tile = tile_index(P);
+    const WinTile t = load_tile(P, tile);
 
     // ---- A0: everything the tile needs from HBM, issued at once, and what does not depend on the LM state
     // before the state is read.  Thread <-> slot: the observations of the tile in keyframe-major order, so that
@@ -195,8 +202,8 @@ __global__ void __launch_bounds__(kWinThreads, kWinLsCtas) k_win_linearize_schur
     if (init_pass) { // cost of the start state: fixed-tree sum of the tile
         const double c = cta_sum(cost, s_red, tid);
         if (tid == 0) {
-            P.tile_sums[2 * (size_t)blockIdx.x] = c;
-            P.tile_sums[2 * (size_t)blockIdx.x + 1] = 0.0;
+            P.tile_sums[2 * (size_t)tile] = c;
+            P.tile_sums[2 * (size_t)tile + 1] = 0.0;
         }
     }
     __syncthreads();
@@ -448,7 +455,8 @@ __global__ void __launch_bounds__(kWinThreads, 5) k_win_update(DevProblem P)
     double* const s_red = reinterpret_cast<double*>(sm + kUsRed);
 
     const int tid = threadIdx.x;
-    const WinTile t = load_tile(P);
+    const int tile = tile_index(P);
+    const WinTile t = load_tile(P, tile);
     // everything that does not depend on the LM state goes out before the state is read (one dependent miss less)
     unsigned int meta[kObsPerThread];
     float2 uv[kObsPerThread];
@@ -585,8 +593,8 @@ __global__ void __launch_bounds__(kWinThreads, 5) k_win_update(DevProblem P)
     const double c = cta_sum(cost, s_red, tid);
     const double sc = cta_sum(scale, s_red + kWarps, tid);
     if (tid == 0) {
-        P.tile_sums[2 * (size_t)blockIdx.x] = c;
-        P.tile_sums[2 * (size_t)blockIdx.x + 1] = sc;
+        P.tile_sums[2 * (size_t)tile] = c;
+        P.tile_sums[2 * (size_t)tile + 1] = sc;
     }
 }
 
@@ -624,7 +632,7 @@ static bool win_configure()
 int launch_win_linearize_schur(const DevProblem& P, int init_pass, double lambda_override, cudaStream_t st)
 {
     if (P.n_tiles <= 0 || !win_configure()) return 0;
-    k_win_linearize_schur<<<P.n_tiles, kWinThreads, kLsBytes, st>>>(P, init_pass, lambda_override);
+    k_win_linearize_schur<<<P.tile_map ? P.n_map_tiles : P.n_tiles, kWinThreads, kLsBytes, st>>>(P, init_pass, lambda_override);
     return 1;
 }
 
@@ -637,7 +645,43 @@ int launch_win_finalize(const DevProblem& P, int init_pass, double lambda_overri
 int launch_win_update(const DevProblem& P, cudaStream_t st)
 {
     if (P.n_tiles <= 0 || !win_configure()) return 0;
-    k_win_update<<<P.n_tiles, kWinThreads, kUsBytes, st>>>(P);
+    k_win_update<<<P.tile_map ? P.n_map_tiles : P.n_tiles, kWinThreads, kUsBytes, st>>>(P);
+    return 1;
+}
+
+// the tiles of the problems still active, in tile order, and their count at P.n_active[1]: one CTA, a running
+// prefix over the problems.  The host sizes the straggler trials' grids with that count.
+__global__ void __launch_bounds__(1024) k_win_active_tiles(DevProblem P, int32_t* map)
+{
+    __shared__ int warp_tot[32];
+    __shared__ int base;
+    if (threadIdx.x == 0) base = 0;
+    __syncthreads();
+    for (int b0 = 0; b0 < P.n_problems; b0 += blockDim.x) {
+        const int b = b0 + threadIdx.x;
+        int t0 = 0, cnt = 0;
+        if (b < P.n_problems && P.lm[b].active) t0 = P.prob_tile_ptr[b], cnt = P.prob_tile_ptr[b + 1] - t0;
+        int inc = cnt; // inclusive prefix inside the warp
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            const int v = __shfl_up_sync(0xffffffffu, inc, off);
+            if ((threadIdx.x & 31) >= off) inc += v;
+        }
+        if ((threadIdx.x & 31) == 31) warp_tot[threadIdx.x >> 5] = inc;
+        __syncthreads();
+        int before = base;
+        for (int w = 0; w < (int)(threadIdx.x >> 5); ++w) before += warp_tot[w];
+        for (int k = 0; k < cnt; ++k) map[before + inc - cnt + k] = t0 + k;
+        __syncthreads();
+        if (threadIdx.x == blockDim.x - 1) base = before + inc;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) P.n_active[1] = base;
+}
+
+int launch_win_active_tiles(const DevProblem& P, int32_t* map, cudaStream_t st)
+{
+    k_win_active_tiles<<<1, 1024, 0, st>>>(P, map);
     return 1;
 }
 

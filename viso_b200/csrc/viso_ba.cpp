@@ -212,6 +212,7 @@ struct viso_ba {
     bool window = false; // tile fast path (ba_window.cu) instead of the pair-list kernels
     int max_n = 0; // largest reduced system over the problems
     double *d_pose_init = nullptr, *d_pts_init = nullptr, *d_pose_out = nullptr, *d_pts_out = nullptr;
+    int32_t* d_tile_map = nullptr; // window path: tiles of the problems still active (straggler trials)
     double* d_allreduce = nullptr; // S_blk | bs   (contiguous)
     size_t allreduce_count = 0;
     // pinned host mirrors
@@ -1109,6 +1110,7 @@ struct DevPtrs { // everything carved out of the arena, in one place so that the
     int32_t *prob_tile_ptr, *prob_pt0;
     int64_t* prob_part_off;
     double *tile_part, *tile_sums;
+    int32_t* tile_map;
     double *pts[2], *pose[2], *cam_rt[2], *pose_init, *pts_init, *pose_out, *pts_out;
     LmState* lm;
     IterStat* iter_stats;
@@ -1156,6 +1158,7 @@ void carve(Arena& A, DevPtrs& d, int64_t Nc, int64_t Np, int64_t Ne, int64_t B, 
     d.prob_pt0 = A.take<int32_t>(BW);
     d.tile_part = A.take<double>((size_t)b.part_max);
     d.tile_sums = A.take<double>((size_t)b.tiles_max * 2);
+    d.tile_map = A.take<int32_t>((size_t)b.tiles_max);
     for (int k = 0; k < 2; ++k) {
         d.pts[k] = A.take<double>((size_t)Np * 3);
         d.pose[k] = A.take<double>((size_t)Nc * 7);
@@ -1180,7 +1183,7 @@ void carve(Arena& A, DevPtrs& d, int64_t Nc, int64_t Np, int64_t Ne, int64_t B, 
     d.dp = A.take<double>((size_t)Nc * 6);
     d.chunk_part = A.take<double>(b.chunks.size() / 4 * 2);
     d.maxdiag_bits = A.take<unsigned long long>((size_t)B);
-    d.n_active = A.take<int32_t>(1);
+    d.n_active = A.take<int32_t>(2); // [1]: tiles of the active problems (k_win_active_tiles)
     if (large) {
         const size_t n = (size_t)b.max_n;
         d.LA = A.take<double>((n + 1) * (size_t)ldL);
@@ -1404,6 +1407,7 @@ extern "C" int32_t viso_ba_upload(viso_ba* h)
         P.tiles = d.tiles, P.pt_mask = d.pt_mask; // n_tiles, n_pairs, win_pairs: set by build_window_on_device
         P.win_meta = d.win_meta, P.win_blkptr = d.win_blkptr, P.win_uv = d.win_uv, P.win_slot = d.win_slot;
         P.prob_tile_ptr = d.prob_tile_ptr, P.prob_part_off = d.prob_part_off, P.tile_part = d.tile_part, P.tile_sums = d.tile_sums;
+        P.tile_map = nullptr, P.n_map_tiles = 0, h->d_tile_map = d.tile_map;
         h->d_pose_init = d.pose_init, h->d_pts_init = d.pts_init, h->d_pose_out = d.pose_out, h->d_pts_out = d.pts_out;
         h->d_allreduce = d.S_blk;
         h->allreduce_count = (size_t)b.n_blocks * 36 + (size_t)Nc * 6;
@@ -1514,7 +1518,8 @@ int32_t enqueue_trial(viso_ba* h)
 
 int32_t run_trials(viso_ba* h, int count)
 {
-    const bool graph_ok = h->cfg.use_cuda_graph && !h->timing && h->n_ranks == 1;
+    // a compacted grid changes from batch to batch: straggler trials are launched directly
+    const bool graph_ok = h->cfg.use_cuda_graph && !h->timing && h->n_ranks == 1 && !h->P.tile_map;
     if (!graph_ok) {
         for (int i = 0; i < count; ++i) {
             int32_t rc = enqueue_trial(h);
@@ -1551,6 +1556,7 @@ int32_t run_lm(viso_ba* h, int iterations, viso_ba_summary* summary)
     int32_t rc;
     if (iterations > kMaxIterStats) return fail(h, VISO_BA_ERR_ARG, "at most %d iterations per call", kMaxIterStats);
     if (iterations < 0) iterations = 0;
+    h->P.tile_map = nullptr;
     CU(cudaEventRecord(h->ev0, st));
     run_k(h, "state_init", [&] { return launch_state_init(P, iterations > 0 ? iterations : 1, h->cfg.lm_max_trials, h->cfg.lm_lambda_init, st); });
     // first linearisation: cost of the start state, lambda_0 = tau * max diag(H)   (g2o computeLambdaInit)
@@ -1571,13 +1577,19 @@ int32_t run_lm(viso_ba* h, int iterations, viso_ba_summary* summary)
     int batch = iterations;
     while (iterations > 0 && done < max_rounds) {
         batch = (int)std::min<long long>(batch, max_rounds - done);
-        if ((rc = run_trials(h, batch))) return rc;
+        rc = run_trials(h, batch);
+        h->P.tile_map = nullptr;
+        if (rc) return rc;
         done += batch;
-        CU(cudaMemcpyAsync(n_active, P.n_active, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+        // window path: the tiles of the problems still active, so that the straggler trials launch only those
+        if (h->window) run_k(h, "active_tiles", [&] { return launch_win_active_tiles(P, h->d_tile_map, st); });
+        CU(cudaMemcpyAsync(n_active, P.n_active, 2 * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
         CU(cudaStreamSynchronize(st));
         if (*n_active <= 0) break;
         batch = std::max(1, std::min(iterations, 4)); // stragglers: a few rejected trials to make up
+        if (h->window && n_active[1] > 0 && n_active[1] < P.n_tiles) h->P.tile_map = h->d_tile_map, h->P.n_map_tiles = n_active[1];
     }
+    h->P.tile_map = nullptr;
     CU(cudaEventRecord(h->ev1, st));
     LmState* lm = reinterpret_cast<LmState*>(static_cast<char*>(h->pin) + 64);
     CU(cudaMemcpyAsync(lm, P.lm, sizeof(LmState) * (size_t)P.n_problems, cudaMemcpyDeviceToHost, st));
