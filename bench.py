@@ -451,31 +451,24 @@ def run_b200(args):
     e2e_serial_ms = 1e3 * e2e_s / max(1, e2e_steps)
     e2e_mode = "one handle, steps back to back"
     if e2e_steps and not sharded:
-        # The same steps as a stream of batches through TWO handles on two host threads (ctypes drops the GIL in
-        # the C ABI; one handle = one stream, include/viso_ba.h): a step's H2D / structure build / D2H overlap the
-        # other handle's LM loop.  Every step still uploads its own inputs and reads its own result.
+        # The same steps as a stream of batches through TWO handles on two host threads (viso_b200/stream.py:
+        # ctypes drops the GIL in the C ABI; one handle = one stream, include/viso_ba.h): a step's H2D / structure
+        # build / D2H overlap the other handle's LM loop, the LM loops take turns.  Every step still uploads its
+        # own inputs and reads its own result.
         try:
             ba2 = make_adjuster(vb, host, huber, local)
-            handles, losses = (ba, ba2), [None, None]
-
-            def worker(j, n):
-                for _ in range(n):
-                    set_problem(handles[j], host)
-                    losses[j] = handles[j].Optimize(args.lm_iters).final_cost
-            for j in (0, 1):  # warm the second handle's arena
-                worker(j, 1)
+            losses = []
+            vb.optimize_stream((ba, ba2), [host, host], args.lm_iters)  # warm the second handle's arena
             barrier()
             t0 = time.perf_counter()
-            th = [threading.Thread(target=worker, args=(j, (e2e_steps + 1 - j) // 2)) for j in (0, 1)]
-            for t in th:
-                t.start()
-            for t in th:
-                t.join()
+            vb.optimize_stream((ba, ba2), [host] * e2e_steps, args.lm_iters,
+                               consume=lambda i, h, s: losses.append(s.final_cost))
             barrier()
             piped_s = max_over_ranks(time.perf_counter() - t0)
-            if losses[0] == loss and (losses[1] is None or losses[1] == loss) and piped_s < e2e_s:
+            if len(losses) == e2e_steps and all(x == loss for x in losses) and piped_s < e2e_s:
                 e2e_s = piped_s
-                e2e_mode = "two handles on two host threads: a step's transfers overlap the other step's LM loop"
+                e2e_mode = ("two handles on two host threads (viso_b200.optimize_stream): a step's transfers and "
+                            "structure build overlap the other step's LM loop")
             ba2.close()
         except Exception as e:  # the one-handle number stands
             e2e_mode += " (two-handle pipeline failed: %s)" % e

@@ -165,6 +165,12 @@ int32_t viso_ba_optimize(viso_ba* h, int32_t iterations, viso_ba_iter_stats* sta
 int32_t viso_ba_reset_state(viso_ba* h);
 /* device-only LM loop: no host<->device copies of poses/points (bench `value` leg) */
 int32_t viso_ba_optimize_resident(viso_ba* h, int32_t iterations, viso_ba_summary* summary);
+/*
+ * device state -> the handle's host copy: the read-back viso_ba_optimize ends with, as a call of its own.
+ * upload / optimize_resident / download are viso_ba_optimize in three steps, for a caller that feeds a stream of
+ * problems through two handles and wants only the LM loops to take turns on the GPU (viso_b200/stream.py).
+ */
+int32_t viso_ba_download(viso_ba* h);
 
 /* read-back the reference never had */
 int64_t viso_ba_num_points(const viso_ba* h);

@@ -410,3 +410,31 @@ def test_window_and_general_paths_agree(vb):
     assert sa.trials == sb.trials
     assert sa.final_cost == pytest.approx(sb.final_cost, rel=1e-11)
     assert np.abs(a.poses() - b.poses()).max() < 1e-10 and np.abs(a.points() - b.points()).max() < 1e-9
+
+
+def test_stream_of_batches_through_two_handles_is_bit_identical(vb):
+    """viso_b200.optimize_stream (upload / optimize_resident / download, LM loops taking turns) against
+    Optimize on one handle, batch by batch: same bits, whatever the interleaving of the two threads"""
+    batches = []
+    for k in range(5):
+        probs = [vb.synth_config(5, 10 * k + w, n_points=260 + 30 * w, target_edges=2000 + 250 * w) for w in range(4)]
+        batches.append(vb.batch_problems(probs))
+    cap = [max(len(b[key]) for b in batches) for key in ("points_init", "poses_init", "edge_pose")]
+    want = []
+    one = vb.BundleAdjuster(*cap)
+    for b in batches:
+        one.set_problem_batched(b["pose_off"], b["point_off"], b["edge_off"], b["poses_init"], b["points_init"],
+                                b["edge_pose"], b["edge_point"], b["edge_uv"])
+        s = one.Optimize(6)
+        want.append((s.final_cost, s.trials, one.poses().copy(), one.points().copy()))
+    got = {}
+    handles = (vb.BundleAdjuster(*cap), vb.BundleAdjuster(*cap))
+    out = vb.optimize_stream(handles, batches, 6, consume=lambda i, h, s: got.__setitem__(i, (h.poses().copy(), h.points().copy())))
+    assert len(out) == len(batches) and sorted(got) == list(range(len(batches)))
+    for i, (fc, tr, po, pt) in enumerate(want):
+        assert out[i].final_cost == fc and out[i].trials == tr
+        assert np.array_equal(got[i][0], po) and np.array_equal(got[i][1], pt)
+    # download needs something on the device
+    fresh = vb.BundleAdjuster(8, 2, 8)
+    with pytest.raises(vb.VisoBaError):
+        fresh.download()

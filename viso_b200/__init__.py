@@ -7,3 +7,4 @@ from .api import (  # noqa: F401
     BundleAdjuster, Config, IterStats, KernelTime, Summary, SynthSpec, VisoBaError, LIB_PATH, SYMBOLS,
     batch_problems, default_config, load_library, nccl_unique_id, shard_point_ranges, synth_config, synth_preset, synth_problem,
 )
+from .stream import optimize_stream  # noqa: F401,E402

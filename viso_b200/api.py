@@ -102,6 +102,7 @@ SYMBOLS = {
     "viso_ba_optimize": (C.c_int32, [_P, C.c_int32, C.POINTER(IterStats), C.POINTER(Summary)]),
     "viso_ba_reset_state": (C.c_int32, [_P]),
     "viso_ba_optimize_resident": (C.c_int32, [_P, C.c_int32, C.POINTER(Summary)]),
+    "viso_ba_download": (C.c_int32, [_P]),
     "viso_ba_num_points": (C.c_int64, [_P]),
     "viso_ba_num_poses": (C.c_int64, [_P]),
     "viso_ba_num_edges": (C.c_int64, [_P]),
@@ -283,6 +284,10 @@ class BundleAdjuster:
         s = Summary()
         self._check(self._lib.viso_ba_optimize_resident(self._h, int(iterations), C.byref(s)))
         return s
+
+    def download(self):
+        """device state -> host copy (what Optimize ends with); pairs with optimize_resident"""
+        self._check(self._lib.viso_ba_download(self._h))
 
     @property
     def num_poses(self):

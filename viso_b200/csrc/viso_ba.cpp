@@ -1654,6 +1654,15 @@ extern "C" int32_t viso_ba_optimize_resident(viso_ba* h, int32_t iterations, vis
     return run_lm(h, iterations, summary);
 }
 
+extern "C" int32_t viso_ba_download(viso_ba* h)
+{
+    if (!h) return VISO_BA_ERR_ARG;
+    if (!h->uploaded) return fail(h, VISO_BA_ERR_STATE, "nothing on the device to read back");
+    int32_t rc = ensure_cuda(h);
+    if (rc) return rc;
+    return read_back(h);
+}
+
 extern "C" int32_t viso_ba_optimize(viso_ba* h, int32_t iterations, viso_ba_iter_stats* stats, viso_ba_summary* summary)
 {
     if (!h) return VISO_BA_ERR_ARG;
