@@ -284,8 +284,13 @@ def roofline(ktimes, trials_per_problem, sizes, nprob=1):
     if ps is None:  # a solve kernel dominates: it has no HBM-bound share worth a roofline; use pass L anyway
         ps = "L"
     members = [k for k in ktimes if PASS_OF.get(k) == ps]
-    # one launch of every member per trial (plus the init linearisation): time per launch of the pass
-    t_us = sum(per_kernel[k]["avg_us"] for k in members)
+    # Units one launch processes: a launch of the pass over EVERY problem moves A[ps] algorithmic bytes.  In a
+    # batch, the straggler launches after the first batch of trials cover only the few problems still active,
+    # so the pass's time is divided by the number of full-launch equivalents it actually processed
+    # (problem-trials / problems, plus the init linearisation for pass L) -- not by the launch count, which
+    # would credit the near-empty straggler launches with a full launch's bytes.  One problem: the same thing.
+    n_equiv = trials_per_problem + (1.0 if ps == "L" else 0.0)
+    t_us = 1e3 * sum(ktimes[k][1] for k in members) / max(n_equiv, 1e-9)
     achieved = A[ps] / (t_us * 1e-6) / 1e9
     # measured DRAM traffic of the same kernels (ncu --set full, one launch over `windows` windows of the
     # same shape): scaled to this run's window count, per launch like `achieved`
@@ -306,7 +311,8 @@ def roofline(ktimes, trials_per_problem, sizes, nprob=1):
     fp64 = None
     if top in FP64_SLOTS_PER_OBS:
         pk, src = fp64_peak()
-        ach = FP64_SLOTS_PER_OBS[top] * No / (per_kernel[top]["avg_us"] * 1e-6) / 1e12
+        n_top = trials_per_problem + (1.0 if PASS_OF.get(top) == "L" else 0.0)  # the init launch counted as a full one
+        ach = FP64_SLOTS_PER_OBS[top] * No * n_top / (ktimes[top][1] * 1e-3) / 1e12
         fp64 = {"kernel": top, "slots_per_observation": FP64_SLOTS_PER_OBS[top], "achieved": ach, "peak": pk,
                 "unit": "T FP64 instructions/s (an FMA is one)", "frac": ach / pk, "peak_source": src,
                 "note": "the binding roof of this kernel: HBM traffic is ~7% of peak because the pair products are FP64-issue-bound"}
@@ -314,6 +320,7 @@ def roofline(ktimes, trials_per_problem, sizes, nprob=1):
         "fp64": fp64,
         "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
         "kernel": top, "pass": ps, "pass_kernels": members, "pass_us_per_launch": t_us,
+        "full_launch_equivalents": n_equiv,
         "algorithmic_bytes_per_launch": A[ps], "algorithmic_bytes_per_lm_iteration": A_iter,
         "peak_source": peak_src, "kernels": per_kernel,
     }
