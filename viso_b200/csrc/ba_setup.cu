@@ -38,7 +38,9 @@ __device__ __forceinline__ int find_segment(const int64_t* __restrict__ off, int
 }
 
 // ---- 1. validate + key ----
-__global__ void k_setup_keys(SetupIn in, unsigned long long* __restrict__ keys, unsigned int* __restrict__ vals, int* __restrict__ err)
+// key = point << cam_bits | pose, cam_bits = the bits n_cams needs: the radix sort walks only the bits in use
+// (C5: 35 bits = 5 passes of 8 instead of the 7 that point << 32 | pose costs)
+__global__ void k_setup_keys(SetupIn in, int cam_bits, unsigned long long* __restrict__ keys, unsigned int* __restrict__ vals, int* __restrict__ err)
 {
     const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= in.n_edges) return;
@@ -60,27 +62,27 @@ __global__ void k_setup_keys(SetupIn in, unsigned long long* __restrict__ keys, 
         atomicMin(reinterpret_cast<unsigned long long*>(err + 2), (unsigned long long)e);
         pose = 0, point = 0;
     }
-    keys[e] = ((unsigned long long)(unsigned)point << 32) | (unsigned)pose;
+    keys[e] = ((unsigned long long)(unsigned)point << cam_bits) | (unsigned)pose;
     vals[e] = (unsigned int)e;
 }
 
 // ---- 3. gather + CSR ----
-__global__ void k_setup_gather(SetupIn in, const unsigned long long* __restrict__ keys, const unsigned int* __restrict__ vals,
+__global__ void k_setup_gather(SetupIn in, int cam_bits, const unsigned long long* __restrict__ keys, const unsigned int* __restrict__ vals,
     int32_t* __restrict__ obs_cam, float2* __restrict__ obs_uv, int* __restrict__ err)
 {
     const int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= in.n_edges) return;
     const unsigned long long k = keys[s];
-    obs_cam[s] = (int32_t)(k & 0xffffffffull);
+    obs_cam[s] = (int32_t)(k & ((1ull << cam_bits) - 1ull));
     obs_uv[s] = in.e_uv[vals[s]];
     if (s > 0 && keys[s - 1] == k) err[1] = 1; // duplicate (point, pose) edge: the general path handles it
 }
 
-__global__ void k_setup_ptptr(int64_t n_edges, int32_t n_points, const unsigned long long* __restrict__ keys, int32_t* __restrict__ pt_ptr)
+__global__ void k_setup_ptptr(int64_t n_edges, int32_t n_points, int cam_bits, const unsigned long long* __restrict__ keys, int32_t* __restrict__ pt_ptr)
 {
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p > n_points) return;
-    const unsigned long long want = (unsigned long long)(unsigned)p << 32;
+    const unsigned long long want = (unsigned long long)(unsigned)p << cam_bits;
     int64_t lo = 0, hi = n_edges; // first s with keys[s] >= want
     while (lo < hi) {
         const int64_t mid = (lo + hi) >> 1;
@@ -311,27 +313,36 @@ size_t setup_sort_temp_bytes(int64_t n_edges)
     return std::max(bytes, scan) + 256;
 }
 
+// bits of the pose index inside a sort key
+static int key_cam_bits(const SetupIn& in)
+{
+    int bits = 1;
+    while (bits < 31 && ((int64_t)1 << bits) < (int64_t)in.n_cams) ++bits;
+    return bits;
+}
+
 int setup_stage0(const SetupIn& in, const SetupWork& w, cudaStream_t st)
 {
     cudaMemsetAsync(w.err, 0, 4 * sizeof(int), st);
     cudaMemsetAsync(w.err + 2, 0xff, 2 * sizeof(int), st); // first offending edge: atomicMin target
     if (in.n_edges <= 0) return 0;
-    k_setup_keys<<<cdiv(in.n_edges, 256), 256, 0, st>>>(in, w.keys, w.vals, w.err);
+    k_setup_keys<<<cdiv(in.n_edges, 256), 256, 0, st>>>(in, key_cam_bits(in), w.keys, w.vals, w.err);
     return 1;
 }
 
 int setup_stage1(const SetupIn& in, const SetupWork& w, const SetupOut& o, cudaStream_t st)
 {
     int launches = 0;
+    const int cam_bits = key_cam_bits(in);
     if (in.n_edges > 0) {
-        int end_bit = 33;
-        while (end_bit < 64 && ((int64_t)1 << (end_bit - 32)) < (int64_t)in.n_points) ++end_bit;
+        int end_bit = cam_bits + 1;
+        while (end_bit < 64 && ((int64_t)1 << (end_bit - cam_bits)) < (int64_t)in.n_points) ++end_bit;
         size_t bytes = w.temp_bytes;
         cub::DeviceRadixSort::SortPairs(w.temp, bytes, w.keys, w.keys_sorted, w.vals, w.vals_sorted, in.n_edges, 0, end_bit, st);
-        k_setup_gather<<<cdiv(in.n_edges, 256), 256, 0, st>>>(in, w.keys_sorted, w.vals_sorted, o.obs_cam, o.obs_uv, w.err);
+        k_setup_gather<<<cdiv(in.n_edges, 256), 256, 0, st>>>(in, cam_bits, w.keys_sorted, w.vals_sorted, o.obs_cam, o.obs_uv, w.err);
         launches += 2;
     }
-    k_setup_ptptr<<<cdiv((int64_t)in.n_points + 1, 256), 256, 0, st>>>(in.n_edges, in.n_points, w.keys_sorted, o.pt_ptr);
+    k_setup_ptptr<<<cdiv((int64_t)in.n_points + 1, 256), 256, 0, st>>>(in.n_edges, in.n_points, cam_bits, w.keys_sorted, o.pt_ptr);
     k_setup_tiles_count<<<cdiv(in.n_problems, 128), 128, 0, st>>>(in, o.pt_ptr, w.prob_ntiles);
     k_setup_prob_offsets<<<1, 32, 0, st>>>(in, w.prob_ntiles, in.prob_nfree, o.prob_tile_ptr, o.prob_part_off, w.prob_blkptr_off, w.totals);
     k_setup_fill_pt_prob<<<cdiv(in.n_points, 256), 256, 0, st>>>(in.n_points, in.n_problems, in.prob_pt0, o.pt_prob);
