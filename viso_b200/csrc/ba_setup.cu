@@ -127,12 +127,30 @@ __device__ __forceinline__ int cut_tiles(const int32_t* __restrict__ pt_ptr, int
     return n;
 }
 
-__global__ void k_setup_tiles_count(SetupIn in, const int32_t* __restrict__ pt_ptr, int32_t* __restrict__ prob_ntiles)
+// One CTA per problem: the problem's slice of pt_ptr is staged in shared memory (a window: 2001 entries), so the
+// probes of the sequential cut cost a shared-memory round trip instead of a dependent L2 miss each; larger
+// problems read pt_ptr in place.
+constexpr int kCutStage = 4096;
+constexpr int kCutThreads = 128;
+
+__device__ __forceinline__ const int32_t* stage_pt_ptr(const int32_t* __restrict__ pt_ptr, int q0, int hi, int32_t* s_buf)
 {
-    const int b = blockIdx.x * blockDim.x + threadIdx.x;
-    if (b >= in.n_problems) return;
+    const bool fits = hi - q0 + 1 <= kCutStage;
+    if (fits)
+        for (int i = threadIdx.x; i <= hi - q0; i += kCutThreads) s_buf[i] = pt_ptr[q0 + i];
+    __syncthreads();
+    return fits ? s_buf - q0 : pt_ptr;
+}
+
+__global__ void __launch_bounds__(kCutThreads) k_setup_tiles_count(SetupIn in, const int32_t* __restrict__ pt_ptr, int32_t* __restrict__ prob_ntiles)
+{
+    __shared__ int32_t s_buf[kCutStage];
+    const int b = blockIdx.x;
+    const int q0 = in.prob_pt0[b], hi = in.prob_pt0[b + 1];
+    const int32_t* src = stage_pt_ptr(pt_ptr, q0, hi, s_buf);
+    if (threadIdx.x) return;
     WinTile proto = {};
-    prob_ntiles[b] = cut_tiles<false>(pt_ptr, in.prob_pt0[b], in.prob_pt0[b + 1], proto, nullptr, 0, 0);
+    prob_ntiles[b] = cut_tiles<false>(src, q0, hi, proto, nullptr, 0, 0);
 }
 
 // one thread: prefix sums over the problems (B is small next to the edge count)
@@ -153,17 +171,20 @@ __global__ void k_setup_prob_offsets(SetupIn in, const int32_t* __restrict__ pro
     totals[0] = t, totals[1] = part, totals[2] = bp;
 }
 
-__global__ void k_setup_tiles_fill(SetupIn in, const int32_t* __restrict__ pt_ptr, const int32_t* __restrict__ prob_nfree,
+__global__ void __launch_bounds__(kCutThreads) k_setup_tiles_fill(SetupIn in, const int32_t* __restrict__ pt_ptr, const int32_t* __restrict__ prob_nfree,
     const int32_t* __restrict__ prob_tile_ptr, const int64_t* __restrict__ prob_part_off, const int64_t* __restrict__ prob_blkptr_off,
     WinTile* __restrict__ tiles)
 {
-    const int b = blockIdx.x * blockDim.x + threadIdx.x;
-    if (b >= in.n_problems) return;
+    __shared__ int32_t s_buf[kCutStage];
+    const int b = blockIdx.x;
+    const int q0 = in.prob_pt0[b], hi = in.prob_pt0[b + 1];
+    const int32_t* src = stage_pt_ptr(pt_ptr, q0, hi, s_buf);
+    if (threadIdx.x) return;
     const int64_t nblk = (int64_t)prob_nfree[b] * (prob_nfree[b] + 1) / 2;
     WinTile proto = {};
     proto.prob = b, proto.cam0 = in.prob_cam0[b], proto.ncam = in.prob_cam0[b + 1] - in.prob_cam0[b], proto.nf = prob_nfree[b];
     proto.part_off = prob_part_off[b], proto.blkptr_off = prob_blkptr_off[b];
-    cut_tiles<true>(pt_ptr, in.prob_pt0[b], in.prob_pt0[b + 1], proto, tiles + prob_tile_ptr[b], nblk * kItemPart, nblk + 1);
+    cut_tiles<true>(src, q0, hi, proto, tiles + prob_tile_ptr[b], nblk * kItemPart, nblk + 1);
 }
 
 // ---- 5a. per tile: keyframe-major slots and pair counts ----
@@ -343,7 +364,7 @@ int setup_stage1(const SetupIn& in, const SetupWork& w, const SetupOut& o, cudaS
         launches += 2;
     }
     k_setup_ptptr<<<cdiv((int64_t)in.n_points + 1, 256), 256, 0, st>>>(in.n_edges, in.n_points, cam_bits, w.keys_sorted, o.pt_ptr);
-    k_setup_tiles_count<<<cdiv(in.n_problems, 128), 128, 0, st>>>(in, o.pt_ptr, w.prob_ntiles);
+    k_setup_tiles_count<<<in.n_problems, kCutThreads, 0, st>>>(in, o.pt_ptr, w.prob_ntiles);
     k_setup_prob_offsets<<<1, 32, 0, st>>>(in, w.prob_ntiles, in.prob_nfree, o.prob_tile_ptr, o.prob_part_off, w.prob_blkptr_off, w.totals);
     k_setup_fill_pt_prob<<<cdiv(in.n_points, 256), 256, 0, st>>>(in.n_points, in.n_problems, in.prob_pt0, o.pt_prob);
     return launches + 4;
@@ -353,7 +374,7 @@ int setup_stage2(const SetupIn& in, const SetupWork& w, const SetupOut& o, int32
 {
     if (n_tiles <= 0) return 0;
     cudaMemsetAsync(w.tile_pairs, 0, sizeof(int64_t) * ((size_t)n_tiles + 1), st);
-    k_setup_tiles_fill<<<cdiv(in.n_problems, 128), 128, 0, st>>>(in, o.pt_ptr, in.prob_nfree, o.prob_tile_ptr, o.prob_part_off, w.prob_blkptr_off, o.tiles);
+    k_setup_tiles_fill<<<in.n_problems, kCutThreads, 0, st>>>(in, o.pt_ptr, in.prob_nfree, o.prob_tile_ptr, o.prob_part_off, w.prob_blkptr_off, o.tiles);
     k_setup_tile_slots<<<n_tiles, kSetupThreads, 0, st>>>(o.tiles, o.pt_ptr, o.obs_cam, o.obs_uv, in.cam_free, o.pt_mask, o.win_meta, o.win_uv,
         o.win_slot, o.win_blkptr, w.tile_pairs);
     size_t bytes = w.temp_bytes;
