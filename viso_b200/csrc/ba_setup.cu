@@ -199,6 +199,8 @@ __global__ void __launch_bounds__(kSetupThreads) k_setup_tile_slots(const WinTil
     __shared__ int s_start[kWinMaxCams + 1];
     __shared__ signed char s_free[kWinMaxCams];
     __shared__ unsigned int s_cnt[kSmallMaxN / 6 * (kSmallMaxN / 6 + 1) / 2 + 1];
+    __shared__ unsigned int s_mask[kWinPtCap];
+    __shared__ unsigned char s_camof[kWinMaxCams];
     const WinTile t = tiles[blockIdx.x];
     const int tid = threadIdx.x;
     const int nblk = t.nf * (t.nf + 1) / 2;
@@ -229,14 +231,23 @@ __global__ void __launch_bounds__(kSetupThreads) k_setup_tile_slots(const WinTil
             win_meta[t.o0 + sl] = (unsigned)c | ((unsigned)p << 8);
             win_uv[t.o0 + sl] = obs_uv[t.o0 + o];
             win_slot[t.o0 + o] = (unsigned short)sl;
-            const int fa = s_free[c];
-            if (fa < 0) continue;
-            for (int o2 = a0; o2 <= o; ++o2) { // sorted by pose: free index of o2 <= fa
-                const int fc = s_free[s_cam[o2]];
-                if (fc >= 0) atomicAdd(&s_cnt[fa * (fa + 1) / 2 + fc + 1], 1u);
-            }
         }
         pt_mask[t.p0 + p] = m;
+        s_mask[p] = m;
+    }
+    if (tid < t.ncam && s_free[tid] >= 0) s_camof[s_free[tid]] = (unsigned char)tid;
+    __syncthreads();
+    // pairs of S block (fa, fc) in this tile = points that both keyframes see (no duplicate edges on this path):
+    // one thread per block counts them from the visibility masks
+    for (int k = tid; k < nblk; k += kSetupThreads) {
+        int fa = (int)((sqrtf(8.0f * (float)k + 1.0f) - 1.0f) * 0.5f);
+        while ((fa + 1) * (fa + 2) / 2 <= k) ++fa;
+        while (fa * (fa + 1) / 2 > k) --fa;
+        const int fc = k - fa * (fa + 1) / 2;
+        const unsigned int both = (1u << s_camof[fa]) | (1u << s_camof[fc]);
+        unsigned int n = 0u;
+        for (int p = 0; p < t.np; ++p) n += (s_mask[p] & both) == both;
+        s_cnt[k + 1] = n;
     }
     __syncthreads();
     // counts -> global (entry k + 1 holds the count of block k; the scan happens in pass b)
