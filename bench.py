@@ -12,7 +12,9 @@ cost evaluation.
   value : device-resident leg (inputs already in HBM), CUDA-event time of the LM loop on the
           stream the kernels are launched on, max over ranks.
   e2e   : the same metric through the C ABI with HOST buffers: set_problem (pinned host arrays)
-          + Optimize (H2D, structure build, LM, D2H of poses and points), wall clock.
+          + Optimize (H2D, structure build, LM, D2H of poses and points), wall clock; timed on one
+          handle and as a stream of steps through two handles (viso_b200.optimize_stream), the
+          faster one reported if both give the identical final cost (`e2e.mode`).
   --impl reference : the CPU oracle (the reference adjuster itself cannot be compiled, see
           DESIGN.md) on all host cores over a bounded sample of the same workload.
 """
