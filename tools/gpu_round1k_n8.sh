@@ -7,3 +7,4 @@ run 29701 bench.py --gpus $N --steps 10 --warmup 3 --no-cpu --no-others > gpurun
 run 29702 bench.py --gpus $N --steps 10 --warmup 3 --workload c3 --no-cpu --no-others > gpurun_out/scale_c3_n$N.json 2> gpurun_out/scale_c3_n$N.err; echo "c3 n$N rc $?"
 run 29703 tools/shard_check.py > gpurun_out/shard_check_n$N.json 2> gpurun_out/shard_check_n$N.err; echo "shard rc $?"; cat gpurun_out/shard_check_n$N.json
 tail -n 2 gpurun_out/scale_c5_n$N.err; tail -n 2 gpurun_out/scale_c3_n$N.err
+run 29704 bench.py --gpus $N --steps 5 --warmup 3 --workload c4 --no-cpu --no-others > gpurun_out/scale_c4_n$N.json 2> gpurun_out/scale_c4_n$N.err; echo "c4 n$N rc $?"
