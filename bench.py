@@ -54,6 +54,7 @@ def parse_args():
     ap.add_argument("--windows", type=int, default=1024, help="windows per GPU (workload c5)")
     ap.add_argument("--cpu-sample-s", type=float, default=12.0, help="target seconds of the CPU baseline sample")
     ap.add_argument("--no-others", action="store_true", help="skip the secondary workloads in the JSON line")
+    ap.add_argument("--sharded", default="c3,c4", help="N > 1: workloads run point-sharded beside the headline line ('' = none)")
     ap.add_argument("--no-e2e", action="store_true", help="skip the end-to-end leg (profiling runs)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg (profiling runs)")
     return ap.parse_args()
@@ -173,11 +174,15 @@ def cpu_leg(vb, workload, lm_iters, target_s, windows):
         _, _, _, _, st = orc.optimize(c, p["poses_init"], p["points_init"], p["edge_pose"], p["edge_point"], p["edge_uv"], lm_iters)
         return len(p["edge_pose"]) * sum(s.trials for s in st)
 
+    single = None
     if workload == "c5":
         probe = vb.synth_config(5, 0)
         t0 = time.perf_counter()
-        solve(probe, 1)
+        u1 = solve(probe, 1)
         t1 = time.perf_counter() - t0
+        # the reference and default g2o are single-threaded: one window on one thread, beside the all-cores figure
+        single = {"value": u1 / t1, "unit": UNIT, "cores": 1, "kind": "port",
+                  "sample": "window 0 of the workload on one thread, %d LM iterations" % lm_iters}
         n = int(max(cores, min(windows, cores * max(1.0, target_s / max(t1, 1e-3)))))
         n = (n // cores) * cores
         probs = [vb.synth_config(5, w) for w in range(n)]
@@ -191,6 +196,11 @@ def cpu_leg(vb, workload, lm_iters, target_s, windows):
             raise SystemExit("the CPU oracle factorises the reduced system densely (n = 11994: minutes per LM iteration); "
                              "no bounded CPU sample of workload c4 exists, use c3 or c5")
         p = vb.synth_config({"c1": 1, "c2": 2, "c3": 3}[workload])
+        t0 = time.perf_counter()
+        u1 = solve(p, 1)
+        t1 = time.perf_counter() - t0
+        single = {"value": u1 / t1, "unit": UNIT, "cores": 1, "kind": "port",
+                  "sample": "the whole problem once on one thread, %d LM iterations" % lm_iters}
         reps, units, dt = 0, 0.0, 0.0
         while dt < target_s and reps < 200:
             t0 = time.perf_counter()
@@ -199,7 +209,7 @@ def cpu_leg(vb, workload, lm_iters, target_s, windows):
             reps += 1
         sample = "the whole problem, %d repetitions of %d LM iterations, OpenMP over points" % (reps, lm_iters)
     return {"value": units / dt, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample,
-            "seconds": round(dt, 3), "units": units}
+            "seconds": round(dt, 3), "units": units, "single_thread": single}
 
 
 def run_reference(args):
@@ -249,11 +259,22 @@ PASS_OF = {"linearize": "L", "schur_blocks": "L", "block_finalize": "L", "win_li
            "update": "BC", "win_update": "BC", "solve_small": None, "solve_large": None, "reduce": None, "decide": None}
 
 
-# FP64-pipe slots (DFMA / DMUL / DADD, one slot each) per observation of one launch, from the ncu
-# capture profiles/r1b_win_kernels_full.csv: sm__pipe_fp64_cycles_active x cycles / 2 cycles per
-# warp instruction x 32 lanes / observations of the captured launch (296 windows).  The path is
-# bound by the FP64 pipe, not by HBM, so this second roof is reported beside the first.
-FP64_SLOTS_PER_OBS = {"win_linearize_schur": 662.0, "win_update": 141.0}
+# FP64 instructions (DFMA / DMUL / DADD ..., one issue slot each) per observation of one launch, derived by
+# tools/ncu_derive.py from an `ncu --set full` capture of THIS build (profiles/derived_roofline.json: keyed by the
+# source digest in viso_b200/.libviso_ba.stamp; `stale` is reported when the library has changed since the capture).
+# The path is bound by the FP64 pipe, not by HBM, so this second roof is reported beside the first.
+def derived_profile():
+    try:
+        with open(os.path.join(ROOT, "profiles", "derived_roofline.json")) as fh:
+            d = json.load(fh)
+    except Exception:
+        return None
+    try:
+        with open(os.path.join(ROOT, "viso_b200", ".libviso_ba.stamp")) as fh:
+            d["stale"] = fh.read().strip() != d.get("source_digest")
+    except Exception:
+        d["stale"] = None
+    return d
 
 
 def fp64_peak():
@@ -296,28 +317,22 @@ def roofline(ktimes, trials_per_problem, sizes, nprob=1):
     achieved = A[ps] / (t_us * 1e-6) / 1e9
     # measured DRAM traffic of the same kernels (ncu --set full, one launch over `windows` windows of the
     # same shape): scaled to this run's window count, per launch like `achieved`
-    traffic = None
-    try:
-        exact = os.path.join(ROOT, "profiles", "traffic_%dwin.json" % nprob)
-        base = 296.0
-        if os.path.exists(exact):  # a capture of exactly this launch
-            base = float(nprob)
-        else:
-            exact = os.path.join(ROOT, "profiles", "traffic_296win.json")
-        with open(exact) as fh:
-            tr = json.load(fh)
-        if all(k in tr for k in members) and nprob > 1:
-            traffic = sum(tr[k] for k in members) * nprob / base
-    except Exception:
-        pass
-    fp64 = None
-    if top in FP64_SLOTS_PER_OBS:
+    traffic, fp64 = None, None
+    prof = derived_profile()
+    pk_ = (prof or {}).get("kernels", {})
+    if prof and all(k in pk_ for k in members) and prof.get("problems"):
+        # dram__bytes_read + dram__bytes_write of the pass's kernels in the captured launch, scaled to this run's
+        # problem count (the capture is of the default bench command, so the scale is normally 1)
+        traffic = sum(pk_[k]["dram_bytes"] for k in members) * nprob / float(prof["problems"])
+    if prof and top in pk_ and pk_[top].get("fp64_inst_per_observation"):
+        slots = float(pk_[top]["fp64_inst_per_observation"])
         pk, src = fp64_peak()
         n_top = trials_per_problem + (1.0 if PASS_OF.get(top) == "L" else 0.0)  # the init launch counted as a full one
-        ach = FP64_SLOTS_PER_OBS[top] * No * n_top / (ktimes[top][1] * 1e-3) / 1e12
-        fp64 = {"kernel": top, "slots_per_observation": FP64_SLOTS_PER_OBS[top], "achieved": ach, "peak": pk,
+        ach = slots * No * n_top / (ktimes[top][1] * 1e-3) / 1e12
+        fp64 = {"kernel": top, "slots_per_observation": slots, "achieved": ach, "peak": pk,
                 "unit": "T FP64 instructions/s (an FMA is one)", "frac": ach / pk, "peak_source": src,
-                "note": "the binding roof of this kernel: HBM traffic is ~7% of peak because the pair products are FP64-issue-bound"}
+                "capture": prof.get("capture"), "capture_is_of_this_build": (not prof["stale"]) if prof.get("stale") is not None else None,
+                "note": "the binding roof of this kernel: the pair products are FP64-issue-bound, HBM is far from saturated"}
     return {
         "fp64": fp64,
         "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
@@ -504,14 +519,110 @@ def run_b200(args):
     }
     if rank == 0 and not args.no_others and world == 1:
         line["others"] = others(vb, args, local)
+    if world > 1 and args.sharded and not sharded:
+        ba.close()  # the headline handle's arena goes back before the large problems are set up
+        sh = sharded_section(vb, torch, dist, args, rank, world, local, barrier, max_over_ranks)
+        if rank == 0:
+            line["sharded"] = sh
     if rank == 0 and not args.no_cpu and args.workload != "c4":
         line["cpu_baseline"] = {k: v for k, v in cpu_leg(vb, args.workload, args.lm_iters, args.cpu_sample_s, args.windows).items()
-                                if k in ("value", "unit", "cores", "kind", "sample")}
+                                if k in ("value", "unit", "cores", "kind", "sample", "single_thread")}
     if rank == 0:
         emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def sharded_section(vb, torch, dist, args, rank, world, local, barrier, max_over_ranks):
+    """N > 1 only (collective: every rank calls it).  The workloads the path SHARDS -- BASELINE configs[2] (c3) and
+    configs[3] (c4): one problem, points sharded over the ranks, the reduced camera system combined over NCCL on the
+    handle's own communicator -- run on the process group of the headline line, so that the driver's scaling record
+    carries a strong-scaling curve, beside the same problem solved by rank 0 alone on its GPU, and a parity check of the
+    sharded path against the CPU oracle at a bounded size (tests/shard_parity.py).  Reference concept being sharded:
+    BlockSolver<6,3> + LinearSolverDense, reference include/bundle_adjuster.h:108-117."""
+    out = {}
+    names = [w for w in ("c3", "c4") if w in args.sharded.split(",")]
+    for name in names:
+        try:
+            probs, huber = make_workload(vb, name, rank, 0)
+            b = vb.batch_problems(probs)
+            No = len(b["edge_pose"])
+            ba = make_adjuster(vb, b, huber, local)
+            ident = [vb.nccl_unique_id() if rank == 0 else None]
+            dist.broadcast_object_list(ident, src=0)
+            ba.shard_init(rank, world, ident[0])
+            t0 = time.perf_counter()
+            set_problem(ba, b)
+            ba.upload()
+            setup_s = max_over_ranks(time.perf_counter() - t0)
+            for _ in range(3):
+                ba.reset_state()
+                s = ba.optimize_resident(args.lm_iters)
+            steps = max(3, min(args.steps, 10 if name == "c3" else 5))
+            barrier()
+            ms = 0.0
+            for _ in range(steps):
+                ba.reset_state()
+                ms += ba.optimize_resident(args.lm_iters).device_ms
+            barrier()
+            ms = max_over_ranks(ms) / steps
+            ba.reset_state()
+            ba.set_kernel_timing(True)
+            ba.optimize_resident(args.lm_iters)
+            kt = ba.kernel_times()
+            ba.set_kernel_timing(False)
+            # end to end through the C ABI with host buffers: every rank hands over the problem, reads the result back
+            t0 = time.perf_counter()
+            set_problem(ba, b)
+            s_e = ba.Optimize(args.lm_iters)
+            barrier()
+            e2e_s = max_over_ranks(time.perf_counter() - t0)
+            # every rank must hold the same refined state, bit for bit
+            t = torch.from_numpy(np.concatenate([ba.poses().ravel(), ba.points().ravel()])).cuda()
+            ref = t.clone()
+            dist.broadcast(ref, src=0)
+            same = torch.tensor([1.0 if bool(torch.equal(t, ref)) else 0.0], device="cuda")
+            dist.all_reduce(same, op=dist.ReduceOp.MIN)
+            ba.close()
+            rec = {"value": No * s.trials / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms, "lm_trials_per_step": s.trials,
+                   "lm_iters_per_sec": s.trials / (ms * 1e-3), "observations": No, "steps": steps, "scaling": "strong",
+                   "final_cost": s.final_cost, "ranks_bit_identical": bool(same.item() == 1.0), "setup_s": setup_s,
+                   "e2e": {"value": No * s_e.trials / e2e_s, "unit": UNIT, "ms_per_step": 1e3 * e2e_s, "final_cost": s_e.final_cost},
+                   "kernels_ms_per_step": {k: v[1] for k, v in kt.items() if k not in ("state_init", "cam_rt", "lm_init", "gather_current")}}
+            if rank == 0:  # the same problem on ONE GPU, measured in the same process on the same box
+                one = make_adjuster(vb, b, huber, local)
+                set_problem(one, b)
+                one.upload()
+                for _ in range(2):
+                    one.reset_state()
+                    s1 = one.optimize_resident(args.lm_iters)
+                m1 = []
+                for _ in range(3):
+                    one.reset_state()
+                    m1.append(one.optimize_resident(args.lm_iters).device_ms)
+                one.close()
+                m1 = float(np.median(m1))
+                rec["one_gpu"] = {"ms_per_step": m1, "value": No * s1.trials / (m1 * 1e-3), "final_cost": s1.final_cost,
+                                  "cost_rel_vs_sharded": abs(s1.final_cost - s.final_cost) / s1.final_cost}
+                rec["speedup_vs_one_gpu"] = m1 / ms
+            barrier()
+            out[name] = rec
+        except Exception as e:  # never fail the headline because of it
+            out[name] = {"error": str(e)}
+            try:
+                barrier()
+            except Exception:
+                pass
+    try:
+        import shard_parity
+        out["parity"] = {
+            "dense_S": shard_parity.check(vb, torch, dist, rank, world, local, config=3, poses=60, points=20000, iters=6),
+            "banded_S": shard_parity.check(vb, torch, dist, rank, world, local, config=4, poses=150, points=15000, iters=5),
+        }
+    except Exception as e:
+        out["parity"] = {"error": str(e)}
+    return out
 
 
 def others(vb, args, device):

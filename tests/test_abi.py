@@ -6,6 +6,7 @@ import ctypes as C
 import os
 import re
 import subprocess
+import sys
 
 import numpy as np
 import pytest
@@ -29,6 +30,24 @@ def test_library_exports_every_declared_symbol(vb):
     out = subprocess.run(["nm", "-D", "--defined-only", vb.LIB_PATH], capture_output=True, text=True).stdout
     exported = set(re.findall(r" T (viso_ba_[a-z0-9_]+)", out))
     assert set(declared) <= exported
+
+
+def test_synth_library_is_host_only_and_exports_its_header(vb):
+    """include/viso_ba_synth.h lives in libviso_synth.so, which links no CUDA: the CPU reference arm of bench.py
+    generates its problems without ever mapping the CUDA backend"""
+    src = open(os.path.join(ROOT, "include", "viso_ba_synth.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    declared = sorted(set(re.findall(r"\b(viso_ba_synth_[a-z0-9_]+)\s*\(", src)))
+    assert sorted(vb.SYNTH_SYMBOLS) == declared and len(declared) == 5
+    out = subprocess.run(["nm", "-D", "--defined-only", vb.SYNTH_LIB_PATH], capture_output=True, text=True).stdout
+    assert set(declared) <= set(re.findall(r" T (viso_ba_synth_[a-z0-9_]+)", out))
+    needed = subprocess.run(["readelf", "-d", vb.SYNTH_LIB_PATH], capture_output=True, text=True).stdout
+    assert "cuda" not in needed.lower() and "nccl" not in needed.lower()
+    # a fresh interpreter that only generates a problem maps libviso_synth.so and not libviso_ba.so
+    code = ("import sys; sys.path.insert(0, %r); import viso_b200 as vb; p = vb.synth_config(1, n_points=50, target_edges=200);"
+            "m = open('/proc/self/maps').read(); print(int('libviso_synth.so' in m), int('libviso_ba.so' in m))" % ROOT)
+    res = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, check=True)
+    assert res.stdout.split() == ["1", "0"]
 
 
 def test_version_config_and_status_strings(vb):

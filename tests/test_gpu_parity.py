@@ -110,6 +110,58 @@ def test_banded_reduced_system_envelope_solver_matches_oracle(vb, oracle):
     assert np.abs(rows - cols).max() <= 24  # co-visibility span of this layout
 
 
+def test_c4_layout_n3000_matches_oracle(vb, oracle):
+    """BASELINE configs[3] layout at the largest size the oracle's dense Cholesky finishes in well under a minute:
+    500 cameras on the trajectory, 50k points, 500k observations, n = 2994 (47 column blocks of 64, envelope ~150
+    columns wide): the banded reduced solve far beyond the n = 894 of the test above"""
+    p = vb.synth_config(4, n_poses=500, n_points=50000, target_edges=500000)
+    ba, s = _check_against_oracle(vb, oracle, p, 3, threads=16)
+    assert s.trials == 3 and s.terminated == 0
+
+
+def test_c5_headline_batch_at_full_size_sample_matches_oracle(vb, oracle):
+    """The benched workload itself (bench.py defaults: 1024 windows x 10 keyframes x 2k points x ~15k observations,
+    seeds 0x5EED0500 + w, 10 LM iterations, path = auto): 16 windows drawn from the FULL batch, plus every window
+    that needed a rejected trial (the stragglers of the compacted launches), each against the oracle at the
+    north_star tolerances -- asserted far tighter, fp64 on both sides"""
+    n_win = 1024
+    probs = [vb.synth_config(5, w) for w in range(n_win)]
+    b = vb.batch_problems(probs)
+    assert len(b["edge_pose"]) > 15_000_000 and len(b["points_init"]) == 2000 * n_win
+    ba = vb.BundleAdjuster(len(b["points_init"]), len(b["poses_init"]), len(b["edge_pose"]))
+    ba.set_problem_batched(b["pose_off"], b["point_off"], b["edge_off"], b["poses_init"], b["points_init"],
+                           b["edge_pose"], b["edge_point"], b["edge_uv"])
+    s = ba.Optimize(10)
+    sums, poses, pts = ba.problem_summaries(), ba.poses(), ba.points()
+    assert s.trials == sum(x.trials for x in sums) and s.trials >= 10 * n_win
+    drawn = set(int(w) for w in np.random.default_rng(5).choice(n_win, 16, replace=False))
+    stragglers = [w for w in range(n_win) if sums[w].trials != 10]
+    drawn.update(stragglers[:8])
+    noise_level = 0
+    for w in sorted(drawn):
+        p = probs[w]
+        po, pt, fc, it, st = oracle.optimize(oracle.cfg(), *_args(p), 10)
+        assert sums[w].iterations == it, w
+        # Accept / reject decisions must be the oracle's -- except in an iteration that has already converged to
+        # rounding noise (cost decrease below 1e-12 relative: window 507's tenth iteration moves the cost by 1e-11 of
+        # 23340), where the sign of chi - chi_new is decided by the summation order and the two sides may need a
+        # different number of rejected trials; the state they end in is the same to the tolerances below either way.
+        at_noise = any(x.trials > 1 and abs(x.cost_before - x.cost_after) <= 1e-12 * x.cost_before for x in st)
+        if sums[w].trials != sum(x.trials for x in st):
+            assert at_noise, (w, sums[w].trials, [x.trials for x in st])
+            noise_level += 1
+        assert sums[w].final_cost == pytest.approx(fc, rel=1e-10), w
+        assert abs(sums[w].final_cost - fc) <= COST_RTOL * fc
+        _quat_close(poses[b["pose_off"][w]:b["pose_off"][w + 1]], po, 1e-9 if not at_noise else 1e-8)
+        assert np.abs(pts[b["point_off"][w]:b["point_off"][w + 1]] - pt).max() < (1e-8 if not at_noise else 1e-7), w
+    assert noise_level <= len(stragglers)
+    # the launch that did it was the tile kernel
+    ba.set_kernel_timing(True)
+    ba.reset_state()
+    ba.optimize_resident(1)
+    assert "win_linearize_schur" in ba.kernel_times()
+
+
 def test_c4_full_size_properties(vb):
     """BASELINE configs[3] at full size (2k cameras, 1M points, 10M observations; n = 11994): the
     oracle's dense solve would take minutes per iteration, so size-independent properties instead:

@@ -3,7 +3,8 @@
 linearises and Schur-reduces ITS points only, the partial reduced camera systems and costs are
 summed with one fp64 allreduce, and only rank 0 contributes the damping of the pose diagonal
 (DevProblem::lambda_scale).  The oracle plays the per-rank kernels; the sum must equal the
-unsharded reduced system.  (The NCCL version of the same exchange runs in the GPU tests.)"""
+unsharded reduced system.  The NCCL version of the same exchange is tests/test_gpu_sharded.py (`-m gpu`, two
+ranks under torch.distributed.run, skipped on a one-GPU box) and the `sharded` section of bench.py at N > 1."""
 import os
 import socket
 import sys

@@ -15,6 +15,7 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libviso_ba.so")
+SYNTH_LIB_PATH = os.path.join(_HERE, "libviso_synth.so")  # host-only generator (include/viso_ba_synth.h)
 
 OK = 0
 STATUS_NAMES = {
@@ -115,6 +116,9 @@ SYMBOLS = {
     "viso_ba_kernel_launches": (C.c_int64, [_P]),
     "viso_ba_set_kernel_timing": (C.c_int32, [_P, C.c_int32]),
     "viso_ba_get_kernel_times": (C.c_int32, [_P, C.c_int32, C.POINTER(KernelTime), _I32]),
+}
+# include/viso_ba_synth.h, exported by libviso_synth.so (no CUDA)
+SYNTH_SYMBOLS = {
     "viso_ba_synth_preset": (C.c_int32, [C.c_int32, C.c_int32, C.POINTER(SynthSpec)]),
     "viso_ba_synth_create": (C.c_int32, [C.POINTER(SynthSpec), C.POINTER(_P)]),
     "viso_ba_synth_destroy": (None, [_P]),
@@ -123,6 +127,22 @@ SYMBOLS = {
 }
 
 _lib = None
+_synth_lib = None
+
+
+def load_synth_library():
+    """dlopen libviso_synth.so (host-only: needs neither a GPU nor the CUDA backend)."""
+    global _synth_lib
+    if _synth_lib is None:
+        if not os.path.exists(SYNTH_LIB_PATH):
+            raise ImportError("%s is missing: build it with `python -m viso_b200.build`" % SYNTH_LIB_PATH)
+        lib = C.CDLL(SYNTH_LIB_PATH)
+        for name, (res, args) in SYNTH_SYMBOLS.items():
+            fn = getattr(lib, name)
+            fn.restype = res
+            fn.argtypes = args
+        _synth_lib = lib
+    return _synth_lib
 
 
 def load_library(path=None):
@@ -375,7 +395,7 @@ def shard_point_ranges(n_points, edge_point, n_ranks):
 # ---- synthetic problems; host-only, needs no GPU ------------------------------------
 def synth_preset(config_id, window=0):
     sp = SynthSpec()
-    st = load_library().viso_ba_synth_preset(int(config_id), int(window), C.byref(sp))
+    st = load_synth_library().viso_ba_synth_preset(int(config_id), int(window), C.byref(sp))
     if st != OK:
         raise VisoBaError(st, "unknown synthetic preset %r" % (config_id,))
     return sp
@@ -383,7 +403,7 @@ def synth_preset(config_id, window=0):
 
 def synth_problem(spec):
     """Generate one problem; returns a dict of numpy arrays."""
-    lib = load_library()
+    lib = load_synth_library()
     s = _P()
     st = lib.viso_ba_synth_create(C.byref(spec), C.byref(s))
     if st != OK:

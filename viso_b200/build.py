@@ -1,4 +1,5 @@
-"""Build libviso_ba.so (CUDA kernels + C ABI host) in-tree with nvcc for sm_100a.
+"""Build libviso_ba.so (CUDA kernels + C ABI host) in-tree with nvcc for sm_100a, and the host-only
+synthetic-problem generator libviso_synth.so (g++, no CUDA) beside it.
 
 The .so is git-ignored but travels to the GPU box with the gpurun snapshot.  nvcc
 cross-compiles without a GPU, so this runs in the CPU container too.
@@ -14,8 +15,10 @@ ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libviso_ba.so")
 STAMP = os.path.join(HERE, ".libviso_ba.stamp")
-SOURCES = ["ba_kernels.cu", "ba_window.cu", "ba_dense.cu", "ba_setup.cu", "direct_pose.cu", "lk_align.cu", "pyramid.cu", "viso_ba.cpp", "synth.cpp"]
-HEADERS = [os.path.join(CSRC, "ba_device.h"), os.path.join(CSRC, "ba_math.cuh"), os.path.join(CSRC, "ba_setup.h"), os.path.join(CSRC, "image_math.cuh"), os.path.join(ROOT, "include", "viso_ba.h"), os.path.join(ROOT, "include", "viso_direct.h"), os.path.join(ROOT, "include", "viso_lk.h")]
+SYNTH_LIB = os.path.join(HERE, "libviso_synth.so")
+SOURCES = ["ba_kernels.cu", "ba_window.cu", "ba_dense.cu", "ba_setup.cu", "direct_pose.cu", "lk_align.cu", "pyramid.cu", "viso_ba.cpp"]
+SYNTH_SOURCES = ["synth.cpp"]
+HEADERS = [os.path.join(CSRC, "ba_device.h"), os.path.join(CSRC, "ba_math.cuh"), os.path.join(CSRC, "ba_setup.h"), os.path.join(CSRC, "image_math.cuh"), os.path.join(ROOT, "include", "viso_ba.h"), os.path.join(ROOT, "include", "viso_ba_synth.h"), os.path.join(ROOT, "include", "viso_direct.h"), os.path.join(ROOT, "include", "viso_lk.h")]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "-Xcompiler", "-fPIC,-O2,-Wall", "-shared", "-cudart", "static",
@@ -31,7 +34,7 @@ def _nvcc():
 
 def _digest():
     h = hashlib.sha256()
-    for f in [os.path.join(CSRC, s) for s in SOURCES] + HEADERS + [os.path.abspath(__file__)]:
+    for f in [os.path.join(CSRC, s) for s in SOURCES + SYNTH_SOURCES] + HEADERS + [os.path.abspath(__file__)]:
         with open(f, "rb") as fh:
             h.update(fh.read())
     return h.hexdigest()
@@ -40,7 +43,7 @@ def _digest():
 def build(force=False, verbose=False):
     """Compile every CUDA source of the package; returns the path of the shared library."""
     dig = _digest()
-    if not force and os.path.exists(LIB) and os.path.exists(STAMP):
+    if not force and os.path.exists(LIB) and os.path.exists(SYNTH_LIB) and os.path.exists(STAMP):
         with open(STAMP) as fh:
             if fh.read().strip() == dig:
                 return LIB
@@ -51,6 +54,11 @@ def build(force=False, verbose=False):
         sys.stderr.write(res.stderr)
     if res.returncode != 0:
         raise RuntimeError("nvcc failed:\n" + res.stdout + res.stderr)
+    gxx = shutil.which("g++") or "g++"
+    res = subprocess.run([gxx, "-O2", "-std=c++17", "-fPIC", "-shared", "-Wall"] + [os.path.join(CSRC, s) for s in SYNTH_SOURCES]
+                         + ["-o", SYNTH_LIB], capture_output=True, text=True)
+    if res.returncode != 0:
+        raise RuntimeError("g++ failed (libviso_synth.so):\n" + res.stdout + res.stderr)
     with open(STAMP, "w") as fh:
         fh.write(dig)
     return LIB

@@ -431,19 +431,10 @@ int large_solve_max_n() { return 6 * 5000; } // 7.2 GB of dense lower triangle; 
 // runtime guarantees that all CTAs are co-resident, which the grid barriers need
 int launch_chol_coop(const LargeSolve& L, cudaStream_t st)
 {
-    static int n_sm = 0;
-    static size_t configured = 0;
+    static PerDeviceOnce once;
     const size_t smem = kCholSmem;
-    if (n_sm == 0) {
-        int dev = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
-        if (n_sm <= 0) n_sm = 1;
-    }
-    if (smem > configured) {
-        if (cudaFuncSetAttribute(k_chol_coop, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return 0;
-        configured = smem;
-    }
+    if (!once.run([] { return cudaFuncSetAttribute(k_chol_coop, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kCholSmem) == cudaSuccess; })) return 0;
+    const int n_sm = once.sm_count();
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)n_sm), cfg.blockDim = dim3(kCT), cfg.dynamicSmemBytes = smem, cfg.stream = st;
     cudaLaunchAttribute attr[1];

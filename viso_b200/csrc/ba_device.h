@@ -16,7 +16,39 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <mutex>
+
 namespace visoba {
+
+// One-time per-DEVICE kernel configuration.  cudaFuncSetAttribute (dynamic shared memory above 48 KB, non-portable
+// cluster sizes) applies to the current device only, and handles of one process may live on different devices and be
+// driven from different host threads (viso_b200/stream.py), so the "configured" state is kept per device ordinal and
+// behind a mutex instead of in a process-wide flag.
+struct PerDeviceOnce {
+    std::mutex mu;
+    signed char state[64] = {}; // 0 unknown, 1 ok, -1 failed
+    int n_sm[64] = {};
+    template <typename F> bool run(F&& f)
+    {
+        int dev = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return false;
+        std::lock_guard<std::mutex> lock(mu);
+        if (state[dev] == 0) state[dev] = f() ? 1 : -1;
+        return state[dev] == 1;
+    }
+    int sm_count()
+    { // SMs of the current device
+        int dev = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 1;
+        std::lock_guard<std::mutex> lock(mu);
+        if (n_sm[dev] <= 0) {
+            int n = 0;
+            cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+            n_sm[dev] = n > 0 ? n : 1;
+        }
+        return n_sm[dev];
+    }
+};
 
 constexpr int kRecDoubles = 12;   // per-observation record
 constexpr int kPtInfoDoubles = 9; // per-point record

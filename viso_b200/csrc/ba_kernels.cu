@@ -698,11 +698,10 @@ int launch_solve_small(const DevProblem& P, int max_n, cudaStream_t st)
 {
     const int ld = (max_n + 1) | 1;
     const size_t smem = sizeof(double) * (size_t)(max_n + 1) * (size_t)ld;
-    static size_t configured = 0;
-    if (smem > 48 * 1024 && smem > configured) {
-        cudaFuncSetAttribute(k_solve_small, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        configured = smem;
-    }
+    static PerDeviceOnce once; // the largest system the kernel takes, once per device
+    constexpr size_t kMaxSmem = sizeof(double) * (size_t)(kSmallMaxN + 1) * (size_t)((kSmallMaxN + 1) | 1);
+    if (smem > kMaxSmem) return 0;
+    if (!once.run([] { return cudaFuncSetAttribute(k_solve_small, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxSmem) == cudaSuccess; })) return 0;
     // more warps than the column has rows only lengthen the three barriers of a column step (C5, n = 54: 256 threads
     // 101 us, 128 threads 80 us, 64 threads 105 us per launch)
     const int threads = max_n <= 64 ? 128 : 256;

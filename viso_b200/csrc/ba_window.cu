@@ -620,13 +620,12 @@ size_t win_shared_bytes() { return kLsBytes; }
 
 static bool win_configure()
 {
-    static int state = 0; // 0 unknown, 1 ok, -1 failed
-    if (state == 0) {
+    static PerDeviceOnce once;
+    return once.run([] {
         cudaError_t e1 = cudaFuncSetAttribute(k_win_linearize_schur, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kLsBytes);
         cudaError_t e2 = cudaFuncSetAttribute(k_win_update, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kUsBytes);
-        state = (e1 == cudaSuccess && e2 == cudaSuccess) ? 1 : -1;
-    }
-    return state == 1;
+        return e1 == cudaSuccess && e2 == cudaSuccess;
+    });
 }
 
 int launch_win_linearize_schur(const DevProblem& P, int init_pass, double lambda_override, cudaStream_t st)

@@ -588,12 +588,9 @@ int32_t viso_direct_set_reference_pose(viso_direct* h, int32_t frame, const doub
 static cudaError_t launch_direct(viso_direct* h, int32_t n_frames, double* d_poses, viso_direct_level_stats* d_stats,
                                  int level_hi, int level_lo, int linearize_only, double* d_lin)
 {
-    static bool allowed = false;
-    if (!allowed) {
-        cudaError_t e = cudaFuncSetAttribute(k_direct, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
-        if (e != cudaSuccess) return e;
-        allowed = true;
-    }
+    static visoba::PerDeviceOnce once; // per device: the attribute applies to the current device only
+    if (!once.run([] { return cudaFuncSetAttribute(k_direct, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess; }))
+        return cudaErrorInvalidValue;
     const int csize = n_frames >= 2 * kClusterBatch ? kClusterBatch : kClusterMax;
     cudaLaunchConfig_t lc = {};
     lc.gridDim = dim3(csize * n_frames), lc.blockDim = dim3(kThreads), lc.dynamicSmemBytes = 0, lc.stream = h->stream;

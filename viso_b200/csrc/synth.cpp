@@ -1,13 +1,15 @@
 // synth.cpp — deterministic synthetic bundle-adjustment problems.
 //
-// Host-only.  One generator feeds both the CUDA backend and the CPU oracle so that
+// Host-only, built as its own library (libviso_synth.so: no CUDA, so the CPU arm of bench.py never maps the
+// CUDA backend).  One generator feeds both the CUDA backend and the CPU oracle so that
 // they read identical bytes.  Scene conventions follow the reference:
 //   intrinsics fx=517.3 fy=516.5 cx=325.1 cy=249.7, 640x480   src/main.cpp:14-17, :73
 //   mean scene depth 1                                         src/viso.cpp:622-637
 //   4 px image margin (half_patch_size)                        include/viso.h:25
 //   measurements are float32 (cv::Point2f)                     include/keyframe.h:15
 //   frame 0 is the identity pose                               include/keyframe.h:34-35
-#include "../../include/viso_ba.h"
+#include "../../include/viso_ba.h" // status codes only
+#include "../../include/viso_ba_synth.h"
 
 #include <algorithm>
 #include <cmath>
