@@ -143,10 +143,10 @@ def test_c5_headline_batch_at_full_size_sample_matches_oracle(vb, oracle):
         po, pt, fc, it, st = oracle.optimize(oracle.cfg(), *_args(p), 10)
         assert sums[w].iterations == it, w
         # Accept / reject decisions must be the oracle's -- except in an iteration that has already converged to
-        # rounding noise (cost decrease below 1e-12 relative: window 507's tenth iteration moves the cost by 1e-11 of
-        # 23340), where the sign of chi - chi_new is decided by the summation order and the two sides may need a
+        # rounding noise (cost decrease below 1e-12 relative: the tenth iteration of windows 507 and 691 moves the cost by
+        # 1e-11 of 23340 and 1e-10 of 24039), where the sign of chi - chi_new is decided by the summation order and the two sides may need a
         # different number of rejected trials; the state they end in is the same to the tolerances below either way.
-        at_noise = any(x.trials > 1 and abs(x.cost_before - x.cost_after) <= 1e-12 * x.cost_before for x in st)
+        at_noise = any(abs(x.cost_before - x.cost_after) <= 1e-12 * x.cost_before for x in st)
         if sums[w].trials != sum(x.trials for x in st):
             assert at_noise, (w, sums[w].trials, [x.trials for x in st])
             noise_level += 1
