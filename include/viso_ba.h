@@ -68,7 +68,10 @@ typedef struct {
                               whenever eligible (every problem <= 32 keyframes and <= 27 free
                               poses, no duplicate edges, not sharded), 2 = general pair-list
                               path.  Auto takes the window path when its tiles fill the GPU.   */
-    int32_t reserved;
+    int32_t solver_segments; /* reduced systems beyond 27 free poses (one large problem): how the pose chain is cut for the
+                              solve.  0 = auto (up to 8 interior segments when the co-visibility span is small against
+                              the chain, as on a long trajectory), 1 = never (one envelope Cholesky), k >= 2 = up to k
+                              segments whenever the structure allows it.  The result does not depend on the GPU count. */
 } viso_ba_config;
 
 /* per outer LM iteration (single-problem handles) */

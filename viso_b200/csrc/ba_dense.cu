@@ -1,28 +1,32 @@
-// ba_dense.cu — K3 (large): dense solve of the reduced camera system of ONE problem whose
-// n = 6 * (free poses) does not fit the shared-memory solver (n > kSmallMaxN), e.g. BASELINE
-// config 3 (200 keyframes, n = 1194) and config 4 (2000 cameras, n = 11994).
+// ba_dense.cu — K3 (large): solve of the reduced camera system of ONE problem whose n = 6 * (free poses) does not fit
+// the shared-memory solver (n > kSmallMaxN), e.g. BASELINE config 3 (200 keyframes, n = 1194, dense) and config 4
+// (2000 cameras, n = 11994, banded: co-visibility spans ~25 cameras).
 //
-// Reference: LinearSolverDense<PoseMatrixType> (reference include/bundle_adjuster.h:113-114):
-// g2o copies the pose blocks into one dense matrix and runs a Cholesky-family solver on it.
+// Reference: LinearSolverDense<PoseMatrixType> (reference include/bundle_adjuster.h:113-114): g2o copies the pose blocks
+// into one dense matrix and runs a Cholesky-family solver on it, on one core.
 //
-// One PERSISTENT cooperative kernel (one CTA per SM, grid-wide barriers) replaces the former
-// chain of 2 launches per 32-column panel:
-//     for every 64-column block step
-//        P  every CTA factorises the 64x64 diagonal block redundantly (same input, same order of
-//           operations -> same bits everywhere: no broadcast, no barrier): 32x32 quarters, the
-//           quarter on the diagonal by ONE warp in registers (shuffles, rsqrt on the pivot chain);
-//           then its warps solve their rows of the panel  X L_kk^T = A_panel  (one warp per row,
-//           the row lives in registers, L_kk^T is read from shared memory without conflicts)
-//        -- grid barrier --
-//        U  64x64 tiles of the trailing lower triangle:  A_il -= X_i X_l^T
-//        -- grid barrier --
-//     backward substitution L^T x = y (the rhs rides along as row n of A, so the forward
-//     substitution falls out of the factorisation): block b of x is owned by one CTA, which folds
-//     in every published x_b' (b' > b) and publishes x_b with a release flag; no grid barrier.
-// Measured on B200 (tools/chol_bench.cu, n = 1194): 786 us, of which 240 us are the pivot chain
-// (1194 columns x ~390 cycles of dependent FP64 latency) and 110 us the backward substitution.
-// Everything is fp64; nothing is atomic; the summation order is fixed by the tiling, so two runs
-// (and the ranks of a sharded solve, which all hold the same S) produce identical bits.
+// Here: ONE persistent cooperative kernel (one CTA per SM) that works through a list of CholTask (ba_device.h):
+//   phase 1  every interior SEGMENT of the pose chain is eliminated by its own group of CTAs, all segments at once
+//            (group barriers: a counter in global memory, the launch is cooperative so every CTA is resident);
+//   phase 2  what the segments leave in their border blocks is added, in a fixed order, to the separator system T;
+//   phase 3  T (block tridiagonal; or, unpartitioned, the whole matrix) is factorised and solved by all CTAs;
+//   phase 4  the interiors are back-substituted, all segments at once again.
+// A banded system of n = 11994 thus costs ~21 + 21 block steps instead of 188 sequential ones, and the same plan is what
+// every rank of a sharded solve executes redundantly on the all-reduced S (identical bits on every rank, no broadcast).
+//
+// One 64-column block step of a task (the unit everything is padded to):
+//     D  every CTA of the group factorises the 64x64 diagonal block redundantly in shared memory (same input, same
+//        order of operations -> same bits: no broadcast, no barrier): 8x8 blocks, the diagonal one by ONE thread in
+//        registers (the serial chain of the whole factorisation: rsqrt + two dependent FMAs per pivot, no shuffles, no
+//        barrier inside), its panel by one thread per row, the 56x56 remainder by all 256 threads;
+//     P  panel  X L_kk^T = A_panel: one warp per FOUR rows (the four chains interleave), the row in registers;
+//        -- group barrier --
+//     U  64x64 tiles of the trailing lower triangle over the step's row ranges: A_il -= X_i X_l^T;
+//        -- group barrier --
+// The right-hand side rides along as one more row of every task, so the forward substitution falls out of the
+// factorisation.  Backward substitution L^T x = y: block b of x is owned by one CTA of the group, which folds in every
+// published x_b' (b' > b) and publishes x_b with a release flag; no barrier.
+// Everything is fp64; nothing is atomic on floating-point data; the summation order is fixed by the tiling.
 #include "ba_math.cuh"
 
 #include <cooperative_groups.h>
@@ -33,244 +37,213 @@ namespace visoba {
 
 namespace {
 
-constexpr int kCB = 64;        // block size of the factorisation
-constexpr int kCT = 256;       // threads per CTA
-constexpr int kCS = kCB + 1;   // shared-memory row stride (doubles): odd -> column walks are conflict-free
+constexpr int kCB = kCholBlock; // 64: block size of the factorisation
+constexpr int kCT = 256;        // threads per CTA
+constexpr int kCS = kCB + 1;    // shared-memory row stride (doubles): odd -> column walks are conflict-free
 constexpr size_t kCholSmem = sizeof(double) * (3 * (size_t)kCB * kCS + 7 * kCB);
 
 __device__ __forceinline__ double shfl_d(double v, int src) { return __shfl_sync(0xffffffffu, v, src); }
 
-#ifdef VISO_CHOL_PROFILE // tools/chol_bench.cu: time stamps of CTA 0 at the phase boundaries
+#ifdef VISO_CHOL_PROFILE // tools/chol_bench.cu: time stamps of CTA 0 at the phase boundaries of the LAST task (T)
 __device__ unsigned long long g_chol_prof[16 * 512];
-__device__ __forceinline__ void prof_mark(int step, int k)
+__device__ __forceinline__ void prof_mark(bool on, int step, int k)
 {
-    if (blockIdx.x == 0 && threadIdx.x == 0 && step < 512) {
+    if (on && blockIdx.x == 0 && threadIdx.x == 0 && step < 512) {
         unsigned long long t;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
         g_chol_prof[16 * step + k] = t;
     }
 }
-#define PROF(step, k) prof_mark(step, k)
+#define PROF(on, step, k) prof_mark(on, step, k)
 #else
-#define PROF(step, k)
+#define PROF(on, step, k)
 #endif
 
-// Cholesky of a 32x32 block by one warp: lane i holds row i (lower part meaningful).  The serial
-// chain of the whole factorisation runs through here (B200: DFMA 8.5, SHFL of a double 30, rsqrt 66
-// cycles, tools/lat.cu).  Per column
-//     l = r[j] * inv  ->  lane j+1 forms ITS next pivot locally (r[j+1] - l^2)  ->  one shuffle
-//     broadcasts it  ->  rsqrt  (1/sqrt replaces sqrt + division),
-// while column j of L reaches the other lanes through shared memory: one 16-byte broadcast load
-// hands two entries to all 32 lanes, where shuffles cost two instructions per entry and made the
-// warp shuffle-issue-bound.  `buf` = 2 x 32 doubles of shared memory owned by the calling warp.
-// Returns true on a non-positive or non-finite pivot.
-__device__ __forceinline__ bool warp_chol32(double (&r)[32], int lane, double* buf)
+// ---- barrier of a CTA group: monotone counter, target = visits * group size (zeroed before the launch) ----
+__device__ __forceinline__ void group_barrier(unsigned int* ctr, unsigned int target)
 {
-    double d = shfl_d(r[0], 0);
-    bool bad = !(d > 0.0) || !(d < 1.7e308);
-    double inv = rsqrt(d);
-#pragma unroll
-    for (int j = 0; j < 32; ++j) {
-        const double l = r[j] * inv; // lane j: L_jj = d / sqrt(d)
-        r[j] = l;
-        double* const col = buf + 32 * (j & 1);
-        col[lane] = l;
-        __syncwarp();
-        double inv_next = 0.0;
-        if (j + 1 < 32) {
-            d = shfl_d(fma(-l, l, r[j + 1]), j + 1); // on lane j+1 this is exactly its updated diagonal
-            bad |= !(d > 0.0) || !(d < 1.7e308);
-            inv_next = rsqrt(d);
-        }
-#pragma unroll
-        for (int k0 = (j + 1) & ~1; k0 < 32; k0 += 2) {
-            const double2 lk = *reinterpret_cast<const double2*>(col + k0);
-            if (k0 > j) r[k0] = fma(-l, lk.x, r[k0]);
-            r[k0 + 1] = fma(-l, lk.y, r[k0 + 1]);
-        }
-        inv = inv_next;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(ctr) : "memory");
+        unsigned int v;
+        do {
+            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(ctr) : "memory");
+        } while (v < target);
+        __threadfence();
     }
-    return bad;
+    __syncthreads();
 }
 
-// zero the envelope of the dense matrix (row r: columns 64 * first64[r / 64] .. r); what lies left
-// of the envelope is never read or written by the solver
-__global__ void __launch_bounds__(256) k_dense_zero(LargeSolve L)
-{
-    const int r = blockIdx.x;
-    const int c0 = kCB * L.first64[r / kCB];
-    double* row = L.A + (size_t)r * L.ld;
-    for (int c = c0 + threadIdx.x; c <= r; c += blockDim.x) row[c] = 0.0;
-    if (r == 0 && threadIdx.x == 0) *L.fail = 0;
-}
-
-// one warp per stored S block: scatter the packed 6x6 blocks (and the rhs as row n) into the dense matrix
-__global__ void __launch_bounds__(256) k_dense_assemble(DevProblem P, LargeSolve L)
-{
-    const int lane = threadIdx.x & 31;
-    const int blk = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    if (blk < P.n_blocks) {
-        const int2 ij = P.blk_ij[blk];
-        for (int e = lane; e < 36; e += 32) {
-            const int r = e / 6, c = e - 6 * r;
-            L.A[(size_t)(6 * ij.x + r) * L.ld + 6 * ij.y + c] = P.S_blk[36 * (size_t)blk + e];
-        }
-    } else if (blk < P.n_blocks + P.n_cams) {
-        const int c = blk - P.n_blocks;
-        const int f = P.cam_free[c];
-        if (f >= 0 && lane < 6) L.A[(size_t)L.n * L.ld + 6 * f + lane] = P.bs[6 * (size_t)c + lane];
+struct Sync { // the barrier of the CTA set that works on a task: the whole grid (cooperative groups) or a group counter
+    cg::grid_group* grid;
+    unsigned int* ctr;
+    unsigned int ncta, visits;
+    __device__ __forceinline__ void wait()
+    {
+        if (grid) grid->sync();
+        else group_barrier(ctr, ++visits * ncta);
     }
-}
+};
 
-__global__ void __launch_bounds__(kCT, 1) k_chol_coop(LargeSolve L)
+// Cholesky of the 64x64 block in D (lower triangle, row stride kCS) by the whole CTA, in place; LT[c][r] = L[r][c] and
+// rinv[c] = 1 / L[c][c] for the panel.  Returns true on a non-positive or non-finite pivot (uniform over the CTA).
+__device__ __forceinline__ bool cta_chol64(double* D, double* LT, double* rinv, int* s_fail, int tid)
 {
-    cg::grid_group grid = cg::this_grid();
-    extern __shared__ __align__(16) double smd[];
-    double* const D = smd;                   // [kCB][kCS]  tile buffer (trailing update, backward substitution)
-    double* const LT = D + kCB * kCS;        // [kCB][kCS]  LT[c][r] = L_kk[r][c]
-    double* const T2 = LT + kCB * kCS;       // [kCB][kCS]  second tile of the trailing update
-    double* const rinv = T2 + kCB * kCS;     // [kCB]       1 / L_kk[c][c]
-    double* const colb = rinv + kCB;         // [2][kCB]    column exchange of warp_chol32; y_b of the backward substitution
-    double* const red = colb + 2 * kCB;      // [4][kCB]    partial sums of the backward substitution
-    __shared__ int s_fail;
-
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int n = L.n, ld = L.ld;
-    const int G = gridDim.x;
-    double* const A = L.A; // written and re-read across grid barriers: no __restrict__
-    const int tx = tid & 15, ty = tid >> 4;
-    const int nblk = (n + kCB - 1) / kCB;
-    int* const flags = reinterpret_cast<int*>(L.Dd + (size_t)nblk * kCB * kCB); // [nblk] x_b published
-    if (tid == 0) s_fail = 0;
-    if (blockIdx.x == 0)
-        for (int i = tid; i < nblk; i += kCT) flags[i] = 0; // visible to everybody after the first grid barrier
-
-    for (int j0 = 0; j0 < n; j0 += kCB) {
-        const int nb = min(kCB, n - j0);
-        PROF(j0 / kCB, 0);
-        // ---------------- P: diagonal block, redundantly in every CTA ----------------
-        // 64x64 = [A11 .; A21 A22] in 32x32 quarters: warp 0 factorises A11 in registers (one row per
-        // lane, shuffles only: no block barrier inside the column chain), all warps solve
-        // L21 = A21 L11^-T and update A22 -= L21 L21^T, warp 0 factorises A22.
-        for (int idx = tid; idx < kCB * kCB; idx += kCT) {
-            const int rr = idx >> 6, c = idx & 63;
-            D[rr * kCS + c] = (rr < nb && c <= rr) ? A[(size_t)(j0 + rr) * ld + j0 + c] : (rr == c ? 1.0 : 0.0);
+#pragma unroll 1
+    for (int c0 = 0; c0 < kCB; c0 += 8) {
+        if (tid == 0) { // 8x8 diagonal block in registers: the pivot chain
+            double a[36];
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+#pragma unroll
+                for (int j = 0; j <= i; ++j) a[i * (i + 1) / 2 + j] = D[(c0 + i) * kCS + c0 + j];
+            bool bad = false;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const double d = a[j * (j + 1) / 2 + j];
+                bad |= !(d > 0.0) || !(d < 1.7e308);
+                const double inv = rsqrt(d);
+                a[j * (j + 1) / 2 + j] = d * inv;
+                rinv[c0 + j] = inv;
+#pragma unroll
+                for (int i = j + 1; i < 8; ++i) a[i * (i + 1) / 2 + j] *= inv;
+#pragma unroll
+                for (int i = j + 1; i < 8; ++i)
+#pragma unroll
+                    for (int k = j + 1; k <= i; ++k) a[i * (i + 1) / 2 + k] = fma(-a[i * (i + 1) / 2 + j], a[k * (k + 1) / 2 + j], a[i * (i + 1) / 2 + k]);
+            }
+            if (bad) *s_fail = 1;
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+#pragma unroll
+                for (int j = 0; j <= i; ++j) D[(c0 + i) * kCS + c0 + j] = a[i * (i + 1) / 2 + j];
         }
         __syncthreads();
-        PROF(j0 / kCB, 1);
-#pragma unroll 1
-        for (int h = 0; h < 2; ++h) {
-            const int o = 32 * h;
-            if (warp == 0) {
-                double r[32];
+        const int m = kCB - c0 - 8; // rows below the 8x8 block
+        if (tid < m) { // panel: one thread per row, x L88^T = a
+            const int r = c0 + 8 + tid;
+            double x[8];
 #pragma unroll
-                for (int k = 0; k < 32; ++k) r[k] = D[(o + lane) * kCS + o + k];
-                const bool bad = warp_chol32(r, lane, colb);
-                if (bad) s_fail = 1;
+            for (int j = 0; j < 8; ++j) x[j] = D[r * kCS + c0 + j];
 #pragma unroll
-                for (int k = 0; k < 32; ++k) {
-                    if (k <= lane) LT[(o + k) * kCS + o + lane] = r[k];
-                    if (k == lane) rinv[o + k] = 1.0 / r[k];
-                }
+            for (int j = 0; j < 8; ++j) {
+                double s = x[j];
+#pragma unroll
+                for (int t = 0; t < j; ++t) s = fma(-x[t], D[(c0 + j) * kCS + c0 + t], s);
+                x[j] = s * rinv[c0 + j];
             }
-            __syncthreads();
-            if (h == 0) {
-                PROF(j0 / kCB, 2);
-                { // L21: rows 32..63, four per warp, the four chains interleaved
-                    double a4[4];
 #pragma unroll
-                    for (int t = 0; t < 4; ++t) a4[t] = D[(32 + 4 * warp + t) * kCS + lane];
+            for (int j = 0; j < 8; ++j) D[r * kCS + c0 + j] = x[j];
+        }
+        __syncthreads();
+        for (int idx = tid; idx < m * m; idx += kCT) { // remainder -= panel panel^T (lower triangle)
+            const int rr = idx / m, cc = idx - rr * m;
+            if (cc > rr) continue;
+            const double* pr = D + (c0 + 8 + rr) * kCS + c0;
+            const double* pc = D + (c0 + 8 + cc) * kCS + c0;
+            double s = 0.0;
+#pragma unroll
+            for (int t = 0; t < 8; ++t) s = fma(pr[t], pc[t], s);
+            D[(c0 + 8 + rr) * kCS + c0 + 8 + cc] -= s;
+        }
+        __syncthreads();
+    }
+    for (int idx = tid; idx < kCB * kCB; idx += kCT) {
+        const int r = idx >> 6, c = idx & 63;
+        LT[c * kCS + r] = c <= r ? D[r * kCS + c] : 0.0;
+    }
+    __syncthreads();
+    return *s_fail != 0;
+}
+
+// row q of a step's row list: the band range, then the border range, then the right-hand side
+__device__ __forceinline__ int step_row(int q, int base, int n1, int r2b, int n2, int rhs)
+{
+    return q < n1 ? base + q : (q < n1 + n2 ? r2b + (q - n1) : rhs);
+}
+
+// Partial Cholesky of a task: eliminate its first n_elim columns.  gb / G: this CTA's index in, and the size of, the
+// CTA set that works on the task.  Returns false when a pivot failed (uniform over the set).
+__device__ bool task_factor(const CholTask& T, int gb, int G, Sync& sync, double* smd, int* s_fail, bool prof)
+{
+    double* const D = smd;                // [kCB][kCS] diagonal block, then tile buffer of the trailing update
+    double* const LT = D + kCB * kCS;     // [kCB][kCS] LT[c][r] = L_kk[r][c]
+    double* const T2 = LT + kCB * kCS;    // [kCB][kCS] second tile of the trailing update
+    double* const rinv = T2 + kCB * kCS;  // [kCB]      1 / L_kk[c][c]
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int ld = T.ld, nrows = T.nrows;
+    double* const A = T.A; // written and re-read across barriers by other CTAs: L2 loads (__ldcg), no __restrict__
+    const int tx = tid & 15, ty = tid >> 4;
+    const int nsteps = T.n_elim / kCB;
+    bool ok = true;
+    for (int k = 0; k < nsteps; ++k) {
+        const int j0 = k * kCB;
+        const int4 st = __ldg(T.steps + k);
+        const int base = j0 + kCB;
+        const int n1 = max(st.x - base, 0), r2b = st.y, n2 = max(st.z - st.y, 0);
+        PROF(prof, k, 0);
+        // ---------------- D: diagonal block, redundantly in every CTA of the set ----------------
+        for (int idx = tid; idx < kCB * kCB; idx += kCT) {
+            const int rr = idx >> 6, c = idx & 63;
+            D[rr * kCS + c] = c <= rr ? __ldcg(A + (size_t)(j0 + rr) * ld + j0 + c) : 0.0;
+        }
+        __syncthreads();
+        PROF(prof, k, 1);
+        const bool bad = cta_chol64(D, LT, rinv, s_fail, tid);
+        PROF(prof, k, 2);
+        if (bad) ok = false; // uniform over the set; the data below is garbage from here on, the barriers still match
+        if (gb == 0) { // the factor of the diagonal block, for the backward substitution
+            double* dd = T.Dd + (size_t)k * kCB * kCB;
+            for (int idx = tid; idx < kCB * kCB; idx += kCT) dd[idx] = LT[(idx & 63) * kCS + (idx >> 6)];
+        }
+        // ---------------- P: panel rows, one warp per four rows (the right-hand side row included) ----------------
+        const int nrow = n1 + n2 + 1;
+        for (int q0 = 4 * (gb * (kCT / 32) + warp); q0 < nrow; q0 += 4 * G * (kCT / 32)) {
+            double* a[4];
+            double a0[4], a1[4];
+#pragma unroll
+            for (int t = 0; t < 4; ++t) {
+                const int q = min(q0 + t, nrow - 1); // a short last group repeats its last row (not written back)
+                a[t] = A + (size_t)step_row(q, base, n1, r2b, n2, nrows) * ld + j0;
+                a0[t] = __ldcg(a[t] + lane), a1[t] = __ldcg(a[t] + lane + 32);
+            }
 #pragma unroll 4
-                    for (int c = 0; c < 32; ++c) {
-                        const double ri = rinv[c], lc = LT[c * kCS + lane];
-#pragma unroll
-                        for (int t = 0; t < 4; ++t) {
-                            const double xc = shfl_d(a4[t], c) * ri;
-                            if (lane == c) a4[t] = xc;
-                            if (lane > c) a4[t] = fma(-xc, lc, a4[t]);
-                        }
-                    }
-#pragma unroll
-                    for (int t = 0; t < 4; ++t) {
-                        D[(32 + 4 * warp + t) * kCS + lane] = a4[t];
-                        LT[lane * kCS + 32 + 4 * warp + t] = a4[t];
-                    }
-                }
-                __syncthreads();
-                PROF(j0 / kCB, 3);
-                { // A22 -= L21 L21^T, 2 x 2 entries per thread
-                    double acc2[2][2] = {};
-#pragma unroll 8
-                    for (int k = 0; k < 32; ++k) {
-                        const double u0 = D[(32 + ty) * kCS + k], u1 = D[(48 + ty) * kCS + k];
-                        const double v0 = D[(32 + tx) * kCS + k], v1 = D[(48 + tx) * kCS + k];
-                        acc2[0][0] = fma(u0, v0, acc2[0][0]), acc2[0][1] = fma(u0, v1, acc2[0][1]);
-                        acc2[1][0] = fma(u1, v0, acc2[1][0]), acc2[1][1] = fma(u1, v1, acc2[1][1]);
-                    }
-#pragma unroll
-                    for (int a = 0; a < 2; ++a)
-#pragma unroll
-                        for (int bb = 0; bb < 2; ++bb) {
-                            const int rr = 32 + ty + 16 * a, c = 32 + tx + 16 * bb;
-                            if (c <= rr) D[rr * kCS + c] -= acc2[a][bb];
-                        }
-                }
-                __syncthreads();
-                PROF(j0 / kCB, 4);
-            }
-        }
-        if (s_fail) { // uniform over the whole grid: nobody reaches another barrier
-            if (blockIdx.x == 0 && tid == 0) *L.fail = 1;
-            return;
-        }
-        PROF(j0 / kCB, 5);
-        if (blockIdx.x == 0) { // the factor of the diagonal block, for the backward substitution
-            double* dd = L.Dd + (size_t)(j0 / kCB) * kCB * kCB;
-            for (int idx = tid; idx < kCB * kCB; idx += kCT) {
-                const int rr = idx >> 6, c = idx & 63;
-                dd[idx] = (rr < nb && c <= rr) ? LT[c * kCS + rr] : 0.0;
-            }
-        }
-        // ---------------- P: panel rows, one warp per row (row n = rhs included) ----------------
-        // Only the rows inside the envelope take part: 64-row blocks up to last64[step]; below them the
-        // block column is structurally zero and stays zero (no fill outside a monotone envelope).
-        const int base = j0 + nb;
-        const int rend = min(n, (L.last64[j0 / kCB] + 1) * kCB);
-        const int nrow = max(rend - base, 0);
-        for (int qr = blockIdx.x * (kCT / 32) + warp; qr <= nrow; qr += G * (kCT / 32)) {
-            const int row = qr < nrow ? base + qr : n;
-            double* a = A + (size_t)row * ld + j0;
-            double a0 = lane < nb ? a[lane] : 0.0;
-            double a1 = lane + 32 < nb ? a[lane + 32] : 0.0;
-#pragma unroll 8
             for (int c = 0; c < 32; ++c) {
-                if (c >= nb) break;
-                const double xc = shfl_d(a0, c) * rinv[c];
-                if (lane == c) a0 = xc;
-                if (lane > c) a0 = fma(-xc, LT[c * kCS + lane], a0);
-                a1 = fma(-xc, LT[c * kCS + lane + 32], a1);
+                const double ri = rinv[c], l0 = LT[c * kCS + lane], l1 = LT[c * kCS + lane + 32];
+#pragma unroll
+                for (int t = 0; t < 4; ++t) {
+                    const double xc = shfl_d(a0[t], c) * ri;
+                    if (lane == c) a0[t] = xc;
+                    if (lane > c) a0[t] = fma(-xc, l0, a0[t]);
+                    a1[t] = fma(-xc, l1, a1[t]);
+                }
             }
-#pragma unroll 8
+#pragma unroll 4
             for (int c = 32; c < kCB; ++c) {
-                if (c >= nb) break;
-                const double xc = shfl_d(a1, c - 32) * rinv[c];
-                if (lane + 32 == c) a1 = xc;
-                if (lane + 32 > c) a1 = fma(-xc, LT[c * kCS + lane + 32], a1);
+                const double ri = rinv[c], l1 = LT[c * kCS + lane + 32];
+#pragma unroll
+                for (int t = 0; t < 4; ++t) {
+                    const double xc = shfl_d(a1[t], c - 32) * ri;
+                    if (lane + 32 == c) a1[t] = xc;
+                    if (lane + 32 > c) a1[t] = fma(-xc, l1, a1[t]);
+                }
             }
-            if (lane < nb) a[lane] = a0;
-            if (lane + 32 < nb) a[lane + 32] = a1;
+#pragma unroll
+            for (int t = 0; t < 4; ++t)
+                if (q0 + t < nrow) a[t][lane] = a0[t], a[t][lane + 32] = a1[t];
         }
-        PROF(j0 / kCB, 6);
-        grid.sync();
-        PROF(j0 / kCB, 7);
-        // ---------------- U: trailing update over 64x64 tiles of the lower triangle ----------------
-        { // tiles (ti >= tl) of the active rows, then one tile per tl for the rhs row n
-            const int nt = (nrow + kCB - 1) / kCB;
+        PROF(prof, k, 3);
+        sync.wait();
+        PROF(prof, k, 4);
+        // ---------------- U: trailing update over 64x64 tiles of the lower triangle of the step's rows ----------------
+        { // tiles (ti >= tl) of the active row tiles, then one tile per tl for the right-hand side row
+            const int n1t = n1 / kCB, nt = n1t + n2 / kCB;
             const int ntri = nt * (nt + 1) / 2;
             const int ntile = ntri + nt;
-            double* const Pi = D;   // the diagonal-block buffers are free again
+            double* const Pi = D; // the diagonal-block buffers are free again
             double* const Pl = T2;
-            for (int t = blockIdx.x; t < ntile; t += G) {
+            for (int t = gb; t < ntile; t += G) {
                 const bool rhs = t >= ntri;
                 int ti = 0, tl = t - ntri;
                 if (!rhs) {
@@ -279,107 +252,263 @@ __global__ void __launch_bounds__(kCT, 1) k_chol_coop(LargeSolve L)
                     while (ti * (ti + 1) / 2 > t) --ti;
                     tl = t - ti * (ti + 1) / 2;
                 }
-                const int i0 = rhs ? n : base + kCB * ti, l0 = base + kCB * tl;
-                const int ni = rhs ? 1 : min(kCB, n - i0); // valid rows of the tile
+                const int i0 = rhs ? nrows : (ti < n1t ? base + kCB * ti : r2b + kCB * (ti - n1t));
+                const int l0 = tl < n1t ? base + kCB * tl : r2b + kCB * (tl - n1t);
+                const int ni = rhs ? 1 : kCB; // valid rows of the tile
                 __syncthreads();
                 for (int idx = tid; idx < kCB * kCB; idx += kCT) {
                     const int r = idx >> 6, c = idx & 63;
-                    Pi[r * kCS + c] = (r < ni && c < nb) ? A[(size_t)(i0 + r) * ld + j0 + c] : 0.0;
-                    Pl[r * kCS + c] = (l0 + r < n && c < nb) ? A[(size_t)(l0 + r) * ld + j0 + c] : 0.0;
+                    Pi[r * kCS + c] = r < ni ? __ldcg(A + (size_t)(i0 + r) * ld + j0 + c) : 0.0;
+                    Pl[r * kCS + c] = __ldcg(A + (size_t)(l0 + r) * ld + j0 + c);
                 }
                 __syncthreads();
                 double acc[4][4] = {};
 #pragma unroll 4
-                for (int k = 0; k < kCB; ++k) {
+                for (int kk = 0; kk < kCB; ++kk) {
                     double av[4], bv[4];
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) av[i] = Pi[(ty + 16 * i) * kCS + k];
+                    for (int i = 0; i < 4; ++i) av[i] = Pi[(ty + 16 * i) * kCS + kk];
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) bv[i] = Pl[(tx + 16 * i) * kCS + k];
+                    for (int i = 0; i < 4; ++i) bv[i] = Pl[(tx + 16 * i) * kCS + kk];
 #pragma unroll
                     for (int i = 0; i < 4; ++i)
 #pragma unroll
                         for (int j = 0; j < 4; ++j) acc[i][j] = fma(av[i], bv[j], acc[i][j]);
                 }
+                const bool diag_tile = !rhs && ti == tl;
 #pragma unroll
                 for (int i = 0; i < 4; ++i)
 #pragma unroll
                     for (int j = 0; j < 4; ++j) {
-                        const int r = i0 + ty + 16 * i, c = l0 + tx + 16 * j;
-                        if (ty + 16 * i < ni && c < n && c <= r) A[(size_t)r * ld + c] -= acc[i][j];
+                        const int r = ty + 16 * i, c = tx + 16 * j;
+                        if (r < ni && (!diag_tile || c <= r)) {
+                            double* e = A + (size_t)(i0 + r) * ld + l0 + c;
+                            *e = __ldcg(e) - acc[i][j];
+                        }
                     }
             }
         }
-        PROF(j0 / kCB, 8);
-        grid.sync();
-        PROF(j0 / kCB, 9);
+        PROF(prof, k, 5);
+        sync.wait();
+        PROF(prof, k, 6);
     }
+    return ok;
+}
 
-    // ---------------- backward substitution  L^T x = y, pipelined over the CTAs with flags ----------------
-    // Block b of x belongs to CTA (nblk - 1 - b) mod G.  Its owner subtracts L[b', b]^T x_b' for every
-    // b' > b as soon as x_b' is published (the L tile is already in registers by then), solves the
-    // 64x64 triangle with one warp and publishes x_b.  Owners take their blocks top down and only
-    // ever wait for higher blocks, and all CTAs are co-resident (cooperative launch): no deadlock.
+// Backward substitution  L^T x = y  of a task's eliminated columns, pipelined over the CTAs of its set with flags.
+// Block b of x belongs to CTA (nb - 1 - b) mod G.  Its owner subtracts L[b', b]^T x_b' for every row block b' the
+// elimination step b touched (border rows: x given and flagged before the call) as soon as x_b' is published (the L tile
+// is already in registers by then), solves the 64x64 triangle with one warp and publishes x_b.  Owners take their
+// blocks top down and only ever wait for higher blocks, and all CTAs are resident (cooperative launch): no deadlock.
+__device__ void task_backward(const CholTask& T, int gb, int G, double* smd)
+{
+    double* const D = smd;                          // [kCB][kCS] L_bb
+    double* const colb = smd + 3 * kCB * kCS + kCB; // [2][kCB]   y_b
+    double* const red = colb + 2 * kCB;             // [4][kCB]   partial sums
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int ld = T.ld, nrows = T.nrows;
+    const double* const A = T.A;
+    const int nb = T.n_elim / kCB;
     const int q = tid >> 6, cc = tid & 63;
-    for (int b = nblk - 1 - (int)blockIdx.x; b >= 0; b -= G) {
+    for (int b = nb - 1 - gb; b >= 0; b -= G) {
         const int cb = b * kCB;
-        const int nbb = min(kCB, n - cb);
-        { // L_bb (row-major) and the reciprocals of its diagonal
-            const double* dd = L.Dd + (size_t)b * kCB * kCB;
+        const int4 st = __ldg(T.steps + b);
+        { // L_bb (row-major)
+            const double* dd = T.Dd + (size_t)b * kCB * kCB;
             for (int idx = tid; idx < kCB * kCB; idx += kCT) D[(idx >> 6) * kCS + (idx & 63)] = __ldcg(dd + idx);
         }
         double* const ysh = colb; // y_b (fetched before the waits)
-        if (tid < kCB) ysh[tid] = tid < nbb ? __ldcg(A + (size_t)n * ld + cb + tid) : 0.0;
+        if (tid < kCB) ysh[tid] = __ldcg(A + (size_t)nrows * ld + cb + tid);
         double acc = 0.0;
-        for (int bp = min(nblk - 1, L.last64[b]); bp > b; --bp) { // blocks below the envelope are zero
-            const int rb = bp * kCB;
-            const int nrow = min(kCB, n - rb);
+        // the row blocks step b touched, highest first: the border range, then the band range
+        const int nb2 = max(st.z - st.y, 0) / kCB, nb1 = max(st.x - (cb + kCB), 0) / kCB;
+        for (int i = nb1 + nb2 - 1; i >= 0; --i) {
+            const int rb = i >= nb1 ? st.y + kCB * (i - nb1) : cb + kCB + kCB * i;
             double t[16];
 #pragma unroll
-            for (int jj = 0; jj < 16; ++jj) {
-                const int j = q * 16 + jj;
-                t[jj] = j < nrow ? __ldcg(A + (size_t)(rb + j) * ld + cb + cc) : 0.0;
-            }
+            for (int jj = 0; jj < 16; ++jj) t[jj] = __ldcg(A + (size_t)(rb + q * 16 + jj) * ld + cb + cc);
             if (tid == 0) {
-                while (*reinterpret_cast<volatile int*>(flags + bp) == 0) {}
+                const int* f = T.flags + rb / kCB;
+                int v;
+                do {
+                    asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
+                } while (v == 0);
                 __threadfence();
             }
             __syncthreads();
 #pragma unroll
-            for (int jj = 0; jj < 16; ++jj) {
-                const int j = q * 16 + jj;
-                const double xj = j < nrow ? __ldcg(L.x + rb + j) : 0.0;
-                acc = fma(t[jj], xj, acc);
-            }
+            for (int jj = 0; jj < 16; ++jj) acc = fma(t[jj], __ldcg(T.x + rb + q * 16 + jj), acc);
         }
         red[q * kCB + cc] = acc;
         __syncthreads();
         if (warp == 0) {
             // reciprocals of the diagonal, one pair per lane: the serial chain below multiplies
-            const double ri0 = lane < nbb ? 1.0 / D[lane * kCS + lane] : 0.0;
-            const double ri1 = lane + 32 < nbb ? 1.0 / D[(lane + 32) * kCS + lane + 32] : 0.0;
-            double y0 = lane < nbb ? ysh[lane] - (red[lane] + red[kCB + lane] + red[2 * kCB + lane] + red[3 * kCB + lane]) : 0.0;
-            double y1 = lane + 32 < nbb ? ysh[lane + 32] - (red[lane + 32] + red[kCB + lane + 32] + red[2 * kCB + lane + 32] + red[3 * kCB + lane + 32]) : 0.0;
-            for (int j = nbb - 1; j >= 32; --j) {
+            const double ri0 = 1.0 / D[lane * kCS + lane];
+            const double ri1 = 1.0 / D[(lane + 32) * kCS + lane + 32];
+            double y0 = ysh[lane] - (red[lane] + red[kCB + lane] + red[2 * kCB + lane] + red[3 * kCB + lane]);
+            double y1 = ysh[lane + 32] - (red[lane + 32] + red[kCB + lane + 32] + red[2 * kCB + lane + 32] + red[3 * kCB + lane + 32]);
+            for (int j = kCB - 1; j >= 32; --j) {
                 const double xj = shfl_d(y1, j - 32) * shfl_d(ri1, j - 32);
                 if (lane + 32 == j) y1 = xj;
                 if (lane + 32 < j) y1 = fma(-xj, D[j * kCS + lane + 32], y1);
                 y0 = fma(-xj, D[j * kCS + lane], y0);
             }
-            for (int j = min(nbb, 32) - 1; j >= 0; --j) {
+            for (int j = 31; j >= 0; --j) {
                 const double xj = shfl_d(y0, j) * shfl_d(ri0, j);
                 if (lane == j) y0 = xj;
                 if (lane < j) y0 = fma(-xj, D[j * kCS + lane], y0);
             }
-            if (lane < nbb) L.x[cb + lane] = y0;
-            if (lane + 32 < nbb) L.x[cb + lane + 32] = y1;
+            T.x[cb + lane] = y0;
+            T.x[cb + lane + 32] = y1;
             __threadfence();
             __syncwarp();
-            if (lane == 0) *reinterpret_cast<volatile int*>(flags + b) = 1;
+            if (lane == 0) asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(T.flags + b), "r"(1) : "memory");
         }
         __syncthreads();
     }
-    PROF(nblk, 0);
+}
+
+} // namespace
+
+// zero the envelope of every task matrix (row r: columns 64 * first64[r / 64] .. r; the right-hand side row: all), put the
+// identity on the padding columns, and reset flags, barrier counters and the failure flag
+__global__ void __launch_bounds__(256) k_dense_zero(LargeSolve L)
+{
+    int t = 0;
+    const int g = blockIdx.x;
+    while (g >= L.row_ptr[t + 1]) ++t;
+    const CholTask& T = L.tasks[t];
+    const int r = g - L.row_ptr[t];
+    double* row = T.A + (size_t)r * T.ld;
+    if (r == T.nrows) {
+        for (int c = threadIdx.x; c < T.nrows; c += blockDim.x) row[c] = 0.0;
+        for (int c = threadIdx.x; c < T.nrows / kCB; c += blockDim.x) T.flags[c] = 0;
+        if (threadIdx.x == 0) L.bars[t] = 0u;
+        if (t == 0 && threadIdx.x == 0) *L.fail = 0;
+    } else {
+        const int c0 = kCB * T.first64[r / kCB];
+        const bool pad = r >= T.n_real && r < T.n_elim;
+        for (int c = c0 + threadIdx.x; c <= r; c += blockDim.x) row[c] = (pad && c == r) ? 1.0 : 0.0;
+    }
+}
+
+// one warp per stored S block: scatter the packed 6x6 blocks (and the rhs) into the task matrices.  Block (I, J), I >= J in
+// free-pose order: both poses in the same task -> its lower triangle; one of them in a separator -> the border rows of the
+// OTHER pose's segment (transposed when the separator pose is J: the separator precedes the segment in the chain).
+__global__ void __launch_bounds__(256) k_dense_assemble(DevProblem P, LargeSolve L)
+{
+    const int lane = threadIdx.x & 31;
+    const int blk = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (blk < P.n_blocks) {
+        const int2 ij = P.blk_ij[blk];
+        const int tI = L.cam_task[ij.x], tJ = L.cam_task[ij.y];
+        const int oI = L.cam_off[ij.x], oJ = L.cam_off[ij.y];
+        const CholTask* T;
+        int r0, c0;
+        bool transpose = false;
+        if (tI == tJ) {
+            T = L.tasks + tI, r0 = oI, c0 = oJ;
+        } else if (tI == L.n_seg) { // I in separator s, J in segment s: the separator is the segment's RIGHT border
+            T = L.tasks + tJ, r0 = T->n_elim + T->sL + (oI - L.sep_cols * L.cam_sep[ij.x]), c0 = oJ;
+        } else { // J in separator s, I in segment s + 1: the separator is the segment's LEFT border
+            T = L.tasks + tI, r0 = T->n_elim + (oJ - L.sep_cols * L.cam_sep[ij.y]), c0 = oI, transpose = true;
+        }
+        for (int e = lane; e < 36; e += 32) {
+            const int r = e / 6, c = e - 6 * r;
+            const double v = P.S_blk[36 * (size_t)blk + e];
+            if (transpose) T->A[(size_t)(r0 + c) * T->ld + c0 + r] = v;
+            else T->A[(size_t)(r0 + r) * T->ld + c0 + c] = v;
+        }
+    } else if (blk < P.n_blocks + P.n_cams) {
+        const int c = blk - P.n_blocks;
+        const int f = P.cam_free[c];
+        if (f >= 0 && lane < 6) {
+            const CholTask& T = L.tasks[L.cam_task[f]];
+            T.A[(size_t)T.nrows * T.ld + L.cam_off[f] + lane] = P.bs[6 * (size_t)c + lane];
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kCT, 1) k_chol_coop(LargeSolve L)
+{
+    cg::grid_group grid = cg::this_grid();
+    extern __shared__ __align__(16) double smd[];
+    __shared__ int s_fail;
+    const int tid = threadIdx.x;
+    const int G = gridDim.x, bid = blockIdx.x;
+    const int P = L.n_seg;
+    if (tid == 0) s_fail = 0;
+    __syncthreads();
+    const CholTask& top = L.tasks[P];
+    int mine = -1; // the segment this CTA works on in phases 1 and 4
+    for (int t = 0; t < P; ++t)
+        if (bid >= L.tasks[t].cta0 && bid < L.tasks[t].cta0 + L.tasks[t].ncta) mine = t;
+    bool ok = true;
+    if (P > 0) {
+        // ---------------- phase 1: the interior segments, each on its own CTA group ----------------
+        if (mine >= 0) {
+            const CholTask& T = L.tasks[mine];
+            Sync s{ nullptr, L.bars + mine, (unsigned)T.ncta, 0u };
+            ok = task_factor(T, bid - T.cta0, T.ncta, s, smd, &s_fail, false);
+        }
+        grid.sync();
+        // ---------------- phase 2: border blocks of the segments -> separator system, in a fixed order ----------------
+        const int s = L.sep_cols;
+        const long long per = (long long)s * s, tot = (long long)(P - 1) * (2 * per + s);
+        for (long long idx = (long long)bid * kCT + tid; idx < tot; idx += (long long)G * kCT) {
+            const int j = (int)(idx / (2 * per + s));
+            const long long rem = idx - (long long)j * (2 * per + s);
+            const CholTask& Ta = L.tasks[j];     // separator j is the RIGHT border of segment j ...
+            const CholTask& Tb = L.tasks[j + 1]; // ... and the LEFT border of segment j + 1
+            const int ra = Ta.n_elim + Ta.sL, rbb = Tb.n_elim;
+            if (rem < per) { // diagonal block of separator j (lower triangle)
+                const int r = (int)(rem / s), c = (int)(rem - (long long)r * s);
+                if (c <= r) {
+                    double* e = top.A + (size_t)(s * j + r) * top.ld + s * j + c;
+                    *e = (*e + __ldcg(Ta.A + (size_t)(ra + r) * Ta.ld + ra + c)) + __ldcg(Tb.A + (size_t)(rbb + r) * Tb.ld + rbb + c);
+                }
+            } else if (rem < 2 * per) { // coupling of separator j with separator j - 1: fill of segment j
+                if (j > 0) {
+                    const long long q = rem - per;
+                    const int r = (int)(q / s), c = (int)(q - (long long)r * s);
+                    double* e = top.A + (size_t)(s * j + r) * top.ld + s * (j - 1) + c;
+                    *e += __ldcg(Ta.A + (size_t)(ra + r) * Ta.ld + Ta.n_elim + c);
+                }
+            } else { // right-hand side
+                const int c = (int)(rem - 2 * per);
+                double* e = top.A + (size_t)top.nrows * top.ld + s * j + c;
+                *e = (*e + __ldcg(Ta.A + (size_t)Ta.nrows * Ta.ld + ra + c)) + __ldcg(Tb.A + (size_t)Tb.nrows * Tb.ld + rbb + c);
+            }
+        }
+        grid.sync();
+    }
+    // ---------------- phase 3: T (the separator system, or the whole matrix) on every CTA ----------------
+    {
+        Sync s{ &grid, nullptr, (unsigned)G, 0u };
+        const bool okT = task_factor(top, bid, G, s, smd, &s_fail, true);
+        ok = ok && okT;
+        PROF(true, top.n_elim / kCB, 0);
+        task_backward(top, bid, G, smd);
+        PROF(true, top.n_elim / kCB, 1);
+    }
+    if (!ok && tid == 0) *L.fail = 1;
+    if (P > 0) {
+        grid.sync();
+        // ---------------- phase 4: separator values into the borders, then the interiors ----------------
+        if (mine >= 0) {
+            const CholTask& T = L.tasks[mine];
+            const int gb = bid - T.cta0;
+            const int s = L.sep_cols;
+            for (int i = gb * kCT + tid; i < T.sL + T.sR; i += T.ncta * kCT) {
+                const int sep = i < T.sL ? mine - 1 : mine;
+                T.x[T.n_elim + i] = __ldcg(top.x + s * sep + (i < T.sL ? i : i - T.sL));
+            }
+            for (int i = gb * kCT + tid; i < (T.sL + T.sR) / kCB; i += T.ncta * kCT) T.flags[T.n_elim / kCB + i] = 1;
+            Sync sy{ nullptr, L.bars + mine, (unsigned)T.ncta, (unsigned)(2 * (T.n_elim / kCB)) }; // continues the counter of phase 1
+            sy.wait();
+            task_backward(T, gb, T.ncta, smd);
+        }
+    }
 }
 
 __global__ void __launch_bounds__(256) k_large_finish(DevProblem P, LargeSolve L)
@@ -390,11 +519,16 @@ __global__ void __launch_bounds__(256) k_large_finish(DevProblem P, LargeSolve L
     const int fail = *L.fail;
     const int cur = st.cur, cand = cur ^ 1;
     const int tid = threadIdx.x;
+    double ss = 0.0;
     for (int c = tid; c < P.n_cams; c += blockDim.x) {
         const int f = P.cam_free[c];
         double d[6];
-        for (int r = 0; r < 6; ++r) d[r] = (f >= 0 && !fail) ? L.x[6 * f + r] : 0.0;
-        for (int r = 0; r < 6; ++r) P.dp[6 * (size_t)c + r] = d[r];
+        for (int r = 0; r < 6; ++r) d[r] = 0.0;
+        if (f >= 0 && !fail) {
+            const double* x = L.tasks[L.cam_task[f]].x + L.cam_off[f];
+            for (int r = 0; r < 6; ++r) d[r] = x[r], L.x[6 * f + r] = x[r];
+        }
+        for (int r = 0; r < 6; ++r) P.dp[6 * (size_t)c + r] = d[r], ss += d[r] * d[r];
         const double* pc = P.pose[cur] + 7 * (size_t)c;
         double* pn = P.pose[cand] + 7 * (size_t)c;
         if (f >= 0 && !fail) pose_oplus(d, pc, pn);
@@ -402,9 +536,6 @@ __global__ void __launch_bounds__(256) k_large_finish(DevProblem P, LargeSolve L
             for (int r = 0; r < 7; ++r) pn[r] = pc[r];
         write_cam_rt(pn, P.cam_rt[cand] + 12 * (size_t)c);
     }
-    double ss = 0.0;
-    if (!fail)
-        for (int i = tid; i < L.n; i += blockDim.x) ss += L.x[i] * L.x[i];
     sh[tid] = ss;
     __syncthreads();
     for (int s = 128; s > 0; s >>= 1) {
@@ -417,18 +548,16 @@ __global__ void __launch_bounds__(256) k_large_finish(DevProblem P, LargeSolve L
     }
 }
 
-} // namespace
+int large_solve_max_n() { return 6 * 5000; } // unpartitioned: 7.2 GB of dense lower triangle; nothing else limits n
 
-size_t large_solve_diag_doubles(int n)
-{ // the factorised diagonal blocks, followed by one int flag per block (backward substitution)
-    const size_t nblk = (size_t)((n + kCB - 1) / kCB);
-    return nblk * kCB * kCB + (nblk + 1) / 2;
+int large_solve_cta_count()
+{
+    static PerDeviceOnce once;
+    return once.sm_count();
 }
 
-int large_solve_max_n() { return 6 * 5000; } // 7.2 GB of dense lower triangle; nothing else limits n
-
-// the factorisation + both substitutions alone (A assembled, x out); cooperative launch: the
-// runtime guarantees that all CTAs are co-resident, which the grid barriers need
+// the factorisation + both substitutions alone (matrices assembled, x out); cooperative launch: the runtime guarantees
+// that all CTAs are co-resident, which the grid and group barriers need
 int launch_chol_coop(const LargeSolve& L, cudaStream_t st)
 {
     static PerDeviceOnce once;
@@ -444,10 +573,16 @@ int launch_chol_coop(const LargeSolve& L, cudaStream_t st)
     return cudaLaunchKernelEx(&cfg, k_chol_coop, L) == cudaSuccess ? 1 : 0;
 }
 
+int launch_dense_zero(const LargeSolve& L, cudaStream_t st)
+{
+    k_dense_zero<<<L.total_rows, 256, 0, st>>>(L);
+    return 1;
+}
+
 int launch_solve_large(const DevProblem& P, const LargeSolve& L, cudaStream_t st)
 {
     const long long warps = (long long)P.n_blocks + P.n_cams;
-    k_dense_zero<<<L.n, 256, 0, st>>>(L);
+    k_dense_zero<<<L.total_rows, 256, 0, st>>>(L);
     k_dense_assemble<<<(unsigned)((warps * 32 + 255) / 256), 256, 0, st>>>(P, L);
     const int k = launch_chol_coop(L, st);
     k_large_finish<<<1, 256, 0, st>>>(P, L);

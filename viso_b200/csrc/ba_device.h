@@ -176,15 +176,42 @@ struct DevProblem {
     double lambda_scale; // 1 on the rank that adds lambda to diag(S) (rank 0), else 0
 };
 
-struct LargeSolve { // dense path for one problem with n > kSmallMaxN
-    int32_t n;      // 6 * free poses
-    int32_t ld;     // leading dimension (doubles) of A, row-major, rows 0..n (row n = rhs)
-    double* A;
-    double* Dd;     // factorised diagonal blocks, [ceil(n/64)][64][64] (A's own are stale)
-    double* x;      // [n]
-    int32_t* fail;  // [1]
-    const int32_t* first64; // [ceil(n/64)] envelope: first 64-column block of every 64-row block (monotone)
-    const int32_t* last64;  // [ceil(n/64)] last 64-row block with first64 <= k: the rows step k touches
+// ---- reduced camera system of ONE large problem (n > kSmallMaxN): LinearSolverDense, reference bundle_adjuster.h:113-114 ----
+// The free poses are cut into P interior SEGMENTS separated by P - 1 SEPARATORS that are at least as wide as the
+// co-visibility span (no S block couples two different interiors).  In the order [interiors ..., separators ...] the matrix
+// is block-diagonal with a border; segment i is the partial Cholesky of
+//     M_i = [ A_ii            ]   rows: interior i (padded to 64), then the LEFT separator's rows, then the RIGHT one's,
+//           [ B_i   0 (fill)  ]   then the right-hand side as one more row
+// over its first n_elim columns, all segments concurrently on disjoint CTA groups; what is left in the border block is the
+// segment's contribution to the separator system T (block tridiagonal), which every CTA then factorises together; the
+// interiors are back-substituted concurrently again.  P = 0: no partition, T is the whole matrix (dense / envelope).
+constexpr int kCholBlock = 64; // every size below is a multiple of it (identity padding)
+
+struct CholTask {
+    double* A;              // row-major [nrows + 1][ld]; row nrows is the right-hand side; only the envelope is touched
+    double* Dd;             // factorised diagonal blocks, [n_elim / 64][64][64] (A's own are stale)
+    double* x;              // [nrows] solution; rows >= n_elim (the border) are inputs of the back substitution
+    int32_t* flags;         // [nrows / 64] block of x published
+    const int4* steps;      // [n_elim / 64] rows below the diagonal block that step k touches: [64 (k + 1), .x) and [.y, .z)
+    const int32_t* first64; // [nrows / 64] first 64-column block of every 64-row block (what gets zeroed)
+    int32_t ld, n_elim, nrows, n_real; // columns [n_real, n_elim) are identity padding
+    int32_t cta0, ncta;     // the CTA group that factorises it
+    int32_t sL, sR;         // border rows: [n_elim, n_elim + sL) left separator, [n_elim + sL, nrows) right separator
+};
+
+struct LargeSolve {
+    int32_t n;              // 6 * free poses
+    int32_t n_seg;          // interior segments P (0: unpartitioned)
+    int32_t sep_cols;       // columns of one separator (multiple of 64)
+    int32_t total_rows;     // sum over the tasks of nrows + 1 (grid of the zeroing kernel)
+    const CholTask* tasks;  // device array [n_seg + 1]; the last one is T (the separator system, or the whole matrix)
+    const int32_t* row_ptr; // [n_seg + 2] prefix of nrows + 1 over the tasks
+    const int32_t* cam_task;// [free poses] task that eliminates the pose (separator poses: n_seg)
+    const int32_t* cam_off; // [free poses] first column of the pose inside that task
+    const int32_t* cam_sep; // [free poses] separator index of the pose or -1
+    double* x;              // [n] the step, free-pose order
+    int32_t* fail;          // [1]
+    unsigned int* bars;     // [n_seg + 1] group barrier counters
 };
 
 // launchers (all asynchronous on `st`); each returns the number of kernels it launched
@@ -199,8 +226,8 @@ int launch_reduce(const DevProblem& P, int which, cudaStream_t st); // 0/2: cost
 int launch_lm_init(const DevProblem& P, double tau, double lambda_init, cudaStream_t st);
 int launch_solve_small(const DevProblem& P, int max_n, cudaStream_t st);
 int launch_solve_large(const DevProblem& P, const LargeSolve& L, cudaStream_t st); // ba_dense.cu
-size_t large_solve_diag_doubles(int n); // size of LargeSolve::Dd
 int large_solve_max_n();                // largest n the dense solver takes
+int large_solve_cta_count();            // CTAs of the cooperative solve kernel on the current device (one per SM)
 int launch_update(const DevProblem& P, cudaStream_t st);
 int launch_decide(const DevProblem& P, cudaStream_t st);
 int launch_eval_cost(const DevProblem& P, cudaStream_t st); // cost of current state -> cost_pt

@@ -9,6 +9,7 @@
 #include "../../include/viso_ba.h"
 #include "ba_device.h"
 #include "ba_setup.h"
+#include "ba_solve_plan.h"
 
 #include <cuda_runtime.h>
 #include <dlfcn.h>
@@ -394,6 +395,7 @@ extern "C" void viso_ba_default_config(viso_ba_config* c)
     c->fix_first_pose = 1;
     c->use_cuda_graph = 1;
     c->path = 0;
+    c->solver_segments = 0;
 }
 
 extern "C" int32_t viso_ba_create(const viso_ba_config* cfg, viso_ba** out)
@@ -821,7 +823,7 @@ struct Built {
     std::vector<int32_t> diag_items, block_item_ptr, block_cam;
     std::vector<int32_t> diag_blk;   // [Nc] S block of the pose's diagonal, -1 for fixed poses
     std::vector<int32_t> blk_ij;     // 2 per S block: (I, J) free indices (compact storage, large solver only)
-    std::vector<int32_t> first64, last64; // envelope of the dense matrix in 64-row blocks (large solver only)
+    SolvePlan plan;                  // segments / separators / elimination steps of the large solver (large solver only)
     bool compact = false;            // S blocks stored for co-visible pose pairs only
     std::vector<int32_t> chunks;     // 4 per chunk
     std::vector<int32_t> prob_chunk_ptr;
@@ -988,9 +990,6 @@ int32_t build_general(viso_ba* h, Built& b)
             }
         }
         remap.assign((size_t)b.n_blocks, -1);
-        const int nb64 = (b.max_n + 63) / 64;
-        b.first64.resize((size_t)nb64);
-        for (int i = 0; i < nb64; ++i) b.first64[(size_t)i] = i;
         int32_t k = 0;
         for (int32_t I = 0; I < nf; ++I)
             for (int32_t J = 0; J <= I; ++J)
@@ -998,16 +997,12 @@ int32_t build_general(viso_ba* h, Built& b)
                     remap[(size_t)I * (I + 1) / 2 + J] = k++;
                     b.blk_ij.push_back(I);
                     b.blk_ij.push_back(J);
-                    const int cb = 6 * J / 64;
-                    for (int rb = 6 * I / 64; rb <= (6 * I + 5) / 64; ++rb) b.first64[(size_t)rb] = std::min(b.first64[(size_t)rb], cb);
                 }
-        // monotone envelope: a row block may not start right of the blocks below it, so that the
-        // active rows of every elimination step are one contiguous range
-        for (int i = nb64 - 2; i >= 0; --i) b.first64[(size_t)i] = std::min(b.first64[(size_t)i], b.first64[(size_t)i + 1]);
-        b.last64.resize((size_t)nb64);
-        for (int kk = 0, i = 0; kk < nb64; ++kk) {
-            while (i + 1 < nb64 && b.first64[(size_t)i + 1] <= kk) ++i;
-            b.last64[(size_t)kk] = std::max(i, kk);
+        // how the solver cuts the pose chain (ba_solve_plan.h): config.solver_segments 0 = auto (up to 8 interior segments
+        // when the co-visibility span is small against the chain), 1 = never, k >= 2 = up to k whenever the structure allows
+        {
+            const int seg = h->cfg.solver_segments;
+            b.plan = make_solve_plan(nf, b.blk_ij, large_solve_cta_count(), seg == 0 ? 8 : seg, seg >= 2);
         }
         b.n_blocks = k;
         b.prob_tri0[1] = k;
@@ -1106,7 +1101,7 @@ namespace {
 struct DevPtrs { // everything carved out of the arena, in one place so that the dry run and the
                  // real pass cannot diverge
     int32_t *pt_ptr, *pt_prob, *obs_cam, *cam_free, *cam_prob, *prob_cam0, *prob_tri0, *prob_nfree;
-    int32_t *diag_blk, *first64, *last64;
+    int32_t* diag_blk;
     int2* blk_ij;
     float2* obs_uv;
     int2* pairs;
@@ -1126,8 +1121,12 @@ struct DevPtrs { // everything carved out of the arena, in one place so that the
     double *rec, *ptinfo, *cost_pt, *cost_new_pt, *scale_pt, *item_part, *S_blk, *bs, *dp, *chunk_part, *prob_sums;
     unsigned long long* maxdiag_bits;
     int32_t* n_active;
-    double *LA, *LDd, *Lx;
-    int32_t* Lfail;
+    // large solver (ba_dense.cu): task matrices / diagonal factors / solutions in one block of doubles, tables in one of ints
+    double *Ldoubles, *Lx;
+    int32_t *Lints, *Lfail;
+    int4* Lsteps;
+    CholTask* Ltasks;
+    unsigned int* Lbars;
 };
 
 constexpr int kMaxIterStats = 4096;
@@ -1152,8 +1151,6 @@ void carve(Arena& A, DevPtrs& d, int64_t Nc, int64_t Np, int64_t Ne, int64_t B, 
     d.block_cam = A.take<int32_t>((size_t)b.n_blocks);
     d.diag_blk = A.take<int32_t>((size_t)Nc);
     d.blk_ij = A.take<int2>(b.blk_ij.size() / 2);
-    d.first64 = A.take<int32_t>(b.first64.size());
-    d.last64 = A.take<int32_t>(b.last64.size());
     d.chunks = A.take<int4>(b.chunks.size() / 4);
     d.prob_chunk_ptr = A.take<int32_t>((size_t)B + 1);
     d.tiles = A.take<WinTile>((size_t)b.tiles_max);
@@ -1194,20 +1191,76 @@ void carve(Arena& A, DevPtrs& d, int64_t Nc, int64_t Np, int64_t Ne, int64_t B, 
     d.maxdiag_bits = A.take<unsigned long long>((size_t)B);
     d.n_active = A.take<int32_t>(2); // [1]: tiles of the active problems (k_win_active_tiles)
     if (large) {
-        const size_t n = (size_t)b.max_n;
-        d.LA = A.take<double>((n + 1) * (size_t)ldL);
-        d.LDd = A.take<double>(large_solve_diag_doubles((int)n));
-        d.Lx = A.take<double>(n);
+        size_t nd = 0, ni = 0, ns = 0;
+        for (const PlanTask& t : b.plan.tasks) {
+            nd += t.a_doubles() + t.dd_doubles() + (size_t)t.nrows;
+            ni += 2 * (size_t)(t.nrows / 64); // flags, first64
+            ns += (size_t)(t.n_elim / 64);
+        }
+        ni += 3 * (size_t)b.plan.nf + b.plan.tasks.size() + 1; // cam_task, cam_off, cam_sep, row_ptr
+        d.Ldoubles = A.take<double>(nd);
+        d.Lx = A.take<double>((size_t)b.max_n);
+        d.Lints = A.take<int32_t>(ni);
+        d.Lsteps = A.take<int4>(ns);
+        d.Ltasks = A.take<CholTask>(b.plan.tasks.size());
+        d.Lbars = A.take<unsigned int>(b.plan.tasks.size());
         d.Lfail = A.take<int32_t>(1);
     } else {
-        d.LA = d.LDd = d.Lx = nullptr;
-        d.Lfail = nullptr;
+        d.Ldoubles = d.Lx = nullptr;
+        d.Lints = d.Lfail = nullptr;
+        d.Lsteps = nullptr, d.Ltasks = nullptr, d.Lbars = nullptr;
     }
+    (void)ldL;
 }
 
 } // namespace
 
 namespace {
+
+// large solver: the plan's tables and the task descriptors (device pointers into the arena) -> device
+int32_t upload_solve_plan(viso_ba* h, const SolvePlan& plan, const DevPtrs& d)
+{
+    const size_t nt = plan.tasks.size();
+    std::vector<CholTask> tasks(nt);
+    std::vector<int32_t> ints;
+    std::vector<int32_t> steps;
+    double* pd = d.Ldoubles;
+    int4* ps = d.Lsteps;
+    // ints layout: per task {flags, first64}, then cam_task, cam_off, cam_sep, row_ptr
+    size_t io = 0;
+    for (size_t t = 0; t < nt; ++t) {
+        const PlanTask& q = plan.tasks[t];
+        CholTask& c = tasks[t];
+        std::memset(&c, 0, sizeof(c));
+        c.A = pd, pd += q.a_doubles();
+        c.Dd = pd, pd += q.dd_doubles();
+        c.x = pd, pd += (size_t)q.nrows;
+        const size_t nb = (size_t)(q.nrows / 64);
+        c.flags = d.Lints + io, io += nb;
+        ints.insert(ints.end(), nb, 0);
+        c.first64 = d.Lints + io, io += nb;
+        ints.insert(ints.end(), q.first64.begin(), q.first64.end());
+        c.steps = ps, ps += q.n_elim / 64;
+        steps.insert(steps.end(), q.steps.begin(), q.steps.end());
+        c.ld = q.ld, c.n_elim = q.n_elim, c.nrows = q.nrows, c.n_real = q.n_real;
+        c.cta0 = q.cta0, c.ncta = q.ncta, c.sL = q.sL, c.sR = q.sR;
+    }
+    LargeSolve& L = h->L;
+    std::memset(&L, 0, sizeof(L));
+    L.n = 6 * plan.nf, L.n_seg = plan.n_seg, L.sep_cols = plan.sep_cols, L.total_rows = plan.total_rows;
+    L.tasks = d.Ltasks;
+    L.cam_task = d.Lints + io, io += (size_t)plan.nf, ints.insert(ints.end(), plan.cam_task.begin(), plan.cam_task.end());
+    L.cam_off = d.Lints + io, io += (size_t)plan.nf, ints.insert(ints.end(), plan.cam_off.begin(), plan.cam_off.end());
+    L.cam_sep = d.Lints + io, io += (size_t)plan.nf, ints.insert(ints.end(), plan.cam_sep.begin(), plan.cam_sep.end());
+    L.row_ptr = d.Lints + io, io += nt + 1, ints.insert(ints.end(), plan.row_ptr.begin(), plan.row_ptr.end());
+    L.x = d.Lx, L.fail = d.Lfail, L.bars = d.Lbars;
+    CU(cudaMemcpyAsync(d.Lints, ints.data(), ints.size() * sizeof(int32_t), cudaMemcpyHostToDevice, h->stream));
+    CU(cudaMemcpyAsync(d.Lsteps, steps.data(), steps.size() * sizeof(int32_t), cudaMemcpyHostToDevice, h->stream));
+    CU(cudaMemcpyAsync(d.Ltasks, tasks.data(), nt * sizeof(CholTask), cudaMemcpyHostToDevice, h->stream));
+    CU(cudaMemsetAsync(d.Lx, 0, sizeof(double) * (size_t)L.n, h->stream));
+    CU(cudaStreamSynchronize(h->stream)); // the host vectors die here
+    return VISO_BA_OK;
+}
 
 // window fast path: sort, CSR, tiles, slots and pair lists are built by kernels (ba_setup.cu).
 // Returns VISO_BA_OK with *fallback = true when the problem has duplicate (point, pose) edges.
@@ -1352,8 +1405,6 @@ extern "C" int32_t viso_ba_upload(viso_ba* h)
         if ((rc = h2d(h, d.block_cam, b.block_cam))) break;
         if ((rc = h2d(h, d.diag_blk, b.diag_blk))) break;
         if ((rc = h2d(h, reinterpret_cast<int32_t*>(d.blk_ij), b.blk_ij))) break;
-        if ((rc = h2d(h, d.first64, b.first64))) break;
-        if ((rc = h2d(h, d.last64, b.last64))) break;
         if (b.window) {
             bool fallback = false;
             if ((rc = build_window_on_device(h, b, d, &fallback))) break;
@@ -1422,8 +1473,7 @@ extern "C" int32_t viso_ba_upload(viso_ba* h)
         h->allreduce_count = (size_t)b.n_blocks * 36 + (size_t)Nc * 6;
         std::memset(&h->L, 0, sizeof(h->L));
         if (h->use_large) {
-            h->L.n = b.max_n, h->L.ld = ldL, h->L.A = d.LA, h->L.Dd = d.LDd, h->L.x = d.Lx, h->L.fail = d.Lfail;
-            h->L.first64 = d.first64, h->L.last64 = d.last64;
+            if ((rc = upload_solve_plan(h, b.plan, d))) break;
         }
         h->blk_ij_host = b.compact ? b.blk_ij : std::vector<int32_t>();
         CU(cudaMemsetAsync(d.S_blk, 0, sizeof(double) * (h->allreduce_count + (size_t)B * 2), h->stream));
