@@ -81,7 +81,7 @@ int main(int argc, char** argv)
     CK(cudaMalloc(&dI, ni * 4));
     CK(cudaMalloc(&dsteps, ns * 16));
     CK(cudaMalloc(&dtasks, nt * sizeof(CholTask)));
-    CK(cudaMalloc(&dbars, nt * 4));
+    CK(cudaMalloc(&dbars, nt * 4 * kBarsPerTask));
     CK(cudaMalloc(&dfail, 4));
     CK(cudaMalloc(&dS, Sblk.size() * 8));
     CK(cudaMalloc(&dbs, (size_t)n * 8));
@@ -160,20 +160,26 @@ int main(int argc, char** argv)
         const int nsteps = plan.tasks.back().n_elim / 64;
         std::vector<unsigned long long> p(16 * 512);
         cudaMemcpyFromSymbol(p.data(), g_chol_prof, sizeof(unsigned long long) * 16 * 512);
-        const char* names[6] = { "load", "chol64", "panel", "sync1", "update", "sync2" };
-        double tot[6] = {};
-        for (int k = 0; k < nsteps && k < 511; ++k) {
+        long long c64[32];
+        cudaMemcpyFromSymbol(c64, g_c64_prof, sizeof(c64));
+        printf("cta_chol64 (CTA 0, last call), cycles: first 8x8 %lld, transpose %lld; per sub-step panel / next-diag+chol8 / wait:", c64[28], c64[29]);
+        for (int i = 0; i < 7; ++i) printf("  %lld/%lld/%lld", c64[4 * i], c64[4 * i + 1], c64[4 * i + 2]);
+        printf("\n");
+        // lead (CTA 0): marks 0..5 = step start, diagonal entries loaded (after U of the previous step), panel there (B),
+        // next diagonal block formed, factorised, published.  Worker (CTA 1): marks 8..13 = step start, factor loaded,
+        // panel done, B passed, update done, U passed.
+        const char* ln[5] = { "wait U + own entries", "wait B", "tile", "chol64", "publish" };
+        const char* wn[5] = { "wait F + load", "panel", "wait B", "update", "wait U" };
+        double lt[5] = {}, wt[5] = {};
+        for (int k = 0; k + 1 < nsteps && k < 511; ++k) {
             const unsigned long long* q = &p[16 * k];
-            for (int i = 0; i < 6; ++i) tot[i] += (double)(q[i + 1] - q[i]) * 1e-3;
-            if (k == 1) {
-                printf("T step 1:");
-                for (int i = 0; i < 6; ++i) printf(" %s %.1f", names[i], (double)(q[i + 1] - q[i]) * 1e-3);
-                printf(" us\n");
-            }
+            for (int i = 0; i < 5; ++i) lt[i] += (double)(q[i + 1] - q[i]) * 1e-3, wt[i] += (double)(q[9 + i] - q[8 + i]) * 1e-3;
         }
-        printf("T totals over %d steps:", nsteps);
-        for (int i = 0; i < 6; ++i) printf(" %s %.1f", names[i], tot[i]);
-        if (nsteps < 511) printf(" | backward %.1f us", (double)(p[16 * nsteps + 1] - p[16 * nsteps]) * 1e-3);
+        printf("T lead CTA, totals over %d steps (us):", nsteps - 1);
+        for (int i = 0; i < 5; ++i) printf("  %s %.1f", ln[i], lt[i]);
+        printf("\nT worker CTA 1, totals (us):");
+        for (int i = 0; i < 5; ++i) printf("  %s %.1f", wn[i], wt[i]);
+        if (nsteps < 511) printf("  | backward %.1f us", (double)(p[16 * nsteps + 1] - p[16 * nsteps]) * 1e-3);
         printf("\n");
 #endif
         return err < 1e-8 && !fail ? 0 : 1;

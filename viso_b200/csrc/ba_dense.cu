@@ -39,6 +39,7 @@ namespace {
 
 constexpr int kCB = kCholBlock; // 64: block size of the factorisation
 constexpr int kCT = 256;        // threads per CTA
+constexpr int kPR = 1;         // panel rows per warp (their substitution chains interleave)
 constexpr int kCS = kCB + 1;    // shared-memory row stride (doubles): odd -> column walks are conflict-free
 constexpr size_t kCholSmem = sizeof(double) * (3 * (size_t)kCB * kCS + 7 * kCB);
 
@@ -48,15 +49,18 @@ __device__ __forceinline__ double shfl_d(double v, int src) { return __shfl_sync
 __device__ unsigned long long g_chol_prof[16 * 512];
 __device__ __forceinline__ void prof_mark(bool on, int step, int k)
 {
-    if (on && blockIdx.x == 0 && threadIdx.x == 0 && step < 512) {
+    if (on && threadIdx.x == 0 && step < 512) {
         unsigned long long t;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
         g_chol_prof[16 * step + k] = t;
     }
 }
 #define PROF(on, step, k) prof_mark(on, step, k)
+__device__ long long g_c64_prof[4 * 8]; // cycles of the sub-step phases of the last cta_chol64 of CTA 0
+#define C64(i, v) ((blockIdx.x == 0 && threadIdx.x == 0) ? (void)(g_c64_prof[i] = (v)) : (void)0)
 #else
 #define PROF(on, step, k)
+#define C64(i, v) ((void)0)
 #endif
 
 // ---- barrier of a CTA group: monotone counter, target = visits * group size (zeroed before the launch) ----
@@ -75,52 +79,55 @@ __device__ __forceinline__ void group_barrier(unsigned int* ctr, unsigned int ta
     __syncthreads();
 }
 
-struct Sync { // the barrier of the CTA set that works on a task: the whole grid (cooperative groups) or a group counter
-    cg::grid_group* grid;
-    unsigned int* ctr;
-    unsigned int ncta, visits;
-    __device__ __forceinline__ void wait()
-    {
-        if (grid) grid->sync();
-        else group_barrier(ctr, ++visits * ncta);
+// 8x8 diagonal block at (c0, c0) of D, by ONE thread in registers: the pivot chain of the whole factorisation
+__device__ __forceinline__ void chol8_thread(double* D, double* rinv, int c0, int* s_fail)
+{
+    double a[36];
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j <= i; ++j) a[i * (i + 1) / 2 + j] = D[(c0 + i) * kCS + c0 + j];
+    bool bad = false;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        const double d = a[j * (j + 1) / 2 + j];
+        bad |= !(d > 0.0) || !(d < 1.7e308);
+        const double inv = rsqrt(d);
+        a[j * (j + 1) / 2 + j] = d * inv;
+        rinv[c0 + j] = inv;
+#pragma unroll
+        for (int i = j + 1; i < 8; ++i) a[i * (i + 1) / 2 + j] *= inv;
+#pragma unroll
+        for (int i = j + 1; i < 8; ++i)
+#pragma unroll
+            for (int k = j + 1; k <= i; ++k) a[i * (i + 1) / 2 + k] = fma(-a[i * (i + 1) / 2 + j], a[k * (k + 1) / 2 + j], a[i * (i + 1) / 2 + k]);
     }
-};
+    if (bad) *s_fail = 1;
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j <= i; ++j) D[(c0 + i) * kCS + c0 + j] = a[i * (i + 1) / 2 + j];
+}
 
 // Cholesky of the 64x64 block in D (lower triangle, row stride kCS) by the whole CTA, in place; LT[c][r] = L[r][c] and
 // rinv[c] = 1 / L[c][c] for the panel.  Returns true on a non-positive or non-finite pivot (uniform over the CTA).
+// Eight sub-steps of 8 columns: panel (one thread per row), then the remainder -= panel panel^T; the NEXT 8x8 diagonal
+// block is updated first by warp 0, whose lane 0 factorises it at once while the other warps finish the remainder, so
+// the single-thread pivot chain runs beside the parallel work instead of between two barriers.
 __device__ __forceinline__ bool cta_chol64(double* D, double* LT, double* rinv, int* s_fail, int tid)
 {
+#ifdef VISO_CHOL_PROFILE
+    long long pq0 = clock64(), pq1, pq2, pq3;
+#endif
+    if (tid == 0) chol8_thread(D, rinv, 0, s_fail);
+    __syncthreads();
+    C64(28, clock64() - pq0);
 #pragma unroll 1
-    for (int c0 = 0; c0 < kCB; c0 += 8) {
-        if (tid == 0) { // 8x8 diagonal block in registers: the pivot chain
-            double a[36];
-#pragma unroll
-            for (int i = 0; i < 8; ++i)
-#pragma unroll
-                for (int j = 0; j <= i; ++j) a[i * (i + 1) / 2 + j] = D[(c0 + i) * kCS + c0 + j];
-            bool bad = false;
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                const double d = a[j * (j + 1) / 2 + j];
-                bad |= !(d > 0.0) || !(d < 1.7e308);
-                const double inv = rsqrt(d);
-                a[j * (j + 1) / 2 + j] = d * inv;
-                rinv[c0 + j] = inv;
-#pragma unroll
-                for (int i = j + 1; i < 8; ++i) a[i * (i + 1) / 2 + j] *= inv;
-#pragma unroll
-                for (int i = j + 1; i < 8; ++i)
-#pragma unroll
-                    for (int k = j + 1; k <= i; ++k) a[i * (i + 1) / 2 + k] = fma(-a[i * (i + 1) / 2 + j], a[k * (k + 1) / 2 + j], a[i * (i + 1) / 2 + k]);
-            }
-            if (bad) *s_fail = 1;
-#pragma unroll
-            for (int i = 0; i < 8; ++i)
-#pragma unroll
-                for (int j = 0; j <= i; ++j) D[(c0 + i) * kCS + c0 + j] = a[i * (i + 1) / 2 + j];
-        }
-        __syncthreads();
+    for (int c0 = 0; c0 < kCB - 8; c0 += 8) {
         const int m = kCB - c0 - 8; // rows below the 8x8 block
+#ifdef VISO_CHOL_PROFILE
+        pq0 = clock64();
+#endif
         if (tid < m) { // panel: one thread per row, x L88^T = a
             const int r = c0 + 8 + tid;
             double x[8];
@@ -137,24 +144,88 @@ __device__ __forceinline__ bool cta_chol64(double* D, double* LT, double* rinv, 
             for (int j = 0; j < 8; ++j) D[r * kCS + c0 + j] = x[j];
         }
         __syncthreads();
-        for (int idx = tid; idx < m * m; idx += kCT) { // remainder -= panel panel^T (lower triangle)
-            const int rr = idx / m, cc = idx - rr * m;
-            if (cc > rr) continue;
+#ifdef VISO_CHOL_PROFILE
+        pq1 = clock64();
+#endif
+        if (tid < 32) { // the next diagonal block first (36 entries: lanes 0..3 take two), then its factorisation by lane 0
+            int rr = 0;
+            while ((rr + 1) * (rr + 2) / 2 <= tid) ++rr;
+            const int cc = tid - rr * (rr + 1) / 2; // tid = 28..31 are the first entries of row 7; 32..35 the last four
+            const bool two = tid < 4;
             const double* pr = D + (c0 + 8 + rr) * kCS + c0;
             const double* pc = D + (c0 + 8 + cc) * kCS + c0;
-            double s = 0.0;
+            const double* pr2 = D + (c0 + 8 + 7) * kCS + c0;
+            const double* pc2 = D + (c0 + 8 + 4 + tid) * kCS + c0;
+            double s = 0.0, s2 = 0.0;
 #pragma unroll
-            for (int t = 0; t < 8; ++t) s = fma(pr[t], pc[t], s);
+            for (int t = 0; t < 8; ++t) {
+                s = fma(pr[t], pc[t], s);
+                if (two) s2 = fma(pr2[t], pc2[t], s2);
+            }
             D[(c0 + 8 + rr) * kCS + c0 + 8 + cc] -= s;
+            if (two) D[(c0 + 8 + 7) * kCS + c0 + 8 + 4 + tid] -= s2;
+            __syncwarp();
+            if (tid == 0) chol8_thread(D, rinv, c0 + 8, s_fail);
+        } else if (m > 8) {
+            // remainder -= panel panel^T below the next diagonal block, in 2x2 micro-tiles of the lower triangle: tile rows
+            // R = 4 .. m/2 - 1 hold R + 1 tiles each; row 4 + rp is folded with row m/2 - 1 - rp into one line of
+            // W = m/2 + 5 tiles, so the enumeration is rectangular and no lane idles on the upper triangle
+            const int h = m >> 1, W = h + 5, nline = (h - 4) >> 1;
+            for (int idx = tid - 32; idx < nline * W; idx += kCT - 32) {
+                const int rp = idx / W, q = idx - rp * W;
+                int R = 4 + rp, C = q;
+                if (q > R) R = h - 1 - rp, C = q - (5 + rp);
+                const double* pr0 = D + (c0 + 8 + 2 * R) * kCS + c0;
+                const double* pc0 = D + (c0 + 8 + 2 * C) * kCS + c0;
+                double s00 = 0.0, s01 = 0.0, s10 = 0.0, s11 = 0.0;
+#pragma unroll
+                for (int t = 0; t < 8; ++t) {
+                    const double r0 = pr0[t], r1 = pr0[kCS + t], q0 = pc0[t], q1 = pc0[kCS + t];
+                    s00 = fma(r0, q0, s00), s01 = fma(r0, q1, s01), s10 = fma(r1, q0, s10), s11 = fma(r1, q1, s11);
+                }
+                double* o = D + (c0 + 8 + 2 * R) * kCS + c0 + 8 + 2 * C;
+                o[0] -= s00;
+                if (C < R) o[1] -= s01;
+                o[kCS] -= s10, o[kCS + 1] -= s11;
+            }
         }
+#ifdef VISO_CHOL_PROFILE
+        pq2 = clock64();
+#endif
         __syncthreads();
+#ifdef VISO_CHOL_PROFILE
+        pq3 = clock64();
+        C64(c0 / 8 * 4 + 0, pq1 - pq0), C64(c0 / 8 * 4 + 1, pq2 - pq1), C64(c0 / 8 * 4 + 2, pq3 - pq2);
+#endif
     }
+#ifdef VISO_CHOL_PROFILE
+    pq0 = clock64();
+#endif
     for (int idx = tid; idx < kCB * kCB; idx += kCT) {
         const int r = idx >> 6, c = idx & 63;
         LT[c * kCS + r] = c <= r ? D[r * kCS + c] : 0.0;
     }
     __syncthreads();
+    C64(29, clock64() - pq0);
     return *s_fail != 0;
+}
+
+// The factor of a diagonal block in T.Dd: L_kk row-major [64][64], then rinv[64], then the failure flag of the
+// factorisation so far (0 / 1), padded to kCholDdStride doubles.
+__device__ __forceinline__ void publish_factor(double* dd, const double* LT, const double* rinv, bool bad, int tid)
+{
+    for (int idx = tid; idx < kCB * kCB; idx += kCT) dd[idx] = LT[(idx & 63) * kCS + (idx >> 6)];
+    if (tid < kCB) dd[kCB * kCB + tid] = rinv[tid];
+    if (tid == kCB) dd[kCB * kCB + kCB] = bad ? 1.0 : 0.0;
+}
+
+__device__ __forceinline__ bool load_factor(const double* dd, double* LT, double* rinv, int tid)
+{
+    for (int idx = tid; idx < kCB * kCB; idx += kCT) LT[(idx & 63) * kCS + (idx >> 6)] = __ldcg(dd + idx);
+    if (tid < kCB) rinv[tid] = __ldcg(dd + kCB * kCB + tid);
+    const bool bad = __ldcg(dd + kCB * kCB + kCB) != 0.0;
+    __syncthreads();
+    return bad;
 }
 
 // row q of a step's row list: the band range, then the border range, then the right-hand side
@@ -163,9 +234,91 @@ __device__ __forceinline__ int step_row(int q, int base, int n1, int r2b, int n2
     return q < n1 ? base + q : (q < n1 + n2 ? r2b + (q - n1) : rhs);
 }
 
+// ---- counters of a task (L.bars + kBarsPerTask * task, zeroed before the launch; all monotone) ----
+//   [0] F  factors published by the lead CTA of the set           (k + 1 after the factor of diagonal block k)
+//   [1] B  worker arrivals after the panel of a step              ((k + 1) * workers after step k)
+//   [2] U  worker arrivals after the trailing update of a step    ((k + 1) * workers after step k)
+//   [3] G  plain barrier of the set (before the back substitution of an interior segment)
+__device__ __forceinline__ void ctr_arrive(unsigned int* ctr)
+{
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(ctr) : "memory");
+    }
+}
+
+__device__ __forceinline__ void ctr_wait(const unsigned int* ctr, unsigned int target)
+{
+    if (threadIdx.x == 0) {
+        unsigned int v;
+        do {
+            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(ctr) : "memory");
+        } while (v < target);
+        __threadfence();
+    }
+    __syncthreads();
+}
+
+// panel rows  X L_kk^T = A_panel  of one step: one warp per R rows (their substitution chains interleave), the row in
+// registers, lane = column (and column + 32).  x of a finished column lives in xv (off the dependent chain: shuffle ->
+// multiply -> FMA -> next shuffle); lanes left of the column see L^T entries that are zero and keep their values.
+template <int R>
+__device__ __forceinline__ void panel_rows(double* A, int ld, int j0, int base, int n1, int r2b, int n2, int nrows, int nrow,
+                                           int first_warp, int n_warps, const double* LT, const double* rinv, int lane)
+{
+    for (int q0 = R * first_warp; q0 < nrow; q0 += R * n_warps) {
+        double* a[R];
+        double a0[R], a1[R], xv0[R], xv1[R];
+#pragma unroll
+        for (int t = 0; t < R; ++t) {
+            const int q = min(q0 + t, nrow - 1); // a short last group repeats its last row (not written back)
+            a[t] = A + (size_t)step_row(q, base, n1, r2b, n2, nrows) * ld + j0;
+            a0[t] = __ldcg(a[t] + lane), a1[t] = __ldcg(a[t] + lane + 32);
+            xv0[t] = 0.0, xv1[t] = 0.0;
+        }
+#pragma unroll 4
+        for (int c = 0; c < 32; ++c) {
+            const double ri = rinv[c], l0 = LT[c * kCS + lane], l1 = LT[c * kCS + lane + 32];
+            double xs[R];
+#pragma unroll
+            for (int t = 0; t < R; ++t) xs[t] = shfl_d(a0[t], c);
+#pragma unroll
+            for (int t = 0; t < R; ++t) {
+                const double xc = xs[t] * ri;
+                if (lane == c) xv0[t] = xc;
+                a0[t] = fma(-xc, l0, a0[t]);
+                a1[t] = fma(-xc, l1, a1[t]);
+            }
+        }
+#pragma unroll 4
+        for (int c = 32; c < kCB; ++c) {
+            const double ri = rinv[c], l1 = LT[c * kCS + lane + 32];
+            double xs[R];
+#pragma unroll
+            for (int t = 0; t < R; ++t) xs[t] = shfl_d(a1[t], c - 32);
+#pragma unroll
+            for (int t = 0; t < R; ++t) {
+                const double xc = xs[t] * ri;
+                if (lane + 32 == c) xv1[t] = xc;
+                a1[t] = fma(-xc, l1, a1[t]);
+            }
+        }
+#pragma unroll
+        for (int t = 0; t < R; ++t)
+            if (q0 + t < nrow) a[t][lane] = xv0[t], a[t][lane + 32] = xv1[t];
+    }
+}
+
 // Partial Cholesky of a task: eliminate its first n_elim columns.  gb / G: this CTA's index in, and the size of, the
-// CTA set that works on the task.  Returns false when a pivot failed (uniform over the set).
-__device__ bool task_factor(const CholTask& T, int gb, int G, Sync& sync, double* smd, int* s_fail, bool prof)
+// CTA set that works on the task; bars: the task's counters.  Returns false when a pivot failed (uniform over the set).
+//
+// Roles.  CTA 0 of the set is the LEAD: it owns the pivot chain.  For every step k it waits until the panel of step k is
+// written (counter B), forms the next diagonal block  A_{k+1,k+1} - X_{k+1,k} X_{k+1,k}^T  in shared memory, factorises
+// it and publishes the factor (counter F).  The other CTAs are WORKERS: wait for factor k, panel of step k, (B), trailing
+// update of step k without the lead's tile, (U).  The lead's 64-pivot chain thus runs beside the workers' update instead
+// of in front of it, and no CTA repeats it.  A set of one CTA plays both roles in turn.
+__device__ bool task_factor(const CholTask& T, int gb, int G, unsigned int* bars, double* smd, int* s_fail, bool prof)
 {
     double* const D = smd;                // [kCB][kCS] diagonal block, then tile buffer of the trailing update
     double* const LT = D + kCB * kCS;     // [kCB][kCS] LT[c][r] = L_kk[r][c]
@@ -173,77 +326,113 @@ __device__ bool task_factor(const CholTask& T, int gb, int G, Sync& sync, double
     double* const rinv = T2 + kCB * kCS;  // [kCB]      1 / L_kk[c][c]
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int ld = T.ld, nrows = T.nrows;
-    double* const A = T.A; // written and re-read across barriers by other CTAs: L2 loads (__ldcg), no __restrict__
+    double* const A = T.A; // written and re-read across the counters by other CTAs: L2 loads (__ldcg), no __restrict__
     const int tx = tid & 15, ty = tid >> 4;
     const int nsteps = T.n_elim / kCB;
+    const bool lead = gb == 0, worker = gb > 0 || G == 1;
+    const int nW = G > 1 ? G - 1 : 1, w = G > 1 ? gb - 1 : 0;
+    unsigned int* const cF = bars, * const cB = bars + 1, * const cU = bars + 2;
     bool ok = true;
+    if (lead) { // the factor of diagonal block 0
+        for (int idx = tid; idx < kCB * kCB; idx += kCT) {
+            const int rr = idx >> 6, c = idx & 63;
+            D[rr * kCS + c] = c <= rr ? __ldcg(A + (size_t)rr * ld + c) : 0.0;
+        }
+        __syncthreads();
+        if (cta_chol64(D, LT, rinv, s_fail, tid)) ok = false;
+        publish_factor(T.Dd, LT, rinv, !ok, tid);
+        ctr_arrive(cF);
+    }
     for (int k = 0; k < nsteps; ++k) {
         const int j0 = k * kCB;
         const int4 st = __ldg(T.steps + k);
         const int base = j0 + kCB;
         const int n1 = max(st.x - base, 0), r2b = st.y, n2 = max(st.z - st.y, 0);
-        PROF(prof, k, 0);
-        // ---------------- D: diagonal block, redundantly in every CTA of the set ----------------
-        for (int idx = tid; idx < kCB * kCB; idx += kCT) {
-            const int rr = idx >> 6, c = idx & 63;
-            D[rr * kCS + c] = c <= rr ? __ldcg(A + (size_t)(j0 + rr) * ld + j0 + c) : 0.0;
+        const int n1t = n1 / kCB, nt = n1t + n2 / kCB;
+        const int ntri = nt * (nt + 1) / 2, ntile = ntri + nt;
+        const bool next = k + 1 < nsteps;
+        const bool lead_tile = next && n1t >= 1; // tile 0 of the update is the next diagonal block: the lead's
+        const unsigned int done = (unsigned)(k + 1) * (unsigned)nW;
+        if (worker) {
+            PROF(prof && gb == 1, k, 8);
+            // ---------------- P: panel of step k ----------------
+            ctr_wait(cF, (unsigned)k + 1u);
+            if (load_factor(T.Dd + (size_t)k * kCholDdStride, LT, rinv, tid)) ok = false;
+            PROF(prof && gb == 1, k, 9);
+            const int nrow = n1 + n2 + 1, nwarps = nW * (kCT / 32), fw = w * (kCT / 32) + warp;
+            if (nrow > 2 * nwarps) panel_rows<4>(A, ld, j0, base, n1, r2b, n2, nrows, nrow, fw, nwarps, LT, rinv, lane);
+            else if (nrow > nwarps) panel_rows<2>(A, ld, j0, base, n1, r2b, n2, nrows, nrow, fw, nwarps, LT, rinv, lane);
+            else panel_rows<1>(A, ld, j0, base, n1, r2b, n2, nrows, nrow, fw, nwarps, LT, rinv, lane);
+            PROF(prof && gb == 1, k, 10);
+            ctr_arrive(cB);
         }
-        __syncthreads();
-        PROF(prof, k, 1);
-        const bool bad = cta_chol64(D, LT, rinv, s_fail, tid);
-        PROF(prof, k, 2);
-        if (bad) ok = false; // uniform over the set; the data below is garbage from here on, the barriers still match
-        if (gb == 0) { // the factor of the diagonal block, for the backward substitution
-            double* dd = T.Dd + (size_t)k * kCB * kCB;
-            for (int idx = tid; idx < kCB * kCB; idx += kCT) dd[idx] = LT[(idx & 63) * kCS + (idx >> 6)];
-        }
-        // ---------------- P: panel rows, one warp per four rows (the right-hand side row included) ----------------
-        const int nrow = n1 + n2 + 1;
-        for (int q0 = 4 * (gb * (kCT / 32) + warp); q0 < nrow; q0 += 4 * G * (kCT / 32)) {
-            double* a[4];
-            double a0[4], a1[4];
+        if (lead && next) {
+            // ---------------- D: the next diagonal block, its factor ----------------
+            PROF(prof, k, 0);
+            double dg[4][4]; // the block's own entries: final once the update of step k - 1 is through
+            if (k > 0) ctr_wait(cU, done - (unsigned)nW);
 #pragma unroll
-            for (int t = 0; t < 4; ++t) {
-                const int q = min(q0 + t, nrow - 1); // a short last group repeats its last row (not written back)
-                a[t] = A + (size_t)step_row(q, base, n1, r2b, n2, nrows) * ld + j0;
-                a0[t] = __ldcg(a[t] + lane), a1[t] = __ldcg(a[t] + lane + 32);
-            }
-#pragma unroll 4
-            for (int c = 0; c < 32; ++c) {
-                const double ri = rinv[c], l0 = LT[c * kCS + lane], l1 = LT[c * kCS + lane + 32];
+            for (int i = 0; i < 4; ++i)
 #pragma unroll
-                for (int t = 0; t < 4; ++t) {
-                    const double xc = shfl_d(a0[t], c) * ri;
-                    if (lane == c) a0[t] = xc;
-                    if (lane > c) a0[t] = fma(-xc, l0, a0[t]);
-                    a1[t] = fma(-xc, l1, a1[t]);
+                for (int j = 0; j < 4; ++j) {
+                    const int r = ty + 16 * i, c = tx + 16 * j;
+                    dg[i][j] = c <= r ? __ldcg(A + (size_t)(base + r) * ld + base + c) : 0.0;
                 }
-            }
-#pragma unroll 4
-            for (int c = 32; c < kCB; ++c) {
-                const double ri = rinv[c], l1 = LT[c * kCS + lane + 32];
+            PROF(prof, k, 1);
+            double acc[4][4] = {};
+            if (lead_tile) {
+                ctr_wait(cB, done);
+                PROF(prof, k, 2);
+                double* const Pi = D;
+                double v[16];
 #pragma unroll
-                for (int t = 0; t < 4; ++t) {
-                    const double xc = shfl_d(a1[t], c - 32) * ri;
-                    if (lane + 32 == c) a1[t] = xc;
-                    if (lane + 32 > c) a1[t] = fma(-xc, l1, a1[t]);
+                for (int q = 0; q < 16; ++q) {
+                    const int idx = tid + q * kCT;
+                    v[q] = __ldcg(A + (size_t)(base + (idx >> 6)) * ld + j0 + (idx & 63));
                 }
+#pragma unroll
+                for (int q = 0; q < 16; ++q) {
+                    const int idx = tid + q * kCT;
+                    Pi[(idx >> 6) * kCS + (idx & 63)] = v[q];
+                }
+                __syncthreads();
+#pragma unroll 4
+                for (int kk = 0; kk < kCB; ++kk) { // lower micro-tiles only (j <= i): the block is symmetric
+                    double av[4], bv[4];
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) av[i] = Pi[(ty + 16 * i) * kCS + kk];
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) bv[i] = Pi[(tx + 16 * i) * kCS + kk];
+#pragma unroll
+                    for (int i = 0; i < 4; ++i)
+#pragma unroll
+                        for (int j = 0; j <= i; ++j) acc[i][j] = fma(av[i], bv[j], acc[i][j]);
+                }
+                __syncthreads();
             }
 #pragma unroll
-            for (int t = 0; t < 4; ++t)
-                if (q0 + t < nrow) a[t][lane] = a0[t], a[t][lane + 32] = a1[t];
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const int r = ty + 16 * i, c = tx + 16 * j;
+                    D[r * kCS + c] = c <= r ? dg[i][j] - acc[i][j] : 0.0;
+                }
+            __syncthreads();
+            PROF(prof, k, 3);
+            if (cta_chol64(D, LT, rinv, s_fail, tid)) ok = false;
+            PROF(prof, k, 4);
+            publish_factor(T.Dd + (size_t)(k + 1) * kCholDdStride, LT, rinv, !ok, tid);
+            ctr_arrive(cF);
+            PROF(prof, k, 5);
         }
-        PROF(prof, k, 3);
-        sync.wait();
-        PROF(prof, k, 4);
-        // ---------------- U: trailing update over 64x64 tiles of the lower triangle of the step's rows ----------------
-        { // tiles (ti >= tl) of the active row tiles, then one tile per tl for the right-hand side row
-            const int n1t = n1 / kCB, nt = n1t + n2 / kCB;
-            const int ntri = nt * (nt + 1) / 2;
-            const int ntile = ntri + nt;
-            double* const Pi = D; // the diagonal-block buffers are free again
+        if (worker) {
+            // ---------------- U: trailing update over 64x64 tiles of the lower triangle of the step's rows ----------------
+            // tiles (ti >= tl) of the active row tiles, then one tile per tl for the right-hand side row
+            ctr_wait(cB, done);
+            PROF(prof && gb == 1, k, 11);
+            double* const Pi = D;
             double* const Pl = T2;
-            for (int t = gb; t < ntile; t += G) {
+            for (int t = (lead_tile ? 1 : 0) + w; t < ntile; t += nW) {
                 const bool rhs = t >= ntri;
                 int ti = 0, tl = t - ntri;
                 if (!rhs) {
@@ -287,11 +476,13 @@ __device__ bool task_factor(const CholTask& T, int gb, int G, Sync& sync, double
                         }
                     }
             }
+            PROF(prof && gb == 1, k, 12);
+            ctr_arrive(cU);
+            if (next) ctr_wait(cU, done); // the next panel reads rows other workers updated
+            PROF(prof && gb == 1, k, 13);
         }
-        PROF(prof, k, 5);
-        sync.wait();
-        PROF(prof, k, 6);
     }
+    ctr_wait(cU, (unsigned)nsteps * (unsigned)nW); // everyone: the factor is complete
     return ok;
 }
 
@@ -314,7 +505,7 @@ __device__ void task_backward(const CholTask& T, int gb, int G, double* smd)
         const int cb = b * kCB;
         const int4 st = __ldg(T.steps + b);
         { // L_bb (row-major)
-            const double* dd = T.Dd + (size_t)b * kCB * kCB;
+            const double* dd = T.Dd + (size_t)b * kCholDdStride;
             for (int idx = tid; idx < kCB * kCB; idx += kCT) D[(idx >> 6) * kCS + (idx & 63)] = __ldcg(dd + idx);
         }
         double* const ysh = colb; // y_b (fetched before the waits)
@@ -383,7 +574,7 @@ __global__ void __launch_bounds__(256) k_dense_zero(LargeSolve L)
     if (r == T.nrows) {
         for (int c = threadIdx.x; c < T.nrows; c += blockDim.x) row[c] = 0.0;
         for (int c = threadIdx.x; c < T.nrows / kCB; c += blockDim.x) T.flags[c] = 0;
-        if (threadIdx.x == 0) L.bars[t] = 0u;
+        if (threadIdx.x < kBarsPerTask) L.bars[kBarsPerTask * t + threadIdx.x] = 0u;
         if (t == 0 && threadIdx.x == 0) *L.fail = 0;
     } else {
         const int c0 = kCB * T.first64[r / kCB];
@@ -448,8 +639,7 @@ __global__ void __launch_bounds__(kCT, 1) k_chol_coop(LargeSolve L)
         // ---------------- phase 1: the interior segments, each on its own CTA group ----------------
         if (mine >= 0) {
             const CholTask& T = L.tasks[mine];
-            Sync s{ nullptr, L.bars + mine, (unsigned)T.ncta, 0u };
-            ok = task_factor(T, bid - T.cta0, T.ncta, s, smd, &s_fail, false);
+            ok = task_factor(T, bid - T.cta0, T.ncta, L.bars + kBarsPerTask * mine, smd, &s_fail, false);
         }
         grid.sync();
         // ---------------- phase 2: border blocks of the segments -> separator system, in a fixed order ----------------
@@ -484,12 +674,11 @@ __global__ void __launch_bounds__(kCT, 1) k_chol_coop(LargeSolve L)
     }
     // ---------------- phase 3: T (the separator system, or the whole matrix) on every CTA ----------------
     {
-        Sync s{ &grid, nullptr, (unsigned)G, 0u };
-        const bool okT = task_factor(top, bid, G, s, smd, &s_fail, true);
+        const bool okT = task_factor(top, bid, G, L.bars + kBarsPerTask * P, smd, &s_fail, true);
         ok = ok && okT;
-        PROF(true, top.n_elim / kCB, 0);
+        PROF(bid == 0, top.n_elim / kCB, 0);
         task_backward(top, bid, G, smd);
-        PROF(true, top.n_elim / kCB, 1);
+        PROF(bid == 0, top.n_elim / kCB, 1);
     }
     if (!ok && tid == 0) *L.fail = 1;
     if (P > 0) {
@@ -504,8 +693,7 @@ __global__ void __launch_bounds__(kCT, 1) k_chol_coop(LargeSolve L)
                 T.x[T.n_elim + i] = __ldcg(top.x + s * sep + (i < T.sL ? i : i - T.sL));
             }
             for (int i = gb * kCT + tid; i < (T.sL + T.sR) / kCB; i += T.ncta * kCT) T.flags[T.n_elim / kCB + i] = 1;
-            Sync sy{ nullptr, L.bars + mine, (unsigned)T.ncta, (unsigned)(2 * (T.n_elim / kCB)) }; // continues the counter of phase 1
-            sy.wait();
+            group_barrier(L.bars + kBarsPerTask * mine + 3, (unsigned)T.ncta);
             task_backward(T, gb, T.ncta, smd);
         }
     }

@@ -186,10 +186,12 @@ struct DevProblem {
 // segment's contribution to the separator system T (block tridiagonal), which every CTA then factorises together; the
 // interiors are back-substituted concurrently again.  P = 0: no partition, T is the whole matrix (dense / envelope).
 constexpr int kCholBlock = 64; // every size below is a multiple of it (identity padding)
+constexpr int kBarsPerTask = 4;  // counters per task of the large solve (ba_dense.cu: F, B, U, G)
+constexpr int kCholDdStride = 64 * 64 + 128; // doubles per published diagonal factor: L_kk, 1 / diag, failure flag (ba_solve_plan.h: dd_doubles)
 
 struct CholTask {
     double* A;              // row-major [nrows + 1][ld]; row nrows is the right-hand side; only the envelope is touched
-    double* Dd;             // factorised diagonal blocks, [n_elim / 64][64][64] (A's own are stale)
+    double* Dd;             // factorised diagonal blocks, [n_elim / 64][kCholDdStride] (A's own are stale)
     double* x;              // [nrows] solution; rows >= n_elim (the border) are inputs of the back substitution
     int32_t* flags;         // [nrows / 64] block of x published
     const int4* steps;      // [n_elim / 64] rows below the diagonal block that step k touches: [64 (k + 1), .x) and [.y, .z)
@@ -211,7 +213,7 @@ struct LargeSolve {
     const int32_t* cam_sep; // [free poses] separator index of the pose or -1
     double* x;              // [n] the step, free-pose order
     int32_t* fail;          // [1]
-    unsigned int* bars;     // [n_seg + 1] group barrier counters
+    unsigned int* bars;     // [(n_seg + 1) * kBarsPerTask] counters of the tasks
 };
 
 // launchers (all asynchronous on `st`); each returns the number of kernels it launched

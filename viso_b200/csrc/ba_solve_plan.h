@@ -20,7 +20,7 @@ struct PlanTask { // mirrors CholTask without the pointers
     std::vector<int32_t> first64;  // [nrows / 64]
     std::vector<int32_t> steps;    // 4 per elimination step: r1_end, r2_begin, r2_end, 0
     size_t a_doubles() const { return (size_t)(nrows + 1) * (size_t)ld; }
-    size_t dd_doubles() const { return (size_t)(n_elim / 64) * 64 * 64; }
+    size_t dd_doubles() const { return (size_t)(n_elim / 64) * (64 * 64 + 128); } // kCholDdStride (ba_device.h) per block
 };
 
 struct SolvePlan {

@@ -1203,7 +1203,7 @@ void carve(Arena& A, DevPtrs& d, int64_t Nc, int64_t Np, int64_t Ne, int64_t B, 
         d.Lints = A.take<int32_t>(ni);
         d.Lsteps = A.take<int4>(ns);
         d.Ltasks = A.take<CholTask>(b.plan.tasks.size());
-        d.Lbars = A.take<unsigned int>(b.plan.tasks.size());
+        d.Lbars = A.take<unsigned int>(kBarsPerTask * b.plan.tasks.size());
         d.Lfail = A.take<int32_t>(1);
     } else {
         d.Ldoubles = d.Lx = nullptr;
