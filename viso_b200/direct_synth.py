@@ -119,3 +119,46 @@ def synth_sequence(seed=1, n_frames=5, n_points=1500, step_rot=(0.003, -0.004, 0
     pv = rng.uniform(60, H - 60, size=n_points)
     pts = np.stack([(pu - CX) / FX, (pv - CY) / FY, np.ones(n_points)], axis=-1)
     return {"images": images, "poses": np.stack(poses), "points": pts}
+
+
+def synth_photo_window(seed=1, n_frames=4, n_points=300, width=320, height=240, pose_noise=1e-3, depth_noise=0.005,
+                       step_rot=(0.004, -0.005, 0.003), step_trans=(0.03, -0.02, 0.015)):
+    """A small window for bundle adjustment over the reference adjuster's photometric edge (reference
+    include/bundle_adjuster.h:58-106): n_frames keyframes over the textured plane, map points on it, and one edge
+    (point, source keyframe, pose vertex) from each point's host keyframe (0 or 1) to every other keyframe.  The
+    initial poses of keyframes >= 2 and the point depths are perturbed; keyframe 0 stays at the identity and keyframe 1
+    at its true pose (with both fixed the scale of the window is pinned; photometric edges alone leave it free).
+    Intrinsics are the reference's scaled to the image size."""
+    rng = np.random.default_rng(seed)
+    T = _texture(rng)
+    sx, sy = width / W, height / H
+    K = (FX * sx, FY * sy, CX * sx, CY * sy)
+    true = [pose_from_rotvec(np.asarray(step_rot) * k, np.asarray(step_trans) * k) for k in range(n_frames)]
+
+    def render(pose):
+        uu, vv = np.meshgrid(np.arange(width, dtype=np.float64), np.arange(height, dtype=np.float64))
+        R, t = quat_to_R(pose[:4]), pose[4:]
+        d = np.stack([(uu - K[2]) / K[0], (vv - K[3]) / K[1], np.ones_like(uu)], axis=-1)
+        Rt_d, Rt_t = d @ R, R.T @ t
+        s = (1.0 + Rt_t[2]) / Rt_d[..., 2]
+        Xw = Rt_d * s[..., None] - Rt_t
+        # the texture lives on the plane z = 1 of the world frame, parametrised by frame 0's full-size pixel grid
+        return np.clip(np.rint(T(FX * Xw[..., 0] / Xw[..., 2] + CX, FY * Xw[..., 1] / Xw[..., 2] + CY)), 0, 255).astype(np.uint8)
+    images = [render(p) for p in true]
+    pu = rng.uniform(0.2 * width, 0.8 * width, size=n_points)
+    pv = rng.uniform(0.2 * height, 0.8 * height, size=n_points)
+    pts_true = np.stack([(pu - K[2]) / K[0], (pv - K[3]) / K[1], np.ones(n_points)], axis=-1)
+    poses_init = np.stack(true).copy()
+    for k in range(2, n_frames):
+        poses_init[k] = pose_from_rotvec(np.asarray(step_rot) * k + rng.normal(0, pose_noise, 3),
+                                         np.asarray(step_trans) * k + rng.normal(0, pose_noise, 3))
+    pts_init = pts_true * (1.0 + rng.normal(0, depth_noise, size=(n_points, 1)))
+    e_point, e_src, e_dst = [], [], []
+    for p in range(n_points):
+        host = p % 2
+        for k in range(n_frames):
+            if k != host:
+                e_point.append(p), e_src.append(host), e_dst.append(k)
+    return {"K": K, "images": images, "poses_true": np.stack(true), "points_true": pts_true, "poses_init": poses_init,
+            "points_init": pts_init, "edge_point": np.array(e_point, np.int32), "edge_src": np.array(e_src, np.int32),
+            "edge_dst": np.array(e_dst, np.int32)}
