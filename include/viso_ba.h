@@ -132,6 +132,27 @@ int32_t viso_ba_set_problem_batched(viso_ba* h, int64_t n_problems, const int64_
                                     const int32_t* edge_pose, const int32_t* edge_point,
                                     const float* edge_uv);
 
+/*
+ * The reference adjuster's OWN edge: EdgeDirectProjection(srcFrame, targetFrame) between VertexPoint and VertexPose
+ * (bundle_adjuster.h:58-106, :154-160): the 16-D photometric residual of a 4 x 4 patch, information I_16.
+ *   - every pose vertex has a keyframe = its level-0 image (CV_8UC1, keyframe.h:29-45): viso_ba_set_pose_image
+ *   - an edge names a point, a SOURCE keyframe (by pose index) and the pose vertex / target keyframe; the source
+ *     projects with the pose its keyframe had at upload (srcFrame->Project, :79), the target with the vertex (:73-78)
+ *   - an edge whose patch leaves an image disables itself at that state (setLevel(1), :91-95)
+ *   - the Jacobian, which the reference leaves to g2o's numeric differentiation, is analytic: image gradient
+ *     (keyframe.h:59-64) x dPixeldXi (viso.cpp:640-658) for the pose, x the projection Jacobians of both frames for the point
+ * A handle holds either reprojection or photometric edges (VISO_BA_ERR_UNSUPPORTED otherwise); photometric
+ * problems are single, unsharded, and run on the general kernels (config.path is ignored).
+ * Photometric edges leave the scale of a window free: fix two poses (viso_ba_set_pose_fixed) to pin it.
+ */
+int32_t viso_ba_set_pose_image(viso_ba* h, int64_t pose, const uint8_t* data, int32_t rows, int32_t cols,
+                               int32_t stride);
+int32_t viso_ba_add_photo_edge(viso_ba* h, int64_t point, int64_t src_pose, int64_t dst_pose);
+/* bulk form: replaces the whole problem (images are set afterwards, per pose) */
+int32_t viso_ba_set_photo_problem(viso_ba* h, int64_t n_poses, const double* poses7, int64_t n_points,
+                                  const double* points3, int64_t n_edges, const int32_t* edge_point,
+                                  const int32_t* edge_src, const int32_t* edge_dst);
+
 /* gauge: g2o setFixed(); the reference fixes nothing, viso keeps frame 0 at identity
  * (keyframe.h:34-35, viso.cpp:82-83).  Batched handles: global pose index. */
 int32_t viso_ba_set_pose_fixed(viso_ba* h, int64_t pose, int32_t fixed);

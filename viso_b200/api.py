@@ -92,6 +92,9 @@ SYMBOLS = {
     "viso_ba_add_edge": (C.c_int32, [_P, C.c_int64, C.c_int64, C.c_float, C.c_float]),
     "viso_ba_set_problem": (C.c_int32, [_P, C.c_int64, _D, C.c_int64, _D, C.c_int64, _I32, _I32, _F]),
     "viso_ba_set_problem_batched": (C.c_int32, [_P, C.c_int64, _I64, _I64, _I64, _D, _D, _I32, _I32, _F]),
+    "viso_ba_set_pose_image": (C.c_int32, [_P, C.c_int64, C.POINTER(C.c_uint8), C.c_int32, C.c_int32, C.c_int32]),
+    "viso_ba_add_photo_edge": (C.c_int32, [_P, C.c_int64, C.c_int64, C.c_int64]),
+    "viso_ba_set_photo_problem": (C.c_int32, [_P, C.c_int64, _D, C.c_int64, _D, C.c_int64, _I32, _I32, _I32]),
     "viso_ba_set_pose_fixed": (C.c_int32, [_P, C.c_int64, C.c_int32]),
     "viso_ba_set_intrinsics": (C.c_int32, [_P, C.c_double, C.c_double, C.c_double, C.c_double]),
     "viso_ba_set_huber_delta": (C.c_int32, [_P, C.c_double]),
@@ -241,6 +244,25 @@ class BundleAdjuster:
 
     def AddEdge(self, point, pose, u, v):
         self._check(self._lib.viso_ba_add_edge(self._h, int(point), int(pose), float(u), float(v)))
+
+    # ---- the reference adjuster's own edge: EdgeDirectProjection (bundle_adjuster.h:58-106) ----
+    def SetPoseImage(self, pose, image):
+        """level-0 image (uint8, rows x cols) of the keyframe of pose vertex `pose`"""
+        im = np.ascontiguousarray(image, dtype=np.uint8)
+        self._check(self._lib.viso_ba_set_pose_image(self._h, int(pose), im.ctypes.data_as(C.POINTER(C.c_uint8)),
+                                                     im.shape[0], im.shape[1], im.strides[0]))
+
+    def AddPhotoEdge(self, point, src_pose, dst_pose):
+        self._check(self._lib.viso_ba_add_photo_edge(self._h, int(point), int(src_pose), int(dst_pose)))
+
+    def set_photo_problem(self, poses7, points3, edge_point, edge_src, edge_dst, images=None):
+        poses7, points3 = _c(poses7, np.float64), _c(points3, np.float64)
+        el, es, ed = (_c(a, np.int32) for a in (edge_point, edge_src, edge_dst))
+        self._check(self._lib.viso_ba_set_photo_problem(
+            self._h, poses7.size // 7, _dptr(poses7), points3.size // 3, _dptr(points3), el.size,
+            el.ctypes.data_as(_I32), es.ctypes.data_as(_I32), ed.ctypes.data_as(_I32)))
+        for k, im in enumerate(images or []):
+            self.SetPoseImage(k, im)
 
     # ---- completed interface --------------------------------------------------------------
     def SetIntrinsics(self, fx, fy, cx, cy):

@@ -16,7 +16,7 @@ CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libviso_ba.so")
 STAMP = os.path.join(HERE, ".libviso_ba.stamp")
 SYNTH_LIB = os.path.join(HERE, "libviso_synth.so")
-SOURCES = ["ba_kernels.cu", "ba_window.cu", "ba_dense.cu", "ba_setup.cu", "direct_pose.cu", "lk_align.cu", "pyramid.cu", "viso_ba.cpp"]
+SOURCES = ["ba_kernels.cu", "ba_window.cu", "ba_dense.cu", "ba_setup.cu", "ba_photo.cu", "direct_pose.cu", "lk_align.cu", "pyramid.cu", "viso_ba.cpp"]
 SYNTH_SOURCES = ["synth.cpp"]
 HEADERS = [os.path.join(CSRC, "ba_device.h"), os.path.join(CSRC, "ba_math.cuh"), os.path.join(CSRC, "ba_setup.h"), os.path.join(CSRC, "image_math.cuh"), os.path.join(ROOT, "include", "viso_ba.h"), os.path.join(ROOT, "include", "viso_ba_synth.h"), os.path.join(ROOT, "include", "viso_direct.h"), os.path.join(ROOT, "include", "viso_lk.h")]
 NVCC_FLAGS = [

@@ -174,6 +174,12 @@ struct DevProblem {
     unsigned long long* maxdiag_bits; // [B]
     int32_t* n_active; // [1]
     double lambda_scale; // 1 on the rank that adds lambda to diag(S) (rank 0), else 0
+    // photometric edges (ba_photo.cu; reference bundle_adjuster.h:58-106); all null for a reprojection problem.  An edge's
+    // obs_cam is its pose vertex / target keyframe, the source keyframe index rides in the bits of obs_uv.x
+    const void* ph_frames;   // visoimg::DevImage [n_cams]: level-0 image of every pose's keyframe
+    const double* ph_src_rt; // [n_cams][12] R|t the keyframes had at upload: srcFrame->Project never sees the optimiser's poses
+    double* ph_sum;          // [n_obs][16] sums over the 16 samples of an edge (k_photo_sample)
+    double* ph_mid;          // [n_obs][4]  w F C_tt F: the 2 x 2 middle of the edge's diagonal-block term
 };
 
 // ---- reduced camera system of ONE large problem (n > kSmallMaxN): LinearSolverDense, reference bundle_adjuster.h:113-114 ----
@@ -233,6 +239,11 @@ int large_solve_cta_count();            // CTAs of the cooperative solve kernel 
 int launch_update(const DevProblem& P, cudaStream_t st);
 int launch_decide(const DevProblem& P, cudaStream_t st);
 int launch_eval_cost(const DevProblem& P, cudaStream_t st); // cost of current state -> cost_pt
+// photometric edges (ba_photo.cu)
+int launch_photo_sample(const DevProblem& P, int which, int full, int even_if_inactive, cudaStream_t st);
+int launch_photo_linearize(const DevProblem& P, int init_pass, double lambda_override, cudaStream_t st);
+int launch_photo_cost(const DevProblem& P, int which, int even_if_inactive, cudaStream_t st);
+size_t photo_sum_doubles();
 // window fast path
 size_t win_shared_bytes();
 int launch_win_linearize_schur(const DevProblem& P, int init_pass, double lambda_override, cudaStream_t st);

@@ -212,6 +212,9 @@ __device__ __forceinline__ void butterfly_reduce(double (&v)[N], int lane)
     }
 }
 
+// PHOTO: photometric edges (ba_photo.cu): the 2 x 2 middle of a diagonal pair is the symmetric matrix w F C_tt F in ph_mid
+// instead of diag(w fx^2, w fy^2)
+template <bool PHOTO>
 __global__ void __launch_bounds__(128) k_schur_blocks(DevProblem P, int diag_only)
 {
     const int lane = threadIdx.x & 31;
@@ -253,8 +256,13 @@ __global__ void __launch_bounds__(128) k_schur_blocks(DevProblem P, int diag_onl
         double m11 = -(a3.y * b3.y + a4.x * b4.x + a4.y * b4.y);
         const bool same = pr.x == pr.y;
         if (same) {
-            m00 += a1.y * fx2;
-            m11 += a1.y * fy2;
+            if (PHOTO) {
+                const double* __restrict__ md = P.ph_mid + 4 * (size_t)pr.x;
+                m00 += md[0], m01 += md[1], m10 += md[1], m11 += md[2];
+            } else {
+                m00 += a1.y * fx2;
+                m11 += a1.y * fy2;
+            }
         }
         double t0[6], t1[6];
 #pragma unroll
@@ -504,6 +512,8 @@ __global__ void __launch_bounds__(256) k_solve_small(DevProblem P)
 // the point's share of g2o's computeScale  sum_j x_j (lambda x_j + b_j), and the robust
 // cost of the candidate state (K5 fused: the new point never leaves registers).
 // ------------------------------------------------------------------------------------------
+// PHOTO: the candidate cost needs the images: left to k_photo_sample + k_photo_cost (ba_photo.cu)
+template <bool PHOTO>
 __global__ void __launch_bounds__(128) k_update(DevProblem P)
 {
     const int p = P.pt_begin + blockIdx.x * blockDim.x + threadIdx.x;
@@ -549,6 +559,8 @@ __global__ void __launch_bounds__(128) k_update(DevProblem P)
     const double X = pt[0] + d0, Y = pt[1] + d1, Z = pt[2] + d2;
     double* pn = P.pts[cand] + 3 * (size_t)p;
     pn[0] = X, pn[1] = Y, pn[2] = Z;
+    P.scale_pt[p] = sc;
+    if (PHOTO) return;
     const double* __restrict__ cam_rt = P.cam_rt[cand];
     double cost = 0.0;
     for (int s = s0; s < s1; ++s) {
@@ -564,7 +576,6 @@ __global__ void __launch_bounds__(128) k_update(DevProblem P)
         cost += huber_rho(ru * ru + rv * rv, P.huber_delta, w);
     }
     P.cost_new_pt[p] = cost;
-    P.scale_pt[p] = sc;
 }
 
 // ------------------------------------------------------------------------------------------
@@ -666,7 +677,8 @@ int launch_schur_blocks(const DevProblem& P, int diag_only, cudaStream_t st)
 {
     const long long warps = diag_only ? P.n_diag_items : P.n_items;
     if (warps <= 0) return 0;
-    k_schur_blocks<<<cdiv(warps * 32, 128), 128, 0, st>>>(P, diag_only);
+    if (P.ph_sum) k_schur_blocks<true><<<cdiv(warps * 32, 128), 128, 0, st>>>(P, diag_only);
+    else k_schur_blocks<false><<<cdiv(warps * 32, 128), 128, 0, st>>>(P, diag_only);
     return 1;
 }
 
@@ -713,7 +725,8 @@ int launch_update(const DevProblem& P, cudaStream_t st)
 {
     const int np = P.pt_end - P.pt_begin;
     if (np <= 0) return 0;
-    k_update<<<cdiv(np, 128), 128, 0, st>>>(P);
+    if (P.ph_sum) k_update<true><<<cdiv(np, 128), 128, 0, st>>>(P);
+    else k_update<false><<<cdiv(np, 128), 128, 0, st>>>(P);
     return 1;
 }
 

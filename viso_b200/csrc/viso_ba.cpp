@@ -236,6 +236,12 @@ struct viso_ba {
     DevBuf raw, scratch, pairbuf, pts_stage;
     bool pts_staged = false;            // pts_stage holds the points exactly as `points` does (bulk set_problem)
     std::vector<int32_t> stage_c0, stage_p0; // source of an H2D copy that may still be in flight
+    // ---- photometric edges (ba_photo.cu): the handle holds either reprojection or photometric edges ----
+    bool photo = false;      // the staged edges are (point, source keyframe, pose vertex); e_uv carries the source index
+    bool photo_next = false; // a photometric bulk problem is being staged (keeps it off the window path)
+    std::vector<std::vector<uint8_t>> ph_img; // [pose] level-0 image of the pose's keyframe, rows * cols bytes (empty: none)
+    std::vector<int32_t> ph_rows, ph_cols;
+    DevBuf ph_img_dev, ph_frames_dev, ph_srcrt_dev, ph_sum_dev, ph_mid_dev;
     // ---- sharding ----
     int rank = 0, n_ranks = 1;
     void* comm = nullptr;
@@ -431,7 +437,7 @@ extern "C" void viso_ba_destroy(viso_ba* h)
         resolve_timing(h);
         if (h->comm && nccl_api()) nccl_api()->CommDestroy(h->comm);
         if (h->arena.base) cudaFree(h->arena.base);
-        for (DevBuf* b : { &h->raw, &h->scratch, &h->pairbuf, &h->pts_stage })
+        for (DevBuf* b : { &h->raw, &h->scratch, &h->pairbuf, &h->pts_stage, &h->ph_img_dev, &h->ph_frames_dev, &h->ph_srcrt_dev, &h->ph_sum_dev, &h->ph_mid_dev })
             if (b->p) cudaFree(b->p);
         if (h->pin) cudaFreeHost(h->pin);
         if (h->ev0) cudaEventDestroy(h->ev0);
@@ -446,6 +452,8 @@ extern "C" const char* viso_ba_last_error(const viso_ba* h) { return h ? h->err.
 extern "C" int32_t viso_ba_clear(viso_ba* h)
 {
     if (!h) return VISO_BA_ERR_ARG;
+    h->ph_img.clear(), h->ph_rows.clear(), h->ph_cols.clear(); // the keyframe images go with the poses
+    h->photo = false;
     h->poses.clear(), h->points.clear(), h->e_pose.clear(), h->e_point.clear(), h->e_uv.clear();
     h->fixed.clear();
     h->pose_off.clear(), h->point_off.clear(), h->edge_off.clear(), h->edge_off_all.clear();
@@ -494,6 +502,7 @@ extern "C" int32_t viso_ba_add_edge(viso_ba* h, int64_t point, int64_t pose, flo
     if (!h) return VISO_BA_ERR_ARG;
     if (!h->pose_off.empty()) return fail(h, VISO_BA_ERR_STATE, "handle holds a batched problem; clear it first");
     if (h->edges_on_device) return fail(h, VISO_BA_ERR_STATE, "handle holds a bulk problem; clear it first");
+    if (h->photo) return fail(h, VISO_BA_ERR_UNSUPPORTED, "handle holds photometric edges: reprojection and photometric edges do not mix");
     if ((int64_t)h->e_pose.size() >= h->cfg.max_edges) return fail(h, VISO_BA_ERR_CAPACITY, "edge pool full (%lld)", (long long)h->cfg.max_edges);
     if (point < 0 || point >= (int64_t)h->points.size() / 3) return fail(h, VISO_BA_ERR_INDEX, "edge refers to point %lld", (long long)point);
     if (pose < 0 || pose >= (int64_t)h->poses.size() / 7) return fail(h, VISO_BA_ERR_INDEX, "edge refers to pose %lld", (long long)pose);
@@ -599,7 +608,7 @@ int64_t tiles_upper_bound(int64_t B, const int64_t* point_off, const int64_t* ed
 // can this problem take the window path whatever the gauge turns out to be?
 bool window_shape_ok(const viso_ba* h, int64_t B, const int64_t* pose_off, int64_t Ne, int max_free)
 {
-    if (h->cfg.path == 2 || h->n_ranks != 1 || h->no_window) return false;
+    if (h->cfg.path == 2 || h->n_ranks != 1 || h->no_window || h->photo || h->photo_next) return false;
     if (h->cfg.path == 0 && Ne < (int64_t)kWinAutoMinTiles * kWinObsCap) return false; // too few tiles to fill the GPU
     for (int64_t b = 0; b < B; ++b)
         if (pose_off[b + 1] - pose_off[b] > std::min(max_free, kWinMaxCams)) return false;
@@ -760,6 +769,73 @@ extern "C" int32_t viso_ba_set_problem(viso_ba* h, int64_t n_poses, const double
 {
     const int64_t po[2] = { 0, n_poses }, pt[2] = { 0, n_points }, eo[2] = { 0, n_edges };
     return viso_ba_set_problem_batched(h, 1, po, pt, eo, poses7, points3, edge_pose, edge_point, edge_uv);
+}
+
+// ------------------------------------------------------------------------------------------
+// photometric edges: EdgeDirectProjection(srcFrame, targetFrame) between VertexPoint and VertexPose
+// (reference bundle_adjuster.h:58-106, :154-160).  The keyframe of a pose vertex is its level-0 image; an edge's
+// source keyframe is another pose's keyframe and projects with the pose that keyframe had at upload (:79).
+// ------------------------------------------------------------------------------------------
+namespace {
+inline float src_bits(int32_t src)
+{
+    float f;
+    std::memcpy(&f, &src, sizeof(f));
+    return f;
+}
+} // namespace
+
+extern "C" int32_t viso_ba_set_pose_image(viso_ba* h, int64_t pose, const uint8_t* data, int32_t rows, int32_t cols, int32_t stride)
+{
+    if (!h || !data) return VISO_BA_ERR_ARG;
+    if (pose < 0 || pose >= (int64_t)h->poses.size() / 7) return fail(h, VISO_BA_ERR_INDEX, "no pose %lld", (long long)pose);
+    if (rows < 8 || cols < 8 || stride < cols || rows > 16384 || cols > 16384) return fail(h, VISO_BA_ERR_ARG, "bad image size %d x %d (stride %d)", cols, rows, stride);
+    const size_t n = h->poses.size() / 7;
+    if (h->ph_img.size() < n) h->ph_img.resize(n), h->ph_rows.resize(n, 0), h->ph_cols.resize(n, 0);
+    std::vector<uint8_t>& im = h->ph_img[(size_t)pose];
+    im.resize((size_t)rows * (size_t)cols);
+    for (int32_t r = 0; r < rows; ++r) std::memcpy(im.data() + (size_t)r * cols, data + (size_t)r * stride, (size_t)cols);
+    h->ph_rows[(size_t)pose] = rows, h->ph_cols[(size_t)pose] = cols;
+    h->uploaded = false;
+    return VISO_BA_OK;
+}
+
+extern "C" int32_t viso_ba_add_photo_edge(viso_ba* h, int64_t point, int64_t src_pose, int64_t dst_pose)
+{
+    if (!h) return VISO_BA_ERR_ARG;
+    if (!h->pose_off.empty()) return fail(h, VISO_BA_ERR_STATE, "handle holds a batched problem; clear it first");
+    if (h->edges_on_device) return fail(h, VISO_BA_ERR_STATE, "handle holds a bulk problem; clear it first");
+    if (!h->photo && !h->e_pose.empty()) return fail(h, VISO_BA_ERR_UNSUPPORTED, "handle holds reprojection edges: reprojection and photometric edges do not mix");
+    if ((int64_t)h->e_pose.size() >= h->cfg.max_edges) return fail(h, VISO_BA_ERR_CAPACITY, "edge pool full (%lld)", (long long)h->cfg.max_edges);
+    const int64_t nc = (int64_t)h->poses.size() / 7;
+    if (point < 0 || point >= (int64_t)h->points.size() / 3) return fail(h, VISO_BA_ERR_INDEX, "edge refers to point %lld", (long long)point);
+    if (dst_pose < 0 || dst_pose >= nc) return fail(h, VISO_BA_ERR_INDEX, "edge refers to pose %lld", (long long)dst_pose);
+    if (src_pose < 0 || src_pose >= nc) return fail(h, VISO_BA_ERR_INDEX, "edge refers to source keyframe %lld", (long long)src_pose);
+    h->e_pose.push_back((int32_t)dst_pose);
+    h->e_point.push_back((int32_t)point);
+    h->e_uv.push_back(src_bits((int32_t)src_pose));
+    h->e_uv.push_back(0.f);
+    h->photo = true;
+    h->uploaded = false;
+    return VISO_BA_OK;
+}
+
+extern "C" int32_t viso_ba_set_photo_problem(viso_ba* h, int64_t n_poses, const double* poses7, int64_t n_points, const double* points3,
+    int64_t n_edges, const int32_t* edge_point, const int32_t* edge_src, const int32_t* edge_dst)
+{
+    if (!h) return VISO_BA_ERR_ARG;
+    if (n_edges < 0 || (n_edges && (!edge_point || !edge_src || !edge_dst))) return fail(h, VISO_BA_ERR_ARG, "null array");
+    std::vector<float> uv(2 * (size_t)n_edges, 0.f);
+    for (int64_t e = 0; e < n_edges; ++e) {
+        if (edge_src[e] < 0 || edge_src[e] >= n_poses) return fail(h, VISO_BA_ERR_INDEX, "edge %lld refers to source keyframe %d", (long long)e, edge_src[e]);
+        uv[2 * (size_t)e] = src_bits(edge_src[e]);
+    }
+    h->photo_next = true; // keeps the edges off the window path
+    const int32_t rc = viso_ba_set_problem(h, n_poses, poses7, n_points, points3, n_edges, edge_dst, edge_point, uv.data());
+    h->photo_next = false;
+    if (rc) return rc;
+    h->photo = n_edges > 0;
+    return VISO_BA_OK;
 }
 
 extern "C" int32_t viso_ba_set_pose_fixed(viso_ba* h, int64_t pose, int32_t fixed)
@@ -1347,6 +1423,55 @@ int32_t edges_back_to_host(viso_ba* h)
 
 } // namespace
 
+namespace {
+// device side of a photometric problem: the keyframe images, their descriptors, the per-edge sums
+int32_t upload_photo(viso_ba* h, int64_t Nc, int64_t Ne, int64_t B)
+{
+    if (B > 1 || h->n_ranks > 1) return fail(h, VISO_BA_ERR_UNSUPPORTED, "photometric edges: one problem on one GPU");
+    if (h->window || h->edges_on_device) return fail(h, VISO_BA_ERR_STATE, "internal: photometric edges on the window path");
+    std::vector<uint8_t> used((size_t)Nc, 0);
+    for (size_t e = 0; e < h->e_pose.size(); ++e) {
+        int32_t src;
+        std::memcpy(&src, &h->e_uv[2 * e], sizeof(src));
+        if (src < 0 || src >= Nc) return fail(h, VISO_BA_ERR_INDEX, "edge %zu refers to source keyframe %d", e, src);
+        used[(size_t)src] = 1, used[(size_t)h->e_pose[e]] = 1;
+    }
+    struct Img { const uint8_t* data; int32_t cols, rows, step, pad; }; // = visoimg::DevImage
+    std::vector<Img> frames((size_t)Nc);
+    size_t bytes = 0;
+    for (int64_t c = 0; c < Nc; ++c) {
+        const bool have = (size_t)c < h->ph_img.size() && !h->ph_img[(size_t)c].empty();
+        if (used[(size_t)c] && !have) return fail(h, VISO_BA_ERR_STATE, "pose %lld takes part in a photometric edge but has no image (viso_ba_set_pose_image)", (long long)c);
+        if (have) bytes += (h->ph_img[(size_t)c].size() + 255) & ~(size_t)255;
+    }
+    int32_t rc;
+    if ((rc = devbuf_reserve(h, h->ph_img_dev, bytes + 256)) || (rc = devbuf_reserve(h, h->ph_frames_dev, sizeof(Img) * (size_t)Nc))
+        || (rc = devbuf_reserve(h, h->ph_srcrt_dev, sizeof(double) * 12 * (size_t)Nc))
+        || (rc = devbuf_reserve(h, h->ph_sum_dev, sizeof(double) * photo_sum_doubles() * (size_t)std::max<int64_t>(Ne, 1)))
+        || (rc = devbuf_reserve(h, h->ph_mid_dev, sizeof(double) * 4 * (size_t)std::max<int64_t>(Ne, 1))))
+        return rc;
+    size_t off = 0;
+    for (int64_t c = 0; c < Nc; ++c) {
+        Img& f = frames[(size_t)c];
+        f.data = nullptr, f.cols = f.rows = f.step = f.pad = 0;
+        if ((size_t)c >= h->ph_img.size() || h->ph_img[(size_t)c].empty()) continue;
+        const std::vector<uint8_t>& im = h->ph_img[(size_t)c];
+        f.data = static_cast<const uint8_t*>(h->ph_img_dev.p) + off;
+        f.cols = h->ph_cols[(size_t)c], f.rows = h->ph_rows[(size_t)c], f.step = f.cols;
+        CU(cudaMemcpyAsync(const_cast<uint8_t*>(f.data), im.data(), im.size(), cudaMemcpyHostToDevice, h->stream));
+        off += (im.size() + 255) & ~(size_t)255;
+    }
+    CU(cudaMemcpyAsync(h->ph_frames_dev.p, frames.data(), sizeof(Img) * (size_t)Nc, cudaMemcpyHostToDevice, h->stream));
+    CU(cudaMemsetAsync(h->ph_sum_dev.p, 0, sizeof(double) * photo_sum_doubles() * (size_t)std::max<int64_t>(Ne, 1), h->stream));
+    CU(cudaStreamSynchronize(h->stream)); // `frames` dies here
+    h->P.ph_frames = h->ph_frames_dev.p;
+    h->P.ph_src_rt = static_cast<const double*>(h->ph_srcrt_dev.p);
+    h->P.ph_sum = static_cast<double*>(h->ph_sum_dev.p);
+    h->P.ph_mid = static_cast<double*>(h->ph_mid_dev.p);
+    return VISO_BA_OK;
+}
+} // namespace
+
 extern "C" int32_t viso_ba_upload(viso_ba* h)
 {
     if (!h) return VISO_BA_ERR_ARG;
@@ -1479,6 +1604,7 @@ extern "C" int32_t viso_ba_upload(viso_ba* h)
         CU(cudaMemsetAsync(d.S_blk, 0, sizeof(double) * (h->allreduce_count + (size_t)B * 2), h->stream));
         CU(cudaMemsetAsync(d.bs, 0, sizeof(double) * (size_t)Nc * 6, h->stream));
         CU(cudaMemsetAsync(d.dp, 0, sizeof(double) * (size_t)Nc * 6, h->stream));
+        if (h->photo && (rc = upload_photo(h, Nc, Ne, B))) break;
         rc = VISO_BA_OK;
         break;
     }
@@ -1505,6 +1631,8 @@ extern "C" int32_t viso_ba_reset_state(viso_ba* h)
     CU(cudaMemsetAsync(P.lm, 0, sizeof(LmState) * (size_t)P.n_problems, h->stream)); // cur = 0
     run_k(h, "state_init", [&] { return launch_state_init(P, 0, h->cfg.lm_max_trials, 0.0, h->stream); });
     run_k(h, "cam_rt", [&] { return launch_cam_rt(P, 0, h->stream); });
+    if (P.ph_sum) // srcFrame->Project uses the pose the keyframe had when the edges were made (bundle_adjuster.h:79): frozen here
+        CU(cudaMemcpyAsync(const_cast<double*>(P.ph_src_rt), P.cam_rt[0], sizeof(double) * 12 * (size_t)P.n_cams, cudaMemcpyDeviceToDevice, h->stream));
     CU(cudaGetLastError());
     return VISO_BA_OK;
 }
@@ -1550,7 +1678,12 @@ void enqueue_linearize(viso_ba* h, int init_pass, double lambda_override)
         run_k(h, "win_linearize_schur", [&] { return launch_win_linearize_schur(P, init_pass, lambda_override, st); });
         run_k(h, "win_finalize", [&] { return launch_win_finalize(P, init_pass, lambda_override, st); });
     } else {
-        run_k(h, "linearize", [&] { return launch_linearize(P, init_pass, lambda_override, st); });
+        if (P.ph_sum) { // photometric edges: sample the patches, then the photometric per-point pass
+            run_k(h, "photo_sample", [&] { return launch_photo_sample(P, 0, 1, lambda_override >= 0.0, st); });
+            run_k(h, "photo_linearize", [&] { return launch_photo_linearize(P, init_pass, lambda_override, st); });
+        } else {
+            run_k(h, "linearize", [&] { return launch_linearize(P, init_pass, lambda_override, st); });
+        }
         run_k(h, "schur_blocks", [&] { return launch_schur_blocks(P, init_pass, st); });
         run_k(h, "block_finalize", [&] { return launch_block_finalize(P, init_pass, lambda_override, st); });
     }
@@ -1574,6 +1707,10 @@ int32_t enqueue_trial(viso_ba* h)
     if (h->use_large) run_k(h, "solve_large", [&] { return launch_solve_large(P, h->L, st); });
     else run_k(h, "solve_small", [&] { return launch_solve_small(P, h->max_n, st); });
     run_k(h, "update", [&] { return launch_update(P, st); });
+    if (P.ph_sum) { // the candidate's cost needs the images again
+        run_k(h, "photo_sample", [&] { return launch_photo_sample(P, 1, 0, 0, st); });
+        run_k(h, "photo_cost", [&] { return launch_photo_cost(P, 1, 0, st); });
+    }
     run_k(h, "reduce", [&] { return launch_reduce(P, 1, st); });
     if ((rc = allreduce(h, P.prob_sums, 2 * (size_t)P.n_problems, kNcclSum))) return rc;
     run_k(h, "decide", [&] { return launch_decide(P, st); });
@@ -1796,7 +1933,12 @@ extern "C" int32_t viso_ba_eval_cost(viso_ba* h, double* cost)
         run_k(h, "win_linearize_schur", [&] { return launch_win_linearize_schur(P, 1, 0.0, h->stream); });
         run_k(h, "reduce", [&] { return launch_win_prob_sums(P, 1, h->stream); });
     } else {
-        run_k(h, "eval_cost", [&] { return launch_eval_cost(P, h->stream); });
+        if (P.ph_sum) {
+            run_k(h, "photo_sample", [&] { return launch_photo_sample(P, 0, 0, 1, h->stream); });
+            run_k(h, "photo_cost", [&] { return launch_photo_cost(P, 0, 1, h->stream); });
+        } else {
+            run_k(h, "eval_cost", [&] { return launch_eval_cost(P, h->stream); });
+        }
         run_k(h, "reduce", [&] { return launch_reduce(P, 2, h->stream); });
     }
     if ((rc = allreduce(h, P.prob_sums, 2 * (size_t)P.n_problems, kNcclSum))) return rc;
