@@ -15,6 +15,7 @@
 // is sorted by destination block, and every cross-thread sum is a fixed-shape tree, so the
 // result is bit-reproducible and independent of the order edges were added in.
 #include "ba_math.cuh"
+#include "ba_small_chol.cuh"
 
 namespace visoba {
 
@@ -417,22 +418,25 @@ __global__ void k_lm_init(DevProblem P, double tau, double lambda_init)
 // factorised by a right-looking Cholesky, back-substituted by one warp, and the candidate
 // poses  T' = exp(d) T  are written straight away.
 // ------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_solve_small(DevProblem P)
+// The body is shared with the single-window LM kernel (ba_window.cu): problem b, shared memory of small_smem_bytes(n8).
+__device__ void solve_small_problem(const DevProblem& P, int b, double* sm, int* s_fail)
 {
-    extern __shared__ double sm[];
-    __shared__ int s_fail;
-    const int b = blockIdx.x;
     LmState& st = P.lm[b];
-    if (!st.active) return;
     const int nf = P.prob_nfree[b];
-    const int n = 6 * nf;
-    const int ld = (n + 1) | 1;
+    const int n = 6 * nf, n8 = (n + 7) & ~7;
+    const int ld = small_ld(n8);
+    double* const rinv = sm + (size_t)(n8 + 1) * ld;
     const int tid = threadIdx.x, nt = blockDim.x;
     const int cam0 = P.prob_cam0[b], cam1 = P.prob_cam0[b + 1];
     const int tri0 = P.prob_tri0[b];
     const int cur = st.cur;
-    if (tid == 0) s_fail = 0;
-    // assemble the lower triangle
+    if (tid == 0) *s_fail = 0;
+    // assemble the lower triangle; rows / columns n .. n8 - 1 are identity padding, row n8 is the right-hand side
+    for (int idx = tid; idx < (n8 - n + 1) * ld; idx += nt) sm[n * ld + idx] = 0.0;
+    for (int i = n + tid; i < n8; i += nt)
+        for (int c = 0; c < n; ++c) sm[c * ld + i] = 0.0; // never read (upper triangle), kept clean
+    __syncthreads();
+    for (int i = n + tid; i < n8; i += nt) sm[i * ld + i] = 1.0;
     const int nblk = nf * (nf + 1) / 2;
     for (int idx = tid; idx < nblk * 36; idx += nt) {
         const int blk = idx / 36, e = idx - 36 * blk;
@@ -446,47 +450,20 @@ __global__ void __launch_bounds__(256) k_solve_small(DevProblem P)
     for (int c = cam0 + tid; c < cam1; c += nt) {
         const int f = P.cam_free[c];
         if (f >= 0)
-            for (int r = 0; r < 6; ++r) sm[n * ld + 6 * f + r] = P.bs[6 * (size_t)c + r];
+            for (int r = 0; r < 6; ++r) sm[n8 * ld + 6 * f + r] = P.bs[6 * (size_t)c + r];
     }
     __syncthreads();
-    const int warp = tid >> 5, lane = tid & 31, nw = nt >> 5;
-    for (int j = 0; j < n; ++j) {
-        if (tid == 0) {
-            const double d = sm[j * ld + j];
-            if (!(d > 0.0) || !isfinite(d)) s_fail = 1;
-            sm[j * ld + j] = sqrt(d);
-        }
-        __syncthreads();
-        if (s_fail) break;
-        const double inv = 1.0 / sm[j * ld + j];
-        for (int i = j + 1 + tid; i <= n; i += nt) sm[i * ld + j] *= inv;
-        __syncthreads();
-        for (int i = j + 1 + warp; i <= n; i += nw) {
-            const double lij = sm[i * ld + j];
-            const int kmax = i < n ? i : n - 1;
-            for (int k = j + 1 + lane; k <= kmax; k += 32) sm[i * ld + k] -= lij * sm[k * ld + j];
-        }
-        __syncthreads();
-    }
-    const int fail = s_fail;
-    // backward substitution  L^T x = y  (y sits in row n), one warp, row-contiguous reads
-    if (warp == 0 && !fail) {
-        double* y = sm + n * ld;
-        for (int j = n - 1; j >= 0; --j) {
-            const double xj = y[j] / sm[j * ld + j];
-            __syncwarp();
-            if (lane == 0) y[j] = xj;
-            for (int i = lane; i < j; i += 32) y[i] -= sm[j * ld + i] * xj;
-            __syncwarp();
-        }
-    }
+    small_chol_forward(sm, n8, ld, rinv, s_fail, tid, nt);
+    __syncthreads();
+    const int fail = *s_fail;
+    if (tid < 32 && !fail) small_backward_warp(sm, n8, ld, rinv, tid);
     __syncthreads();
     // scatter the step, build candidate poses
     const int cand = cur ^ 1;
     for (int c = cam0 + tid; c < cam1; c += nt) {
         const int f = P.cam_free[c];
         double d[6];
-        for (int r = 0; r < 6; ++r) d[r] = (f >= 0 && !fail) ? sm[n * ld + 6 * f + r] : 0.0;
+        for (int r = 0; r < 6; ++r) d[r] = (f >= 0 && !fail) ? sm[n8 * ld + 6 * f + r] : 0.0;
         for (int r = 0; r < 6; ++r) P.dp[6 * (size_t)c + r] = d[r];
         const double* pc = P.pose[cur] + 7 * (size_t)c;
         double* pn = P.pose[cand] + 7 * (size_t)c;
@@ -498,10 +475,19 @@ __global__ void __launch_bounds__(256) k_solve_small(DevProblem P)
     if (tid == 0) {
         double ss = 0.0;
         if (!fail)
-            for (int i = 0; i < n; ++i) ss += sm[n * ld + i] * sm[n * ld + i];
+            for (int i = 0; i < n; ++i) ss += sm[n8 * ld + i] * sm[n8 * ld + i];
         st.dp_sq = ss;
         st.ok2 = fail ? 0 : 1;
     }
+}
+
+__global__ void __launch_bounds__(256) k_solve_small(DevProblem P)
+{
+    extern __shared__ double sm[];
+    __shared__ int s_fail;
+    const int b = blockIdx.x;
+    if (!P.lm[b].active) return;
+    solve_small_problem(P, b, sm, &s_fail);
 }
 
 // K3 (large, one problem): ba_dense.cu
@@ -708,14 +694,12 @@ int launch_lm_init(const DevProblem& P, double tau, double lambda_init, cudaStre
 
 int launch_solve_small(const DevProblem& P, int max_n, cudaStream_t st)
 {
-    const int ld = (max_n + 1) | 1;
-    const size_t smem = sizeof(double) * (size_t)(max_n + 1) * (size_t)ld;
+    const int n8 = (max_n + 7) & ~7;
+    const size_t smem = small_smem_bytes(n8);
     static PerDeviceOnce once; // the largest system the kernel takes, once per device
-    constexpr size_t kMaxSmem = sizeof(double) * (size_t)(kSmallMaxN + 1) * (size_t)((kSmallMaxN + 1) | 1);
+    constexpr size_t kMaxSmem = small_smem_bytes(kSmallN8);
     if (smem > kMaxSmem) return 0;
     if (!once.run([] { return cudaFuncSetAttribute(k_solve_small, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxSmem) == cudaSuccess; })) return 0;
-    // more warps than the column has rows only lengthen the three barriers of a column step (C5, n = 54: 256 threads
-    // 101 us, 128 threads 80 us, 64 threads 105 us per launch)
     const int threads = max_n <= 64 ? 128 : 256;
     k_solve_small<<<P.n_problems, threads, smem, st>>>(P);
     return 1;
