@@ -67,7 +67,7 @@ typedef struct {
     int32_t path;          /* which kernels linearise: 0 = auto (default), 1 = window fast path
                               whenever eligible (every problem <= 32 keyframes and <= 27 free
                               poses, no duplicate edges, not sharded), 2 = general pair-list
-                              path.  Auto takes the window path when its tiles fill the GPU.   */
+                              path.  Auto takes the window path whenever the problem is eligible. */
     int32_t solver_segments; /* reduced systems beyond 27 free poses (one large problem): how the pose chain is cut for the
                               solve.  0 = auto (up to 8 interior segments when the co-visibility span is small against
                               the chain, as on a long trajectory), 1 = never (one envelope Cholesky), k >= 2 = up to k

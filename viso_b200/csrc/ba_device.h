@@ -71,7 +71,6 @@ constexpr int kWinObsCap = VISO_WIN_OBS_CAP; // observations per tile (their rec
 constexpr int kWinPtCap = VISO_WIN_PT_CAP;   // points per tile
 constexpr int kWinLsCtas = VISO_WIN_LS_CTAS; // CTAs of k_win_linearize_schur resident per SM (registers and shared memory)
 constexpr int kWinMaxCams = 32; // keyframes per problem (visibility mask is 32 bits)
-constexpr int kWinAutoMinTiles = 2 * 148; // "auto": fewer tiles than this cannot fill the GPU -> general path
 
 struct WinTile { // one CTA's share of a problem: consecutive points and all their observations
     int32_t prob, p0, np, o0, no, cam0, ncam, nf;
@@ -250,6 +249,7 @@ int launch_win_linearize_schur(const DevProblem& P, int init_pass, double lambda
 int launch_win_finalize(const DevProblem& P, int init_pass, double lambda_override, cudaStream_t st);
 int launch_win_update(const DevProblem& P, cudaStream_t st);
 int launch_win_prob_sums(const DevProblem& P, int even_if_inactive, cudaStream_t st);
+int launch_win_sums_decide(const DevProblem& P, cudaStream_t st); // prob_sums + decide of a trial in one launch
 int launch_win_active_tiles(const DevProblem& P, int32_t* map, cudaStream_t st);
 
 } // namespace visoba

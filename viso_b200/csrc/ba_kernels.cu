@@ -572,50 +572,7 @@ __global__ void k_decide(DevProblem P)
 {
     const int b = blockIdx.x * blockDim.x + threadIdx.x;
     if (b >= P.n_problems) return;
-    LmState& s = P.lm[b];
-    if (!s.active) return;
-    if (s.q == 0) {
-        s.chi_start = s.chi;
-        s.accepted = 0;
-    }
-    double chi_new = P.prob_sums[2 * (size_t)b];
-    if (!s.ok2) chi_new = DBL_MAX;
-    const double scale = P.prob_sums[2 * (size_t)b + 1] + s.lambda * s.dp_sq + 1e-3;
-    const double rho = (s.chi - chi_new) / scale;
-    s.rho = rho;
-    bool lambda_bad = false;
-    if (rho > 0.0 && isfinite(chi_new)) {
-        double alpha = 1.0 - (2.0 * rho - 1.0) * (2.0 * rho - 1.0) * (2.0 * rho - 1.0);
-        alpha = fmin(alpha, 2.0 / 3.0);
-        s.lambda *= fmax(1.0 / 3.0, alpha);
-        s.nu = 2.0;
-        s.chi = chi_new;
-        s.cur ^= 1;
-        s.accepted = 1;
-    } else {
-        s.lambda *= s.nu;
-        s.nu *= 2.0;
-        if (!isfinite(s.lambda)) lambda_bad = true;
-    }
-    s.q += 1;
-    s.trials += 1;
-    if (!lambda_bad && rho < 0.0 && s.q < s.max_trials) return; // another trial, same iteration
-    if (P.iter_stats && b == 0) {
-        IterStat& r = P.iter_stats[s.it];
-        r.cost_before = s.chi_start;
-        r.cost_after = s.chi;
-        r.lambda = s.lambda;
-        r.trials = s.q;
-        r.accepted = s.accepted;
-    }
-    const bool term = (s.q == s.max_trials) || rho == 0.0 || lambda_bad;
-    s.it += 1;
-    s.q = 0;
-    if (term) s.terminated = 1;
-    if (term || s.it >= s.target_it) {
-        s.active = 0;
-        atomicSub(P.n_active, 1);
-    }
+    lm_decide(P, b);
 }
 
 // ------------------------------------------------------------------------------------------

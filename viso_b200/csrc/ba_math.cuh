@@ -132,5 +132,55 @@ __device__ __forceinline__ void jtilde(double xn, double yn, double iz, double (
     r1[0] = 0.0, r1[1] = iz, r1[2] = -yn * iz, r1[3] = -(1.0 + yn * yn), r1[4] = xn * yn, r1[5] = xn;
 }
 
+// LM decision of problem b: g2o OptimizationAlgorithmLevenberg::solve, the part after the candidate has been evaluated
+// (prob_sums[b] = {candidate cost, point part of computeScale}).  Accepting flips `cur`; rejecting leaves the state.
+__device__ __forceinline__ void lm_decide(const DevProblem& P, int b)
+{
+    LmState& s = P.lm[b];
+    if (!s.active) return;
+    if (s.q == 0) {
+        s.chi_start = s.chi;
+        s.accepted = 0;
+    }
+    double chi_new = P.prob_sums[2 * (size_t)b];
+    if (!s.ok2) chi_new = DBL_MAX;
+    const double scale = P.prob_sums[2 * (size_t)b + 1] + s.lambda * s.dp_sq + 1e-3;
+    const double rho = (s.chi - chi_new) / scale;
+    s.rho = rho;
+    bool lambda_bad = false;
+    if (rho > 0.0 && isfinite(chi_new)) {
+        double alpha = 1.0 - (2.0 * rho - 1.0) * (2.0 * rho - 1.0) * (2.0 * rho - 1.0);
+        alpha = fmin(alpha, 2.0 / 3.0);
+        s.lambda *= fmax(1.0 / 3.0, alpha);
+        s.nu = 2.0;
+        s.chi = chi_new;
+        s.cur ^= 1;
+        s.accepted = 1;
+    } else {
+        s.lambda *= s.nu;
+        s.nu *= 2.0;
+        if (!isfinite(s.lambda)) lambda_bad = true;
+    }
+    s.q += 1;
+    s.trials += 1;
+    if (!lambda_bad && rho < 0.0 && s.q < s.max_trials) return; // another trial, same iteration
+    if (P.iter_stats && b == 0) {
+        IterStat& r = P.iter_stats[s.it];
+        r.cost_before = s.chi_start;
+        r.cost_after = s.chi;
+        r.lambda = s.lambda;
+        r.trials = s.q;
+        r.accepted = s.accepted;
+    }
+    const bool term = (s.q == s.max_trials) || rho == 0.0 || lambda_bad;
+    s.it += 1;
+    s.q = 0;
+    if (term) s.terminated = 1;
+    if (term || s.it >= s.target_it) {
+        s.active = 0;
+        atomicSub(P.n_active, 1);
+    }
+}
+
 } // namespace visoba
 #endif

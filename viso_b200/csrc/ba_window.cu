@@ -418,7 +418,8 @@ __global__ void __launch_bounds__(256) k_win_finalize(DevProblem P, int init_pas
     const double* __restrict__ part = P.tile_part + P.prob_part_off[b];
     const size_t stride = (size_t)nblk * kItemPart;
     const int tri0 = P.prob_tri0[b];
-    for (int idx = threadIdx.x; idx < nblk * kItemPart; idx += blockDim.x) {
+    // gridDim.y chunks per problem: a lone window's partials would otherwise be summed by ONE CTA (config 2: 8 MB)
+    for (int idx = blockIdx.y * blockDim.x + threadIdx.x; idx < nblk * kItemPart; idx += gridDim.y * blockDim.x) {
         const int blk = idx / kItemPart, e = idx - blk * kItemPart;
         const int cam = P.block_cam[tri0 + blk];
         if (cam < 0 && (e >= 36 || init_pass)) continue;
@@ -637,7 +638,11 @@ int launch_win_linearize_schur(const DevProblem& P, int init_pass, double lambda
 
 int launch_win_finalize(const DevProblem& P, int init_pass, double lambda_override, cudaStream_t st)
 {
-    k_win_finalize<<<P.n_problems, 256, 0, st>>>(P, init_pass, lambda_override);
+    // enough CTAs to fill the GPU: a batch of windows has them already (one CTA per problem reads its partials at the HBM
+    // roof), a few windows get their entries cut into chunks of 256
+    const int per = (int)(((long long)P.n_blocks * kItemPart / (P.n_problems > 0 ? P.n_problems : 1) + 255) / 256);
+    const int chunks = P.n_problems >= 296 ? 1 : (per < 1 ? 1 : (per > 64 ? 64 : per));
+    k_win_finalize<<<dim3((unsigned)P.n_problems, (unsigned)chunks), 256, 0, st>>>(P, init_pass, lambda_override);
     return 1;
 }
 
@@ -681,6 +686,33 @@ __global__ void __launch_bounds__(1024) k_win_active_tiles(DevProblem P, int32_t
 int launch_win_active_tiles(const DevProblem& P, int32_t* map, cudaStream_t st)
 {
     k_win_active_tiles<<<1, 1024, 0, st>>>(P, map);
+    return 1;
+}
+
+// the per-problem totals and the LM decision in one launch (one thread per problem: both are a few dozen operations)
+__global__ void k_win_sums_decide(DevProblem P)
+{
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= P.n_problems) return;
+    if (!P.lm[b].active) return;
+    double s0 = 0.0, s1 = 0.0; // in tile order; the loads of eight tiles go out together, the sums stay sequential
+    const int t1 = P.prob_tile_ptr[b + 1];
+    for (int t = P.prob_tile_ptr[b]; t < t1; t += 8) {
+        double2 v[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) v[k] = t + k < t1 ? *reinterpret_cast<const double2*>(P.tile_sums + 2 * (size_t)(t + k)) : make_double2(0.0, 0.0);
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+            if (t + k < t1) s0 += v[k].x, s1 += v[k].y;
+    }
+    P.prob_sums[2 * (size_t)b] = s0;
+    P.prob_sums[2 * (size_t)b + 1] = s1;
+    lm_decide(P, b);
+}
+
+int launch_win_sums_decide(const DevProblem& P, cudaStream_t st)
+{
+    k_win_sums_decide<<<(P.n_problems + 127) / 128, 128, 0, st>>>(P);
     return 1;
 }
 

@@ -609,7 +609,6 @@ int64_t tiles_upper_bound(int64_t B, const int64_t* point_off, const int64_t* ed
 bool window_shape_ok(const viso_ba* h, int64_t B, const int64_t* pose_off, int64_t Ne, int max_free)
 {
     if (h->cfg.path == 2 || h->n_ranks != 1 || h->no_window || h->photo || h->photo_next) return false;
-    if (h->cfg.path == 0 && Ne < (int64_t)kWinAutoMinTiles * kWinObsCap) return false; // too few tiles to fill the GPU
     for (int64_t b = 0; b < B; ++b)
         if (pose_off[b + 1] - pose_off[b] > std::min(max_free, kWinMaxCams)) return false;
     return true;
@@ -1698,8 +1697,7 @@ int32_t enqueue_trial(viso_ba* h)
         enqueue_linearize(h, 0, -1.0);
         run_k(h, "solve_small", [&] { return launch_solve_small(P, h->max_n, st); });
         run_k(h, "win_update", [&] { return launch_win_update(P, st); });
-        run_k(h, "reduce", [&] { return launch_win_prob_sums(P, 0, st); });
-        run_k(h, "decide", [&] { return launch_decide(P, st); });
+        run_k(h, "decide", [&] { return launch_win_sums_decide(P, st); }); // per-problem totals + the LM decision
         return VISO_BA_OK;
     }
     enqueue_linearize(h, 0, -1.0);
