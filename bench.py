@@ -646,11 +646,26 @@ def others(vb, args, device):
                 ms.append(ba.optimize_resident(args.lm_iters).device_ms)
             m = float(np.median(ms))
             out[name] = {"value": len(b["edge_pose"]) * s.trials / (m * 1e-3), "unit": UNIT, "ms_per_step": m,
+                         "us_per_lm_iteration": 1e3 * m / max(1, s.trials),
                          "lm_iters_per_sec": s.trials / (m * 1e-3), "observations": len(b["edge_pose"]),
                          "final_cost": s.final_cost, "note": "device-resident, L2 not flushed"}
+            if name in ("c1", "c2"):  # the VO call (reference src/viso.cpp:121): one window per Optimize, host buffers in and out
+                wall = []
+                for _ in range(5):
+                    t0 = time.perf_counter()
+                    set_problem(ba, b)
+                    se = ba.Optimize(args.lm_iters)
+                    wall.append(time.perf_counter() - t0)
+                w = float(np.median(wall))
+                out[name]["e2e"] = {"value": len(b["edge_pose"]) * se.trials / w, "unit": UNIT, "ms_per_step": 1e3 * w,
+                                    "final_cost": se.final_cost, "note": "set_problem + Optimize with host arrays: H2D, structure build, LM, D2H"}
             ba.close()
         except Exception as e:  # context only: never fail the headline because of it
             out[name] = {"error": str(e)}
+    try:
+        out["photo_ba"] = photo_leg(vb, device, args.lm_iters, cpu=not args.no_cpu)
+    except Exception as e:
+        out["photo_ba"] = {"error": str(e)}
     try:
         out["direct_pose"] = direct_leg(device, cpu=not args.no_cpu)
     except Exception as e:
@@ -660,6 +675,44 @@ def others(vb, args, device):
     except Exception as e:
         out["lk_align"] = {"error": str(e)}
     return out
+
+
+def photo_leg(vb, device, lm_iters, cpu=True):
+    """LM over the reference adjuster's photometric edge (reference include/bundle_adjuster.h:58-106): a
+    window of 6 keyframes (320 x 240) and 1500 points, 16 samples per edge.  Unit: edges x LM trials per second."""
+    from viso_b200.direct_synth import synth_photo_window
+    win = synth_photo_window(seed=9, n_frames=6, n_points=1500)
+    K = win["K"]
+    ba = vb.BundleAdjuster(len(win["points_init"]), len(win["poses_init"]), len(win["edge_point"]), device=device,
+                           fx=K[0], fy=K[1], cx=K[2], cy=K[3])
+    ba.set_photo_problem(win["poses_init"], win["points_init"], win["edge_point"], win["edge_src"], win["edge_dst"], win["images"])
+    ba.SetPoseFixed(0, True), ba.SetPoseFixed(1, True)
+    ba.upload()
+    ms = []
+    for i in range(8):
+        ba.reset_state()
+        s = ba.optimize_resident(lm_iters)
+        if i >= 3:
+            ms.append(s.device_ms)
+    m = float(np.median(ms))
+    ne = len(win["edge_point"])
+    res = {"edges": ne, "samples_per_edge": 16, "keyframes": len(win["poses_init"]), "points": len(win["points_init"]),
+           "unit": "edges x LM trials / s", "value": ne * s.trials / (m * 1e-3), "ms_per_step": m, "lm_trials_per_step": s.trials,
+           "initial_cost": s.initial_cost, "final_cost": s.final_cost}
+    ba.close()
+    if cpu:
+        import oracle_lib as orc
+        import photo_ba_oracle_lib as porc
+        sub = 150  # the oracle forms ONE dense system over poses and points: a bounded sample of the points
+        sel = win["edge_point"] < sub
+        t0 = time.perf_counter()
+        _, _, fc, it, st = porc.optimize(orc.cfg(K=K), win["images"], win["poses_init"], win["points_init"][:sub], win["edge_point"][sel],
+                                         win["edge_src"][sel], win["edge_dst"][sel], 3, fixed=[1, 1, 0, 0, 0, 0])
+        dt = time.perf_counter() - t0
+        tr = sum(x.trials for x in st)
+        res["cpu_oracle"] = {"value": int(sel.sum()) * tr / dt, "unit": res["unit"], "cores": 1, "kind": "port",
+                             "sample": "%d of the %d points, 3 LM iterations, dense normal equations" % (sub, len(win["points_init"]))}
+    return res
 
 
 def lk_leg(device, cpu=True, n_points=4000):

@@ -65,6 +65,11 @@ public:
     {
         pending_.push_back({ point, pose });
     }
+    // The reference's own edge (bundle_adjuster.h:58-106, :154-160): EdgeDirectProjection(srcFrame, targetFrame) between point
+    // and pose.  The keyframe of a pose vertex is its level-0 image (cv::Mat CV_8UC1: data, rows, cols, step); the source
+    // keyframe is named by its pose index and projects with the pose it had when Optimize was called (:79).
+    inline void SetPoseImage(int pose, const unsigned char* data, int rows, int cols, int step) { last_ = viso_ba_set_pose_image(h_, pose, data, rows, cols, step); }
+    inline void AddPhotoEdge(int point, int src_pose, int dst_pose) { last_ = viso_ba_add_photo_edge(h_, point, src_pose, dst_pose); }
     inline void SetEdgeMeasurement(int pending_index, double u, double v)
     {
         if (pending_index < 0 || pending_index >= (int)pending_.size()) {
