@@ -129,34 +129,53 @@ void direct_linearize(const direct_cfg* c, int32_t level, const direct_image* re
     accumulate(c, level, ref, cur, ref_pose, T21, points, n_points, H, b, cost, n_good);
 }
 
-/* update = H.inverse() * b (viso.cpp:735): Eigen inverts a 6x6 through a partially pivoted LU;
- * restated as Gauss-Jordan with partial pivoting on [H | I], then the product with b. */
+/* update = H.inverse() * b (viso.cpp:735).  Eigen's inverse() of a dynamic-free 6x6 goes through PartialPivLU: P H = L U with
+ * row pivoting, then the inverse column by column from the unit vectors.  Restated exactly that way (Doolittle LU in
+ * place, forward / backward substitution per column of the identity, then the product with b) — deliberately NOT the
+ * Gauss-Jordan tableau the device kernel uses (viso_b200/csrc/direct_pose.cu), so that the two statements of this solve
+ * are independent texts. */
 static void inverse_times(const double H[36], const double b[6], double x[6])
 {
-    double A[6][12];
-    for (int r = 0; r < 6; ++r)
-        for (int q = 0; q < 6; ++q) A[r][q] = H[6 * r + q], A[r][6 + q] = r == q ? 1.0 : 0.0;
-    for (int k = 0; k < 6; ++k) {
+    double LU[6][6], inv[6][6];
+    int perm[6];
+    for (int r = 0; r < 6; ++r) {
+        perm[r] = r;
+        for (int q = 0; q < 6; ++q) LU[r][q] = H[6 * r + q];
+    }
+    for (int k = 0; k < 6; ++k) { /* P H = L U: unit lower L below the diagonal, U on and above it */
         int p = k;
         for (int r = k + 1; r < 6; ++r)
-            if (fabs(A[r][k]) > fabs(A[p][k])) p = r;
-        if (p != k)
-            for (int q = 0; q < 12; ++q) {
-                const double t = A[k][q];
-                A[k][q] = A[p][q], A[p][q] = t;
+            if (fabs(LU[r][k]) > fabs(LU[p][k])) p = r;
+        if (p != k) {
+            for (int q = 0; q < 6; ++q) {
+                const double t = LU[k][q];
+                LU[k][q] = LU[p][q], LU[p][q] = t;
             }
-        const double inv = 1.0 / A[k][k]; /* singular H: inf / NaN propagate like in the reference */
-        for (int q = 0; q < 12; ++q) A[k][q] *= inv;
+            const int t = perm[k];
+            perm[k] = perm[p], perm[p] = t;
+        }
+        for (int r = k + 1; r < 6; ++r) { /* singular H: inf / NaN propagate like in the reference */
+            LU[r][k] /= LU[k][k];
+            for (int q = k + 1; q < 6; ++q) LU[r][q] -= LU[r][k] * LU[k][q];
+        }
+    }
+    for (int col = 0; col < 6; ++col) { /* column `col` of the inverse: L U z = P e_col */
+        double y[6];
         for (int r = 0; r < 6; ++r) {
-            if (r == k) continue;
-            const double f = A[r][k];
-            for (int q = 0; q < 12; ++q) A[r][q] -= f * A[k][q];
+            double v = perm[r] == col ? 1.0 : 0.0;
+            for (int q = 0; q < r; ++q) v -= LU[r][q] * y[q];
+            y[r] = v;
+        }
+        for (int r = 5; r >= 0; --r) {
+            double v = y[r];
+            for (int q = r + 1; q < 6; ++q) v -= LU[r][q] * inv[q][col];
+            inv[r][col] = v / LU[r][r];
         }
     }
     for (int r = 0; r < 6; ++r) {
-        double s = 0.0;
-        for (int q = 0; q < 6; ++q) s += A[r][6 + q] * b[q];
-        x[r] = s;
+        double v = 0.0;
+        for (int q = 0; q < 6; ++q) v += inv[r][q] * b[q];
+        x[r] = v;
     }
 }
 

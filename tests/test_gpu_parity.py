@@ -490,3 +490,19 @@ def test_stream_of_batches_through_two_handles_is_bit_identical(vb):
     fresh = vb.BundleAdjuster(8, 2, 8)
     with pytest.raises(vb.VisoBaError):
         fresh.download()
+
+
+@pytest.mark.parametrize("n_poses", [2, 3, 5, 12, 17, 28])
+def test_small_solver_sizes_and_padding(vb, oracle, n_poses):
+    """the blocked shared-memory Cholesky (ba_small_chol.cuh) pads n = 6 * free poses to a multiple of 8: every residue of
+    the padding (n = 6, 12, 24, 66, 96) and the largest system it takes (27 free poses, n = 162 -> 168), on both paths"""
+    p = vb.synth_config(1, n_poses=n_poses, n_points=60 * n_poses, target_edges=60 * n_poses * min(n_poses, 6), seed=0x5EED0300 + n_poses)
+    c = oracle.cfg()
+    poses, points, fc, it, ostats = oracle.optimize(c, *_args(p), 4)
+    for path in (1, 2):
+        ba = _adjuster(vb, p, path=path)
+        s, stats = ba.Optimize(4, with_stats=True)
+        assert s.iterations == it and [x.trials for x in stats] == [x.trials for x in ostats]
+        assert s.final_cost == pytest.approx(fc, rel=1e-10)
+        _quat_close(ba.poses(), poses, 1e-9)
+        assert np.abs(ba.points() - points).max() < 1e-8
