@@ -346,6 +346,31 @@ def roofline(ktimes, trials_per_problem, sizes, nprob=1):
 # ---------------------------------------------------------------------------------------------
 # the B200 arm
 # ---------------------------------------------------------------------------------------------
+def bind_to_gpu_numa_node(torch, local):
+    """N ranks on one box: keep this rank's host threads, and with them the page-locked buffers it allocates from here on
+    (first touch), on the NUMA node its GPU hangs off.  Eight ranks x two host threads x 345 MB per step otherwise meet on
+    whatever node the launcher left them on.  Best effort: returns the node, or None when sysfs does not say."""
+    try:
+        bus = torch.cuda.get_device_properties(local).pci_bus_id
+        dom = getattr(torch.cuda.get_device_properties(local), "pci_domain_id", 0)
+        dev = getattr(torch.cuda.get_device_properties(local), "pci_device_id", 0)
+        path = "/sys/bus/pci/devices/%04x:%02x:%02x.0/numa_node" % (dom, bus, dev)
+        node = int(open(path).read().strip())
+        if node < 0:
+            return None
+        cpus = set()
+        for part in open("/sys/devices/system/node/node%d/cpulist" % node).read().strip().split(","):
+            lo, _, hi = part.partition("-")
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return node
+    except Exception:
+        return None
+
+
 def run_b200(args):
     import torch
     import torch.distributed as dist
@@ -360,6 +385,7 @@ def run_b200(args):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a B200: no CUDA device is visible and this backend has no CPU fallback")
     torch.cuda.set_device(local)
+    numa = bind_to_gpu_numa_node(torch, local) if world > 1 else None
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
@@ -508,6 +534,7 @@ def run_b200(args):
             "problems_per_gpu": nprob, "observations_per_gpu": No, "points_per_gpu": Np, "poses_per_gpu": Nc,
             "parallelism": ("point-sharded x%d + fp64 NCCL allreduce" % world) if sharded else ("replicas x%d" % world),
             "l2": "flushed between steps (256 MiB write)" if flush is not None else "working set larger than L2 (126 MB)",
+            "host_numa_node": numa,
         },
         "lm_iters_per_sec": lm_trials_job / (ms_per_step * 1e-3),
         "lm_trials_per_step": lm_trials_job, "final_cost": s.final_cost,
