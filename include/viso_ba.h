@@ -217,6 +217,11 @@ int32_t viso_ba_eval_cost(viso_ba* h, double* cost);
 int32_t viso_ba_debug_reduced_system(viso_ba* h, double lambda, int32_t n_cap, double* S,
                                      double* bs, int32_t* n_out);
 
+/* debug / test hook: the host part of the general structure build (sort by point and pose, pair lists by S block, work
+ * items) with `threads` host threads (<= 0: the default policy); needs no GPU.  The checksum covers every table it builds:
+ * it must not depend on the thread count. */
+int32_t viso_ba_debug_host_build(viso_ba* h, int32_t threads, double* ms_out, uint64_t* checksum_out);
+
 /* launch accounting for bench.py: kernels launched by this handle since creation */
 int64_t viso_ba_kernel_launches(const viso_ba* h);
 /* algorithmic bytes / per-kernel device time of the last optimize call (bench roofline) */

@@ -172,3 +172,17 @@ def test_synthetic_generator_is_deterministic_and_well_formed(vb):
     w0, w1 = vb.synth_config(5, 0), vb.synth_config(5, 1)
     assert not np.array_equal(w0["points_init"], w1["points_init"])
     assert abs(a["points_true"][:, 2].mean() - 1.0) < 0.1  # mean depth 1 (viso.cpp:622-637)
+
+
+def test_host_structure_build_does_not_depend_on_the_thread_count():
+    """the general path's host build (sort by point and pose, pair lists by S block, work items) on 1, 3 and 8 host
+    threads: identical tables (no GPU needed: viso_ba_debug_host_build)"""
+    import viso_b200 as vb
+    for kw in (dict(config_id=3, n_poses=40, n_points=9000, target_edges=60000), dict(config_id=4, n_poses=120, n_points=12000, target_edges=90000)):
+        cid = kw.pop("config_id")
+        p = vb.synth_config(cid, **kw)
+        ba = vb.BundleAdjuster(len(p["points_init"]), len(p["poses_init"]), len(p["edge_pose"]), path=2)
+        ba.set_problem(p["poses_init"], p["points_init"], p["edge_pose"], p["edge_point"], p["edge_uv"])
+        sums = {t: ba.host_build(t)[1] for t in (1, 3, 8)}
+        assert len(set(sums.values())) == 1, sums
+        ba.close()

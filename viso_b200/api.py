@@ -116,6 +116,7 @@ SYMBOLS = {
     "viso_ba_get_problem_summaries": (C.c_int32, [_P, C.POINTER(Summary)]),
     "viso_ba_eval_cost": (C.c_int32, [_P, _D]),
     "viso_ba_debug_reduced_system": (C.c_int32, [_P, C.c_double, C.c_int32, _D, _D, _I32]),
+    "viso_ba_debug_host_build": (C.c_int32, [_P, C.c_int32, _D, C.POINTER(C.c_uint64)]),
     "viso_ba_kernel_launches": (C.c_int64, [_P]),
     "viso_ba_set_kernel_timing": (C.c_int32, [_P, C.c_int32]),
     "viso_ba_get_kernel_times": (C.c_int32, [_P, C.c_int32, C.POINTER(KernelTime), _I32]),
@@ -373,6 +374,12 @@ class BundleAdjuster:
         S, bs = np.empty((n.value, n.value)), np.empty(n.value)
         self._check(self._lib.viso_ba_debug_reduced_system(self._h, float(lam), n.value, _dptr(S), _dptr(bs), C.byref(n)))
         return S, bs
+
+    def host_build(self, threads=0):
+        """host part of the general structure build alone (no GPU): (milliseconds, checksum of the tables)"""
+        ms, ck = C.c_double(), C.c_uint64()
+        self._check(self._lib.viso_ba_debug_host_build(self._h, int(threads), C.byref(ms), C.byref(ck)))
+        return ms.value, ck.value
 
     def kernel_launches(self):
         return int(self._lib.viso_ba_kernel_launches(self._h))

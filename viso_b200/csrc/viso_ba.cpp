@@ -242,6 +242,7 @@ struct viso_ba {
     std::vector<std::vector<uint8_t>> ph_img; // [pose] level-0 image of the pose's keyframe, rows * cols bytes (empty: none)
     std::vector<int32_t> ph_rows, ph_cols;
     DevBuf ph_img_dev, ph_frames_dev, ph_srcrt_dev, ph_sum_dev, ph_mid_dev;
+    int host_threads_override = 0; // > 0: host threads of the general structure build (debug / tests)
     // ---- sharding ----
     int rank = 0, n_ranks = 1;
     void* comm = nullptr;
@@ -288,6 +289,38 @@ int32_t fail(viso_ba* h, int32_t code, const char* fmt, ...)
         if (e_ != 0)                                                                            \
             return fail(h, VISO_BA_ERR_NCCL, "%s: %s", #call, nccl_api()->GetErrorString(e_));  \
     } while (0)
+
+// ---- host threads of the general structure build ----
+// The pair-list build of a large problem is tens of millions of simple operations (config 4: 55 M pairs); it runs on a few
+// host threads, each on a contiguous range of points, and produces exactly the tables the one-thread build does (the
+// lists are ordered by point, ranges are taken in order).  VISO_BA_HOST_THREADS overrides the count (1 = serial).
+int host_threads(const viso_ba* h)
+{
+    if (h->host_threads_override > 0) return h->host_threads_override;
+    if (const char* e = std::getenv("VISO_BA_HOST_THREADS")) {
+        const int v = std::atoi(e);
+        if (v > 0) return std::min(v, 64);
+    }
+    unsigned hw = std::thread::hardware_concurrency();
+    if (hw == 0) hw = 1;
+    const int per_rank = (int)hw / std::max(1, h->n_ranks); // the ranks of a sharded problem share one box
+    return std::max(1, std::min(16, per_rank));
+}
+
+template <typename F> void parallel_ranges(int nt, int64_t lo, int64_t hi, F&& f)
+{ // f(t, range_lo, range_hi) on nt contiguous ranges of [lo, hi)
+    if (nt <= 1 || hi - lo < 4096) {
+        f(0, lo, hi);
+        return;
+    }
+    std::vector<std::thread> th;
+    th.reserve((size_t)nt);
+    for (int t = 0; t < nt; ++t) {
+        const int64_t a = lo + (hi - lo) * t / nt, b = lo + (hi - lo) * (t + 1) / nt;
+        th.emplace_back([&f, t, a, b] { f(t, a, b); });
+    }
+    for (std::thread& x : th) x.join();
+}
 
 void drop_graph(viso_ba* h)
 {
@@ -698,16 +731,26 @@ extern "C" int32_t viso_ba_set_problem_batched(viso_ba* h, int64_t B, const int6
     // usable device: the edges never touch host memory of this library
     h->no_window = false; // a duplicate edge of the PREVIOUS problem says nothing about this one
     const bool direct = Nc > 0 && Np > 0 && window_shape_ok(h, B, pose_off, Ne, kSmallMaxN / 6) && ensure_cuda(h) == VISO_BA_OK;
-    if (!direct) {
+    const int nt_host = host_threads(h);
+    if (!direct) { // validation of the edges on a few host threads: the first offending edge (lowest index) is reported
         for (int64_t b = 0; b < B; ++b) {
             const int64_t nc = pose_off[b + 1] - pose_off[b], np = point_off[b + 1] - point_off[b];
-            for (int64_t e = edge_off[b]; e < edge_off[b + 1]; ++e) {
+            std::vector<int64_t> bad((size_t)nt_host, -1);
+            parallel_ranges(nt_host, edge_off[b], edge_off[b + 1], [&](int t, int64_t lo, int64_t hi) {
+                for (int64_t e = lo; e < hi; ++e)
+                    if (edge_pose[e] < 0 || edge_pose[e] >= nc || edge_point[e] < 0 || edge_point[e] >= np || !std::isfinite(edge_uv[2 * e])
+                        || !std::isfinite(edge_uv[2 * e + 1])) {
+                        bad[(size_t)t] = e;
+                        return;
+                    }
+            });
+            for (int64_t e : bad) {
+                if (e < 0) continue;
                 if (edge_pose[e] < 0 || edge_pose[e] >= nc) return fail(h, VISO_BA_ERR_INDEX, "edge %lld refers to pose %d", (long long)e, edge_pose[e]);
                 if (edge_point[e] < 0 || edge_point[e] >= np) return fail(h, VISO_BA_ERR_INDEX, "edge %lld refers to point %d", (long long)e, edge_point[e]);
+                return fail(h, VISO_BA_ERR_NONFINITE, "edge_uv[%lld] is not finite", (long long)(std::isfinite(edge_uv[2 * e]) ? 2 * e + 1 : 2 * e));
             }
         }
-        for (int64_t e = 0; e < 2 * Ne; ++e)
-            if (!std::isfinite(edge_uv[e])) return fail(h, VISO_BA_ERR_NONFINITE, "edge_uv[%lld] is not finite", (long long)e);
     }
     viso_ba_clear(h);
     if (direct) {
@@ -742,14 +785,17 @@ extern "C" int32_t viso_ba_set_problem_batched(viso_ba* h, int64_t B, const int6
         h->edges_on_device = true, h->edges_local = true, h->n_edges_dev = Ne;
         h->pts_staged = true;
     } else {
-        h->e_uv.assign(edge_uv, edge_uv + 2 * Ne);
+        h->e_uv.resize(2 * (size_t)Ne);
         h->e_pose.resize((size_t)Ne);
         h->e_point.resize((size_t)Ne);
         for (int64_t b = 0; b < B; ++b) // store GLOBAL indices
-            for (int64_t e = edge_off[b]; e < edge_off[b + 1]; ++e) {
-                h->e_pose[(size_t)e] = (int32_t)(edge_pose[e] + pose_off[b]);
-                h->e_point[(size_t)e] = (int32_t)(edge_point[e] + point_off[b]);
-            }
+            parallel_ranges(B == 1 ? nt_host : 1, edge_off[b], edge_off[b + 1], [&](int, int64_t lo, int64_t hi) {
+                for (int64_t e = lo; e < hi; ++e) {
+                    h->e_pose[(size_t)e] = (int32_t)(edge_pose[e] + pose_off[b]);
+                    h->e_point[(size_t)e] = (int32_t)(edge_point[e] + point_off[b]);
+                    h->e_uv[2 * (size_t)e] = edge_uv[2 * e], h->e_uv[2 * (size_t)e + 1] = edge_uv[2 * e + 1];
+                }
+            });
     }
     h->poses.assign(poses7, poses7 + 7 * Nc);
     h->fixed.assign((size_t)Nc, -1);
@@ -998,43 +1044,57 @@ int32_t build_general(viso_ba* h, Built& b)
     const int64_t Nc = (int64_t)h->poses.size() / 7, Np = (int64_t)h->points.size() / 3;
     const int64_t Ne = (int64_t)h->e_pose.size();
     const int64_t B = h->n_problems;
+    const double t_begin = now_ms();
     const std::vector<int64_t>& pt0 = b.pt0;
     b.pt_prob.assign((size_t)Np, 0);
     for (int64_t p = 0; p < B; ++p)
         for (int64_t q = pt0[(size_t)p]; q < pt0[(size_t)p + 1]; ++q) b.pt_prob[(size_t)q] = (int32_t)p;
     // ---- stable counting sort by point, then by pose inside each point ----
+    // every thread owns a contiguous range of POINTS and scans all edges for them: no shared counters, and the order of a
+    // point's edges stays the order they were added in (stable), whatever the thread count
+    const int nt = host_threads(h);
     b.pt_ptr.assign((size_t)Np + 1, 0);
-    for (int64_t e = 0; e < Ne; ++e) b.pt_ptr[(size_t)h->e_point[(size_t)e] + 1]++;
+    parallel_ranges(nt, 0, Np, [&](int, int64_t lo, int64_t hi) {
+        for (int64_t e = 0; e < Ne; ++e) {
+            const int32_t p = h->e_point[(size_t)e];
+            if (p >= lo && p < hi) b.pt_ptr[(size_t)p + 1]++;
+        }
+    });
     for (int64_t p = 0; p < Np; ++p) b.pt_ptr[(size_t)p + 1] += b.pt_ptr[(size_t)p];
     b.obs_cam.resize((size_t)Ne);
     b.obs_uv.resize((size_t)Ne * 2);
     {
         std::vector<int32_t> cur(b.pt_ptr.begin(), b.pt_ptr.end() - 1);
-        for (int64_t e = 0; e < Ne; ++e) {
-            const int32_t s = cur[(size_t)h->e_point[(size_t)e]]++;
-            b.obs_cam[(size_t)s] = h->e_pose[(size_t)e];
-            b.obs_uv[2 * (size_t)s] = h->e_uv[2 * (size_t)e];
-            b.obs_uv[2 * (size_t)s + 1] = h->e_uv[2 * (size_t)e + 1];
-        }
-    }
-    for (int64_t p = 0; p < Np; ++p) { // insertion sort: tracks are short
-        const int32_t s0 = b.pt_ptr[(size_t)p], s1 = b.pt_ptr[(size_t)p + 1];
-        for (int32_t i = s0 + 1; i < s1; ++i) {
-            const int32_t c = b.obs_cam[(size_t)i];
-            const float u = b.obs_uv[2 * (size_t)i], v = b.obs_uv[2 * (size_t)i + 1];
-            int32_t j = i - 1;
-            while (j >= s0 && b.obs_cam[(size_t)j] > c) {
-                b.obs_cam[(size_t)j + 1] = b.obs_cam[(size_t)j];
-                b.obs_uv[2 * (size_t)j + 2] = b.obs_uv[2 * (size_t)j];
-                b.obs_uv[2 * (size_t)j + 3] = b.obs_uv[2 * (size_t)j + 1];
-                --j;
+        parallel_ranges(nt, 0, Np, [&](int, int64_t lo, int64_t hi) {
+            for (int64_t e = 0; e < Ne; ++e) {
+                const int32_t p = h->e_point[(size_t)e];
+                if (p < lo || p >= hi) continue;
+                const int32_t s = cur[(size_t)p]++;
+                b.obs_cam[(size_t)s] = h->e_pose[(size_t)e];
+                b.obs_uv[2 * (size_t)s] = h->e_uv[2 * (size_t)e];
+                b.obs_uv[2 * (size_t)s + 1] = h->e_uv[2 * (size_t)e + 1];
             }
-            b.obs_cam[(size_t)j + 1] = c;
-            b.obs_uv[2 * (size_t)j + 2] = u;
-            b.obs_uv[2 * (size_t)j + 3] = v;
-        }
+            for (int64_t p = lo; p < hi; ++p) { // insertion sort by pose: tracks are short
+                const int32_t s0 = b.pt_ptr[(size_t)p], s1 = b.pt_ptr[(size_t)p + 1];
+                for (int32_t i = s0 + 1; i < s1; ++i) {
+                    const int32_t c = b.obs_cam[(size_t)i];
+                    const float u = b.obs_uv[2 * (size_t)i], v = b.obs_uv[2 * (size_t)i + 1];
+                    int32_t j = i - 1;
+                    while (j >= s0 && b.obs_cam[(size_t)j] > c) {
+                        b.obs_cam[(size_t)j + 1] = b.obs_cam[(size_t)j];
+                        b.obs_uv[2 * (size_t)j + 2] = b.obs_uv[2 * (size_t)j];
+                        b.obs_uv[2 * (size_t)j + 3] = b.obs_uv[2 * (size_t)j + 1];
+                        --j;
+                    }
+                    b.obs_cam[(size_t)j + 1] = c;
+                    b.obs_uv[2 * (size_t)j + 2] = u;
+                    b.obs_uv[2 * (size_t)j + 3] = v;
+                }
+            }
+        });
     }
 
+    const double t_sort = now_ms();
     // ---- this rank's point range (sharding: contiguous points, balanced on edge count) ----
     {
         std::vector<int64_t> bounds((size_t)h->n_ranks + 1);
@@ -1052,18 +1112,22 @@ int32_t build_general(viso_ba* h, Built& b)
         const int32_t nf = b.prob_nfree[0];
         std::vector<uint8_t> present((size_t)b.n_blocks, 0);
         for (int32_t f = 0; f < nf; ++f) present[(size_t)f * (f + 1) / 2 + f] = 1;
-        for (int64_t p = 0; p < Np; ++p) {
-            const int32_t s0 = b.pt_ptr[(size_t)p], s1 = b.pt_ptr[(size_t)p + 1];
-            for (int32_t a = s0; a < s1; ++a) {
-                const int32_t fa = b.cam_free[(size_t)b.obs_cam[(size_t)a]];
-                if (fa < 0) continue;
-                const size_t row = (size_t)fa * (fa + 1) / 2;
-                for (int32_t c = s0; c < a; ++c) {
-                    const int32_t fc = b.cam_free[(size_t)b.obs_cam[(size_t)c]];
-                    if (fc >= 0) present[row + (size_t)fc] = 1;
+        // every thread writes the same value (1) and nothing reads until the threads have joined
+        uint8_t* const pres = present.data();
+        parallel_ranges(nt, 0, Np, [&](int, int64_t lo, int64_t hi) {
+            for (int64_t p = lo; p < hi; ++p) {
+                const int32_t s0 = b.pt_ptr[(size_t)p], s1 = b.pt_ptr[(size_t)p + 1];
+                for (int32_t a = s0; a < s1; ++a) {
+                    const int32_t fa = b.cam_free[(size_t)b.obs_cam[(size_t)a]];
+                    if (fa < 0) continue;
+                    const size_t row = (size_t)fa * (fa + 1) / 2;
+                    for (int32_t c = s0; c < a; ++c) {
+                        const int32_t fc = b.cam_free[(size_t)b.obs_cam[(size_t)c]];
+                        if (fc >= 0 && !__atomic_load_n(&pres[row + (size_t)fc], __ATOMIC_RELAXED)) __atomic_store_n(&pres[row + (size_t)fc], (uint8_t)1, __ATOMIC_RELAXED);
+                    }
                 }
             }
-        }
+        });
         remap.assign((size_t)b.n_blocks, -1);
         int32_t k = 0;
         for (int32_t I = 0; I < nf; ++I)
@@ -1091,11 +1155,14 @@ int32_t build_general(viso_ba* h, Built& b)
         }
     }
 
+    const double t_struct = now_ms();
     // ---- pair list sorted by S block (two passes: count, fill) ----
+    // thread t takes the t-th contiguous range of this rank's points; inside a block the pairs of range 0 come first, then
+    // range 1, ...: the list is ordered by point exactly as a single pass over the points leaves it
     std::vector<int64_t> blk_ptr((size_t)b.n_blocks + 1, 0);
-    auto for_pairs = [&](auto&& emit0) {
+    auto for_pairs = [&](int64_t lo, int64_t hi, auto&& emit0) {
         auto emit = [&](int32_t blk, int32_t a, int32_t c) { emit0(b.compact ? remap[(size_t)blk] : blk, a, c); };
-        for (int32_t p = pt_begin; p < pt_end; ++p) {
+        for (int64_t p = lo; p < hi; ++p) {
             const int32_t tri0 = b.prob_tri0[(size_t)b.pt_prob[(size_t)p]];
             const int32_t s0 = b.pt_ptr[(size_t)p], s1 = b.pt_ptr[(size_t)p + 1];
             for (int32_t a = s0; a < s1; ++a) {
@@ -1109,20 +1176,34 @@ int32_t build_general(viso_ba* h, Built& b)
             }
         }
     };
-    for_pairs([&](int32_t blk, int32_t, int32_t) { blk_ptr[(size_t)blk + 1]++; });
-    for (int32_t k = 0; k < b.n_blocks; ++k) blk_ptr[(size_t)k + 1] += blk_ptr[(size_t)k];
+    const int ntp = (pt_end - pt_begin) >= 4096 ? nt : 1;
+    std::vector<std::vector<int64_t>> cnt((size_t)ntp, std::vector<int64_t>((size_t)b.n_blocks, 0));
+    parallel_ranges(ntp, pt_begin, pt_end, [&](int t, int64_t lo, int64_t hi) {
+        std::vector<int64_t>& c = cnt[(size_t)t];
+        for_pairs(lo, hi, [&](int32_t blk, int32_t, int32_t) { c[(size_t)blk]++; });
+    });
+    for (int32_t k = 0; k < b.n_blocks; ++k) { // cnt[t][k] becomes the first slot of thread t in block k
+        int64_t run = blk_ptr[(size_t)k];
+        for (int t = 0; t < ntp; ++t) {
+            const int64_t c = cnt[(size_t)t][(size_t)k];
+            cnt[(size_t)t][(size_t)k] = run;
+            run += c;
+        }
+        blk_ptr[(size_t)k + 1] = run;
+    }
     b.n_pairs = blk_ptr[(size_t)b.n_blocks];
     if (b.n_pairs > 0x7fffffff) return fail(h, VISO_BA_ERR_UNSUPPORTED, "pair list too long (%lld)", (long long)b.n_pairs);
     b.pairs.resize((size_t)b.n_pairs * 2);
-    {
-        std::vector<int64_t> cur(blk_ptr.begin(), blk_ptr.end() - 1);
-        for_pairs([&](int32_t blk, int32_t a, int32_t c) {
+    parallel_ranges(ntp, pt_begin, pt_end, [&](int t, int64_t lo, int64_t hi) {
+        std::vector<int64_t>& cur = cnt[(size_t)t];
+        for_pairs(lo, hi, [&](int32_t blk, int32_t a, int32_t c) {
             const int64_t q = cur[(size_t)blk]++;
             b.pairs[2 * (size_t)q] = a;
             b.pairs[2 * (size_t)q + 1] = c;
         });
-    }
+    });
 
+    const double t_pairs = now_ms();
     // ---- work items: slices of one block's pairs, one warp each ----
     int64_t item_pairs = (b.n_pairs / 16384 + 31) / 32 * 32;
     item_pairs = std::max<int64_t>(64, std::min<int64_t>(512, item_pairs));
@@ -1156,6 +1237,9 @@ int32_t build_general(viso_ba* h, Built& b)
         }
         b.prob_chunk_ptr[(size_t)p + 1] = (int32_t)(b.chunks.size() / 4);
     }
+    if (h->cfg.verbose)
+        fprintf(stderr, "[viso_ba] host structure build, %d threads: sort %.1f ms, block structure + solve plan %.1f ms, pair lists %.1f ms (%lld pairs), items %.1f ms\n",
+            nt, t_sort - t_begin, t_struct - t_sort, t_pairs - t_struct, (long long)b.n_pairs, now_ms() - t_pairs);
     return VISO_BA_OK;
 }
 
@@ -1615,6 +1699,38 @@ extern "C" int32_t viso_ba_upload(viso_ba* h)
     }
     CU(cudaStreamSynchronize(h->stream));
     h->setup_ms = (float)(now_ms() - t0);
+    return VISO_BA_OK;
+}
+
+// debug / test hook: the HOST part of the general structure build (tables, sort by point and pose, pair lists by S block,
+// work items) with `threads` host threads, no GPU needed: elapsed time and an FNV-1a checksum of everything it produced
+extern "C" int32_t viso_ba_debug_host_build(viso_ba* h, int32_t threads, double* ms_out, uint64_t* checksum_out)
+{
+    if (!h) return VISO_BA_ERR_ARG;
+    if (h->edges_on_device) return fail(h, VISO_BA_ERR_STATE, "the edges of this problem live on the device (window path)");
+    if (h->poses.size() < 7 || h->points.size() < 3) return fail(h, VISO_BA_ERR_STATE, "nothing staged");
+    const int keep = h->host_threads_override;
+    h->host_threads_override = threads > 0 ? threads : 0;
+    const double t0 = now_ms();
+    Built b;
+    int32_t rc = build_tables(h, b);
+    if (!rc) {
+        b.window = false;
+        rc = build_general(h, b);
+    }
+    const double t1 = now_ms();
+    h->host_threads_override = keep;
+    if (rc) return rc;
+    uint64_t x = 1469598103934665603ull;
+    auto mix = [&](const void* p, size_t n) {
+        const unsigned char* c = static_cast<const unsigned char*>(p);
+        for (size_t i = 0; i < n; ++i) x = (x ^ c[i]) * 1099511628211ull;
+    };
+    auto mixv = [&](const std::vector<int32_t>& v) { mix(v.data(), v.size() * sizeof(int32_t)); };
+    mixv(b.pt_ptr), mixv(b.obs_cam), mix(b.obs_uv.data(), b.obs_uv.size() * sizeof(float)), mixv(b.pairs), mixv(b.items);
+    mixv(b.diag_items), mixv(b.block_item_ptr), mixv(b.blk_ij), mixv(b.chunks), mix(&b.n_pairs, sizeof(b.n_pairs));
+    if (ms_out) *ms_out = t1 - t0;
+    if (checksum_out) *checksum_out = x;
     return VISO_BA_OK;
 }
 
