@@ -164,7 +164,7 @@ int main(int argc, char** argv)
         cudaMemcpyFromSymbol(c64, g_c64_prof, sizeof(c64));
         printf("cta_chol64 (CTA 0, last call), cycles: first 8x8 %lld, transpose %lld; per sub-step panel / next-diag+chol8 / wait:", c64[28], c64[29]);
         for (int i = 0; i < 7; ++i) printf("  %lld/%lld/%lld", c64[4 * i], c64[4 * i + 1], c64[4 * i + 2]);
-        printf("\n");
+        printf("\n  warp 0 after its panel rows, last sub-step: arrive %lld, next-diagonal update %lld cycles\n", c64[30], c64[31]);
         // lead (CTA 0): marks 0..5 = step start, diagonal entries loaded (after U of the previous step), panel there (B),
         // next diagonal block formed, factorised, published.  Worker (CTA 1): marks 8..13 = step start, factor loaded,
         // panel done, B passed, update done, U passed.

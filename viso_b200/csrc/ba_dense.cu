@@ -109,12 +109,22 @@ __device__ __forceinline__ void chol8_thread(double* D, double* rinv, int c0, in
         for (int j = 0; j <= i; ++j) D[(c0 + i) * kCS + c0 + j] = a[i * (i + 1) / 2 + j];
 }
 
-// Cholesky of the 64x64 block in D (lower triangle, row stride kCS) by the whole CTA, in place; LT[c][r] = L[r][c] and
-// rinv[c] = 1 / L[c][c] for the panel.  Returns true on a non-positive or non-finite pivot (uniform over the CTA).
-// Eight sub-steps of 8 columns: panel (one thread per row), then the remainder -= panel panel^T; the NEXT 8x8 diagonal
-// block is updated first by warp 0, whose lane 0 factorises it at once while the other warps finish the remainder, so
-// the single-thread pivot chain runs beside the parallel work instead of between two barriers.
-__device__ __forceinline__ bool cta_chol64(double* D, double* LT, double* rinv, int* s_fail, int tid)
+// named barriers of the CTA (id 0 is __syncthreads): a warp that has nothing to wait for ARRIVES and goes on
+__device__ __forceinline__ void bar_arrive(int id, int count)
+{
+    __threadfence_block();
+    asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(count) : "memory");
+}
+__device__ __forceinline__ void bar_sync(int id, int count) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory"); }
+
+// Cholesky of the 64x64 block in D (lower triangle, row stride kCS; the upper triangle is and stays zero) by the whole
+// CTA, in place; rinv[c] = 1 / L[c][c].  Returns true on a non-positive or non-finite pivot (uniform over the CTA).
+// Eight sub-steps of 8 columns.  Warp 0 carries the pivot chain: its lanes 0..7 solve the panel rows of the NEXT diagonal
+// block, it arrives at the panel barrier without waiting, updates that block (36 entries) and its lane 0 factorises it
+// in registers, while warps 1..7 wait for the whole panel and apply  remainder -= panel panel^T  in 2 x 2 micro-tiles.
+// The single-thread pivot chain thus runs beside the parallel work, and the chain never waits for a full-CTA barrier
+// between a panel and the diagonal block that depends on it.
+__device__ __forceinline__ bool cta_chol64(double* D, double* rinv, int* s_fail, int tid)
 {
 #ifdef VISO_CHOL_PROFILE
     long long pq0 = clock64(), pq1, pq2, pq3;
@@ -143,30 +153,40 @@ __device__ __forceinline__ bool cta_chol64(double* D, double* LT, double* rinv, 
 #pragma unroll
             for (int j = 0; j < 8; ++j) D[r * kCS + c0 + j] = x[j];
         }
-        __syncthreads();
 #ifdef VISO_CHOL_PROFILE
         pq1 = clock64();
 #endif
-        if (tid < 32) { // the next diagonal block first (36 entries: lanes 0..3 take two), then its factorisation by lane 0
-            int rr = 0;
-            while ((rr + 1) * (rr + 2) / 2 <= tid) ++rr;
-            const int cc = tid - rr * (rr + 1) / 2; // tid = 28..31 are the first entries of row 7; 32..35 the last four
+        if (tid < 32) { // the next diagonal block (36 entries: lanes 0..3 take two), then its factorisation by lane 0
+            __syncwarp(); // its panel rows are rows 0..7 of this warp
+            bar_arrive(1, kCT);
+#ifdef VISO_CHOL_PROFILE
+            const long long pa = clock64();
+#endif
+            // entry e = tid of the packed lower triangle: row rr, column cc (no loop: this is the pivot chain's time)
+            const int rr = tid >= 28 ? 7 : tid >= 21 ? 6 : tid >= 15 ? 5 : tid >= 10 ? 4 : tid >= 6 ? 3 : tid >= 3 ? 2 : tid >= 1 ? 1 : 0;
+            const int cc = tid - rr * (rr + 1) / 2; // tid = 28..31 are the first entries of row 7; entries 32..35 the last four
             const bool two = tid < 4;
             const double* pr = D + (c0 + 8 + rr) * kCS + c0;
             const double* pc = D + (c0 + 8 + cc) * kCS + c0;
             const double* pr2 = D + (c0 + 8 + 7) * kCS + c0;
-            const double* pc2 = D + (c0 + 8 + 4 + tid) * kCS + c0;
-            double s = 0.0, s2 = 0.0;
+            const double* pc2 = D + (c0 + 8 + 4 + (tid & 3)) * kCS + c0;
+            // two half-sums per entry: the dependent FMA chain is 4 + 1 long instead of 8
+            double sa = 0.0, sb = 0.0, s2a = 0.0, s2b = 0.0;
 #pragma unroll
-            for (int t = 0; t < 8; ++t) {
-                s = fma(pr[t], pc[t], s);
-                if (two) s2 = fma(pr2[t], pc2[t], s2);
+            for (int t = 0; t < 4; ++t) {
+                sa = fma(pr[t], pc[t], sa), sb = fma(pr[t + 4], pc[t + 4], sb);
+                s2a = fma(pr2[t], pc2[t], s2a), s2b = fma(pr2[t + 4], pc2[t + 4], s2b);
             }
-            D[(c0 + 8 + rr) * kCS + c0 + 8 + cc] -= s;
-            if (two) D[(c0 + 8 + 7) * kCS + c0 + 8 + 4 + tid] -= s2;
+            D[(c0 + 8 + rr) * kCS + c0 + 8 + cc] -= sa + sb;
+            if (two) D[(c0 + 8 + 7) * kCS + c0 + 8 + 4 + tid] -= s2a + s2b;
             __syncwarp();
+#ifdef VISO_CHOL_PROFILE
+            const long long pb = clock64();
+            if (c0 == 48) C64(30, pa - pq1), C64(31, pb - pa);
+#endif
             if (tid == 0) chol8_thread(D, rinv, c0 + 8, s_fail);
-        } else if (m > 8) {
+        } else {
+            bar_sync(1, kCT); // every panel row is written
             // remainder -= panel panel^T below the next diagonal block, in 2x2 micro-tiles of the lower triangle: tile rows
             // R = 4 .. m/2 - 1 hold R + 1 tiles each; row 4 + rp is folded with row m/2 - 1 - rp into one line of
             // W = m/2 + 5 tiles, so the enumeration is rectangular and no lane idles on the upper triangle
@@ -198,23 +218,14 @@ __device__ __forceinline__ bool cta_chol64(double* D, double* LT, double* rinv, 
         C64(c0 / 8 * 4 + 0, pq1 - pq0), C64(c0 / 8 * 4 + 1, pq2 - pq1), C64(c0 / 8 * 4 + 2, pq3 - pq2);
 #endif
     }
-#ifdef VISO_CHOL_PROFILE
-    pq0 = clock64();
-#endif
-    for (int idx = tid; idx < kCB * kCB; idx += kCT) {
-        const int r = idx >> 6, c = idx & 63;
-        LT[c * kCS + r] = c <= r ? D[r * kCS + c] : 0.0;
-    }
-    __syncthreads();
-    C64(29, clock64() - pq0);
     return *s_fail != 0;
 }
 
-// The factor of a diagonal block in T.Dd: L_kk row-major [64][64], then rinv[64], then the failure flag of the
-// factorisation so far (0 / 1), padded to kCholDdStride doubles.
-__device__ __forceinline__ void publish_factor(double* dd, const double* LT, const double* rinv, bool bad, int tid)
+// The factor of a diagonal block in T.Dd: L_kk row-major [64][64] (straight from the factorised block: its upper triangle
+// is zero), then rinv[64], then the failure flag of the factorisation so far (0 / 1), padded to kCholDdStride doubles.
+__device__ __forceinline__ void publish_factor(double* dd, const double* D, const double* rinv, bool bad, int tid)
 {
-    for (int idx = tid; idx < kCB * kCB; idx += kCT) dd[idx] = LT[(idx & 63) * kCS + (idx >> 6)];
+    for (int idx = tid; idx < kCB * kCB; idx += kCT) dd[idx] = D[(idx >> 6) * kCS + (idx & 63)];
     if (tid < kCB) dd[kCB * kCB + tid] = rinv[tid];
     if (tid == kCB) dd[kCB * kCB + kCB] = bad ? 1.0 : 0.0;
 }
@@ -264,10 +275,10 @@ __device__ __forceinline__ void ctr_wait(const unsigned int* ctr, unsigned int t
 // registers, lane = column (and column + 32).  x of a finished column lives in xv (off the dependent chain: shuffle ->
 // multiply -> FMA -> next shuffle); lanes left of the column see L^T entries that are zero and keep their values.
 template <int R>
-__device__ __forceinline__ void panel_rows(double* A, int ld, int j0, int base, int n1, int r2b, int n2, int nrows, int nrow,
+__device__ __forceinline__ void panel_rows(double* A, int ld, int j0, int base, int n1, int r2b, int n2, int nrows, int qb, int nrow,
                                            int first_warp, int n_warps, const double* LT, const double* rinv, int lane)
-{
-    for (int q0 = R * first_warp; q0 < nrow; q0 += R * n_warps) {
+{ // rows qb .. nrow - 1 of the step's row list
+    for (int q0 = qb + R * first_warp; q0 < nrow; q0 += R * n_warps) {
         double* a[R];
         double a0[R], a1[R], xv0[R], xv1[R];
 #pragma unroll
@@ -318,6 +329,8 @@ __device__ __forceinline__ void panel_rows(double* A, int ld, int j0, int base, 
 // it and publishes the factor (counter F).  The other CTAs are WORKERS: wait for factor k, panel of step k, (B), trailing
 // update of step k without the lead's tile, (U).  The lead's 64-pivot chain thus runs beside the workers' update instead
 // of in front of it, and no CTA repeats it.  A set of one CTA plays both roles in turn.
+// (Tried and dropped: the lead solving the next row block itself in shared memory — 8.5 us per step for the 64-row solve
+// against 5.3 us of waiting for the workers' panel: C3 491 -> 530 us.)
 __device__ bool task_factor(const CholTask& T, int gb, int G, unsigned int* bars, double* smd, int* s_fail, bool prof)
 {
     double* const D = smd;                // [kCB][kCS] diagonal block, then tile buffer of the trailing update
@@ -339,8 +352,8 @@ __device__ bool task_factor(const CholTask& T, int gb, int G, unsigned int* bars
             D[rr * kCS + c] = c <= rr ? __ldcg(A + (size_t)rr * ld + c) : 0.0;
         }
         __syncthreads();
-        if (cta_chol64(D, LT, rinv, s_fail, tid)) ok = false;
-        publish_factor(T.Dd, LT, rinv, !ok, tid);
+        if (cta_chol64(D, rinv, s_fail, tid)) ok = false;
+        publish_factor(T.Dd, D, rinv, !ok, tid);
         ctr_arrive(cF);
     }
     for (int k = 0; k < nsteps; ++k) {
@@ -360,9 +373,10 @@ __device__ bool task_factor(const CholTask& T, int gb, int G, unsigned int* bars
             if (load_factor(T.Dd + (size_t)k * kCholDdStride, LT, rinv, tid)) ok = false;
             PROF(prof && gb == 1, k, 9);
             const int nrow = n1 + n2 + 1, nwarps = nW * (kCT / 32), fw = w * (kCT / 32) + warp;
-            if (nrow > 2 * nwarps) panel_rows<4>(A, ld, j0, base, n1, r2b, n2, nrows, nrow, fw, nwarps, LT, rinv, lane);
-            else if (nrow > nwarps) panel_rows<2>(A, ld, j0, base, n1, r2b, n2, nrows, nrow, fw, nwarps, LT, rinv, lane);
-            else panel_rows<1>(A, ld, j0, base, n1, r2b, n2, nrows, nrow, fw, nwarps, LT, rinv, lane);
+            const int qb = 0;
+            if (nrow - qb > 2 * nwarps) panel_rows<4>(A, ld, j0, base, n1, r2b, n2, nrows, qb, nrow, fw, nwarps, LT, rinv, lane);
+            else if (nrow - qb > nwarps) panel_rows<2>(A, ld, j0, base, n1, r2b, n2, nrows, qb, nrow, fw, nwarps, LT, rinv, lane);
+            else panel_rows<1>(A, ld, j0, base, n1, r2b, n2, nrows, qb, nrow, fw, nwarps, LT, rinv, lane);
             PROF(prof && gb == 1, k, 10);
             ctr_arrive(cB);
         }
@@ -419,9 +433,9 @@ __device__ bool task_factor(const CholTask& T, int gb, int G, unsigned int* bars
                 }
             __syncthreads();
             PROF(prof, k, 3);
-            if (cta_chol64(D, LT, rinv, s_fail, tid)) ok = false;
+            if (cta_chol64(D, rinv, s_fail, tid)) ok = false;
             PROF(prof, k, 4);
-            publish_factor(T.Dd + (size_t)(k + 1) * kCholDdStride, LT, rinv, !ok, tid);
+            publish_factor(T.Dd + (size_t)(k + 1) * kCholDdStride, D, rinv, !ok, tid);
             ctr_arrive(cF);
             PROF(prof, k, 5);
         }
@@ -445,11 +459,29 @@ __device__ bool task_factor(const CholTask& T, int gb, int G, unsigned int* bars
                 const int l0 = tl < n1t ? base + kCB * tl : r2b + kCB * (tl - n1t);
                 const int ni = rhs ? 1 : kCB; // valid rows of the tile
                 __syncthreads();
-                for (int idx = tid; idx < kCB * kCB; idx += kCT) {
-                    const int r = idx >> 6, c = idx & 63;
-                    Pi[r * kCS + c] = r < ni ? __ldcg(A + (size_t)(i0 + r) * ld + j0 + c) : 0.0;
-                    Pl[r * kCS + c] = __ldcg(A + (size_t)(l0 + r) * ld + j0 + c);
+                const bool diag_tile = !rhs && ti == tl;
+                { // all 32 loads of the two panel tiles in flight at once (L2 latency is the cost of a tile, not its bytes)
+                    double vi[16], vl[16];
+#pragma unroll
+                    for (int q = 0; q < 16; ++q) {
+                        const int idx = tid + q * kCT, r = idx >> 6, c = idx & 63;
+                        vi[q] = r < ni ? __ldcg(A + (size_t)(i0 + r) * ld + j0 + c) : 0.0;
+                        vl[q] = __ldcg(A + (size_t)(l0 + r) * ld + j0 + c);
+                    }
+#pragma unroll
+                    for (int q = 0; q < 16; ++q) {
+                        const int idx = tid + q * kCT, r = idx >> 6, c = idx & 63;
+                        Pi[r * kCS + c] = vi[q], Pl[r * kCS + c] = vl[q];
+                    }
                 }
+                double old[4][4]; // the entries the tile updates, fetched now: their latency hides under the product
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const int r = ty + 16 * i, c = tx + 16 * j;
+                        old[i][j] = (r < ni && (!diag_tile || c <= r)) ? __ldcg(A + (size_t)(i0 + r) * ld + l0 + c) : 0.0;
+                    }
                 __syncthreads();
                 double acc[4][4] = {};
 #pragma unroll 4
@@ -464,16 +496,12 @@ __device__ bool task_factor(const CholTask& T, int gb, int G, unsigned int* bars
 #pragma unroll
                         for (int j = 0; j < 4; ++j) acc[i][j] = fma(av[i], bv[j], acc[i][j]);
                 }
-                const bool diag_tile = !rhs && ti == tl;
 #pragma unroll
                 for (int i = 0; i < 4; ++i)
 #pragma unroll
                     for (int j = 0; j < 4; ++j) {
                         const int r = ty + 16 * i, c = tx + 16 * j;
-                        if (r < ni && (!diag_tile || c <= r)) {
-                            double* e = A + (size_t)(i0 + r) * ld + l0 + c;
-                            *e = __ldcg(e) - acc[i][j];
-                        }
+                        if (r < ni && (!diag_tile || c <= r)) A[(size_t)(i0 + r) * ld + l0 + c] = old[i][j] - acc[i][j];
                     }
             }
             PROF(prof && gb == 1, k, 12);

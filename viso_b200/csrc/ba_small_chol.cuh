@@ -6,8 +6,9 @@
 // barriers and a shared-memory round trip per column):
 //     - the 8 x 8 diagonal block by ONE thread in registers: the pivot chain (rsqrt + two dependent FMAs per pivot);
 //     - panel: one thread per row below it,  x L88^T = a;
-//     - remainder -= panel panel^T in 2 x 2 micro-tiles of the lower triangle; warp 0 updates the NEXT diagonal block
-//       first and its lane 0 factorises it at once, so the pivot chain runs beside the remainder, not between barriers.
+//     - remainder -= panel panel^T in 2 x 2 micro-tiles of the lower triangle by warps 1..; warp 0 (whose lanes 0..7 own the
+//       panel rows of the NEXT diagonal block) arrives at the panel barrier without waiting, updates that block and its
+//       lane 0 factorises it at once: the pivot chain runs beside the remainder and never waits for a full-CTA barrier.
 // The right-hand side rides along as one more row, so the forward substitution falls out; the backward substitution
 // is one warp with the solution in registers (shuffle -> multiply -> FMA per unknown).  Everything is fp64 and in a fixed
 // order: bit-identical from run to run and between the two callers.
@@ -80,27 +81,31 @@ __device__ __forceinline__ void small_chol_forward(double* A, int n8, int ld, do
             for (int j = 0; j < 8; ++j) row[j] = x[j];
         }
         if (mt == 0) break;
-        __syncthreads();
-        if (tid < 32) { // the next diagonal block first (36 entries: lanes 0..3 take two), then its factorisation by lane 0
-            int rr = 0;
-            while ((rr + 1) * (rr + 2) / 2 <= tid) ++rr;
-            const int cc = tid - rr * (rr + 1) / 2;
+        if (tid < 32) { // the next diagonal block (36 entries: lanes 0..3 take two), then its factorisation by lane 0
+            __syncwarp();  // its panel rows are rows 0..7 of this warp: no need to wait for the other warps' rows
+            __threadfence_block();
+            asm volatile("bar.arrive 1, %0;" ::"r"(nt) : "memory");
+            // entry e = tid of the packed lower triangle: row rr, column cc (no loop: this is the pivot chain's time)
+            const int rr = tid >= 28 ? 7 : tid >= 21 ? 6 : tid >= 15 ? 5 : tid >= 10 ? 4 : tid >= 6 ? 3 : tid >= 3 ? 2 : tid >= 1 ? 1 : 0;
+            const int cc = tid - rr * (rr + 1) / 2; // tid = 28..31 are the first entries of row 7; entries 32..35 the last four
             const bool two = tid < 4;
             const double* pr = A + (c0 + 8 + rr) * ld + c0;
             const double* pc = A + (c0 + 8 + cc) * ld + c0;
             const double* pr2 = A + (c0 + 8 + 7) * ld + c0;
-            const double* pc2 = A + (c0 + 8 + 4 + tid) * ld + c0;
-            double s = 0.0, s2 = 0.0;
+            const double* pc2 = A + (c0 + 8 + 4 + (tid & 3)) * ld + c0;
+            // two half-sums per entry: the dependent FMA chain is 4 + 1 long instead of 8
+            double sa = 0.0, sb = 0.0, s2a = 0.0, s2b = 0.0;
 #pragma unroll
-            for (int t = 0; t < 8; ++t) {
-                s = fma(pr[t], pc[t], s);
-                if (two) s2 = fma(pr2[t], pc2[t], s2);
+            for (int t = 0; t < 4; ++t) {
+                sa = fma(pr[t], pc[t], sa), sb = fma(pr[t + 4], pc[t + 4], sb);
+                s2a = fma(pr2[t], pc2[t], s2a), s2b = fma(pr2[t + 4], pc2[t + 4], s2b);
             }
-            A[(c0 + 8 + rr) * ld + c0 + 8 + cc] -= s;
-            if (two) A[(c0 + 8 + 7) * ld + c0 + 8 + 4 + tid] -= s2;
+            A[(c0 + 8 + rr) * ld + c0 + 8 + cc] -= sa + sb;
+            if (two) A[(c0 + 8 + 7) * ld + c0 + 8 + 4 + tid] -= s2a + s2b;
             __syncwarp();
             if (tid == 0) small_chol8(A, ld, rinv, c0 + 8, s_fail);
         } else {
+            asm volatile("bar.sync 1, %0;" ::"r"(nt) : "memory"); // every panel row is written
             // triangle below the next diagonal block in 2 x 2 micro-tiles: tile rows R = 4 .. h - 1 hold R + 1 tiles each; row
             // 4 + rp is folded with row h - 1 - rp into one line of W = h + 5 tiles (rectangular enumeration, no idle
             // lanes on the upper triangle); then the right-hand side row, one entry per work item
