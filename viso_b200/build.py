@@ -5,6 +5,7 @@ The .so is git-ignored but travels to the GPU box with the gpurun snapshot.  nvc
 cross-compiles without a GPU, so this runs in the CPU container too.
 """
 import hashlib
+import glob
 import os
 import shutil
 import subprocess
@@ -18,7 +19,7 @@ STAMP = os.path.join(HERE, ".libviso_ba.stamp")
 SYNTH_LIB = os.path.join(HERE, "libviso_synth.so")
 SOURCES = ["ba_kernels.cu", "ba_window.cu", "ba_dense.cu", "ba_setup.cu", "ba_photo.cu", "direct_pose.cu", "lk_align.cu", "pyramid.cu", "viso_ba.cpp"]
 SYNTH_SOURCES = ["synth.cpp"]
-HEADERS = [os.path.join(CSRC, "ba_device.h"), os.path.join(CSRC, "ba_math.cuh"), os.path.join(CSRC, "ba_setup.h"), os.path.join(CSRC, "image_math.cuh"), os.path.join(ROOT, "include", "viso_ba.h"), os.path.join(ROOT, "include", "viso_ba_synth.h"), os.path.join(ROOT, "include", "viso_direct.h"), os.path.join(ROOT, "include", "viso_lk.h")]
+HEADERS = sorted(glob.glob(os.path.join(CSRC, "*.h")) + glob.glob(os.path.join(CSRC, "*.cuh"))) + [os.path.join(ROOT, "include", h) for h in ("viso_ba.h", "viso_ba_synth.h", "viso_direct.h", "viso_lk.h")]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "-Xcompiler", "-fPIC,-O2,-Wall", "-shared", "-cudart", "static",

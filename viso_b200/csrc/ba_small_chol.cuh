@@ -93,15 +93,12 @@ __device__ __forceinline__ void small_chol_forward(double* A, int n8, int ld, do
             const double* pc = A + (c0 + 8 + cc) * ld + c0;
             const double* pr2 = A + (c0 + 8 + 7) * ld + c0;
             const double* pc2 = A + (c0 + 8 + 4 + (tid & 3)) * ld + c0;
-            // two half-sums per entry: the dependent FMA chain is 4 + 1 long instead of 8
-            double sa = 0.0, sb = 0.0, s2a = 0.0, s2b = 0.0;
+            // one 8-term sum per entry, in the order every other entry of the remainder uses (same arithmetic for all)
+            double s = 0.0, s2 = 0.0;
 #pragma unroll
-            for (int t = 0; t < 4; ++t) {
-                sa = fma(pr[t], pc[t], sa), sb = fma(pr[t + 4], pc[t + 4], sb);
-                s2a = fma(pr2[t], pc2[t], s2a), s2b = fma(pr2[t + 4], pc2[t + 4], s2b);
-            }
-            A[(c0 + 8 + rr) * ld + c0 + 8 + cc] -= sa + sb;
-            if (two) A[(c0 + 8 + 7) * ld + c0 + 8 + 4 + tid] -= s2a + s2b;
+            for (int t = 0; t < 8; ++t) s = fma(pr[t], pc[t], s), s2 = fma(pr2[t], pc2[t], s2);
+            A[(c0 + 8 + rr) * ld + c0 + 8 + cc] -= s;
+            if (two) A[(c0 + 8 + 7) * ld + c0 + 8 + 4 + tid] -= s2;
             __syncwarp();
             if (tid == 0) small_chol8(A, ld, rinv, c0 + 8, s_fail);
         } else {
