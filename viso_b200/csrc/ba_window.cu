@@ -5,12 +5,15 @@
 // movement.  A problem's points are cut into TILES of consecutive points (<= kWinPtCap points,
 // <= kWinObsCap observations).  One CTA owns one tile and keeps every per-observation
 // quantity of the tile in shared memory, so that per LM trial HBM sees only
-//     linearize_schur : observations (12 B) + points (24 B) in, per-point 72 B + per-tile
-//                       partial reduced-system blocks out
+//     linearize_schur : observations (14 B) + points (24 B) + the tile's pair lists (4 B per pair, built once at upload by
+//                       ba_setup.cu from the per-point visibility masks) in, per-point 72 B + per-tile partial
+//                       reduced-system blocks out
 //     update          : observations + points + per-point 72 B in, points out
-// and no per-observation record, no materialised 6x3 cross block and no pair list exists in
-// global memory.  Which observations of a point meet in which S block is derived on the fly
-// from a 32-bit visibility mask per point (bit c = keyframe c of the window sees the point).
+// and no per-observation record and no materialised 6x3 cross block exists in global memory.
+//
+// Staging: the contiguous inputs of a tile (points, per-point records, the problem's R|t tables and pose steps) arrive by
+// TMA bulk copies (cp.async.bulk, completion on an mbarrier) issued by one thread, in the layout they have in global
+// memory; the observation words are coalesced 4 / 8 / 2-byte loads into registers.
 //
 // Shared-memory layout of the records: structure of arrays (six 16-byte chunks per
 // observation), observations ordered KEYFRAME-major inside the tile.  The pair phase of block
@@ -32,33 +35,69 @@ constexpr int kSub = 8;                         // lanes per S block
 constexpr int kSubsPerCta = kWinThreads / kSub; // blocks in flight per CTA
 constexpr int kWarps = kWinThreads / 32;
 constexpr int kObsPerThread = (kWinObsCap + kWinThreads - 1) / kWinThreads;
-constexpr int kPtStride = kWinPtCap + 1; // odd stride: the (point, coordinate) transposes stay conflict-free
+// points and per-point records live in shared memory in the layout of global memory, [point][3] and [point][9], so that one
+// bulk copy (TMA, cp.async.bulk + mbarrier) stages a tile's slice; a tile may start at an odd point, i.e. 8 bytes off the
+// 16-byte alignment the copy needs: it then starts one double early and the accessors skip that lead slot.  Strides 3 and 9
+// doubles are odd multiples of a bank pair: a half-warp of consecutive points hits 16 different bank pairs.
+constexpr int kPtDoubles = 3 * kWinPtCap + 2;   // + lead slot + padding to a multiple of 16 bytes
+constexpr int kInfoDoubles = 9 * kWinPtCap + 2;
 
 __host__ __device__ constexpr size_t align16(size_t x) { return (x + 15) & ~(size_t)15; }
 
 // ---- shared memory of k_win_linearize_schur (byte offsets) ----
 constexpr size_t kLsRec = 0;                                                   // double2 [6][kWinObsCap]
-constexpr size_t kLsPt = kLsRec + 6 * sizeof(double2) * kWinObsCap;            // double [3][kPtStride]
-constexpr size_t kLsInfo = kLsPt + sizeof(double) * 3 * kPtStride;             // double [9][kPtStride]
-constexpr size_t kLsRt = kLsPt + align16(sizeof(double) * 12 * kPtStride);
+constexpr size_t kLsPt = kLsRec + 6 * sizeof(double2) * kWinObsCap;            // double [lead + np][3]
+constexpr size_t kLsInfo = kLsPt + align16(sizeof(double) * kPtDoubles);       // double [np][9]
+constexpr size_t kLsRt = kLsInfo + align16(sizeof(double) * kInfoDoubles);     // double [kWinMaxCams][12]
 constexpr int kMaxBlkPtr = (kSmallMaxN / 6) * (kSmallMaxN / 6 + 1) / 2 + 1;
 constexpr size_t kLsBlkPtr = kLsRt + sizeof(double) * 12 * kWinMaxCams;        // u32 [kMaxBlkPtr]
 constexpr size_t kLsObs0 = kLsBlkPtr + align16(sizeof(unsigned) * kMaxBlkPtr); // u16 [kWinPtCap + 1]
 constexpr size_t kLsSlot = kLsObs0 + align16(sizeof(unsigned short) * (kWinPtCap + 1)); // u16 [kWinObsCap]
 constexpr size_t kLsRed = kLsSlot + align16(sizeof(unsigned short) * kWinObsCap);       // double [kWarps]
-constexpr size_t kLsBytes = kLsRed + sizeof(double) * kWarps;
+constexpr size_t kLsBar = align16(kLsRed + sizeof(double) * kWarps);                    // mbarrier of the bulk copies
+constexpr size_t kLsBytes = kLsBar + 16;
 
 // ---- shared memory of k_win_update ----
 constexpr size_t kUsTmp = 0;                                                   // double2 [2][kWinObsCap]
-constexpr size_t kUsPt = kUsTmp + 2 * sizeof(double2) * kWinObsCap;            // double [3][kPtStride]
-constexpr size_t kUsInfo = kUsPt + sizeof(double) * 3 * kPtStride;             // double [9][kPtStride]
-constexpr size_t kUsRt = align16(kUsInfo + sizeof(double) * 9 * kPtStride);    // double [kWinMaxCams][12] current
+constexpr size_t kUsPt = kUsTmp + 2 * sizeof(double2) * kWinObsCap;            // double [lead + np][3]
+constexpr size_t kUsInfo = kUsPt + align16(sizeof(double) * kPtDoubles);       // double [lead + np][9]
+constexpr size_t kUsRt = kUsInfo + align16(sizeof(double) * kInfoDoubles);     // double [kWinMaxCams][12] current
 constexpr size_t kUsRt2 = kUsRt + sizeof(double) * 12 * kWinMaxCams;           // candidate
 constexpr size_t kUsDp = kUsRt2 + sizeof(double) * 12 * kWinMaxCams;           // double [kWinMaxCams][6]
 constexpr size_t kUsObs0 = kUsDp + sizeof(double) * 6 * kWinMaxCams;           // u16 [kWinPtCap + 1]
 constexpr size_t kUsSlot = kUsObs0 + align16(sizeof(unsigned short) * (kWinPtCap + 1)); // u16 [kWinObsCap]
 constexpr size_t kUsRed = kUsSlot + align16(sizeof(unsigned short) * kWinObsCap);       // double [2][kWarps]
-constexpr size_t kUsBytes = kUsRed + sizeof(double) * 2 * kWarps;
+constexpr size_t kUsBar = align16(kUsRed + sizeof(double) * 2 * kWarps);
+constexpr size_t kUsBytes = kUsBar + 16;
+
+// ---- TMA bulk copies global -> shared, completion on an mbarrier (one per CTA, one phase: a CTA stages one tile) ----
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(void* bar, unsigned count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); // the async proxy must see the initialised barrier
+}
+__device__ __forceinline__ void mbar_expect_tx(void* bar, unsigned bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned bytes, void* bar)
+{ // dst, src 16-byte aligned, bytes a multiple of 16
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)), "l"(src),
+                 "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(void* bar, unsigned parity)
+{
+    unsigned done;
+    do {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(done)
+                     : "r"(smem_u32(bar)), "r"(parity)
+                     : "memory");
+    } while (!done);
+}
+__device__ __forceinline__ unsigned round16(unsigned x) { return (x + 15u) & ~15u; }
 
 // fixed-shape sum over the CTA: shuffles inside a warp, then the warp totals in warp order
 __device__ __forceinline__ double cta_sum(double v, double* red, int tid)
@@ -130,6 +169,11 @@ __global__ void __launch_bounds__(kWinThreads, kWinLsCtas) k_win_linearize_schur
     const int tid = threadIdx.x;
     const int tile = tile_index(P);
     const WinTile t = load_tile(P, tile);
+    void* const bar = sm + kLsBar;
+    if (tid == 0) mbar_init(bar, 1);
+    // the tile's points start 8 bytes off a 16-byte boundary when its first point is odd: the bulk copy starts one double early
+    const int lead_pt = t.p0 & 1;
+    const double* const pt_s = s_pt + lead_pt; // point p, coordinate k: pt_s[3 p + k]
 
     // ---- A0: everything the tile needs from HBM, issued at once, and what does not depend on the LM state
     // before the state is read.  Thread <-> slot: the observations of the tile in keyframe-major order, so that
@@ -164,13 +208,14 @@ __global__ void __launch_bounds__(kWinThreads, kWinLsCtas) k_win_linearize_schur
     const int cur = st.cur;
     const double lambda = init_pass ? 0.0 : (lambda_override >= 0.0 ? lambda_override : st.lambda);
     {
-        const double* __restrict__ gp = P.pts[cur] + 3 * (size_t)t.p0;
-        for (int i = tid; i < 3 * t.np; i += kWinThreads) {
-            const int p = i / 3, k = i - 3 * p;
-            cp_async8(s_pt + k * kPtStride + p, gp + i);
+        if (tid == 0) { // TMA: the tile's points and its problem's R|t, two bulk copies, one mbarrier
+            const double* gp = P.pts[cur] + 3 * (size_t)t.p0 - lead_pt;
+            const double* grt = P.cam_rt[cur] + 12 * (size_t)t.cam0; // 96 bytes per pose: always aligned
+            const unsigned b_pt = round16(8u * (unsigned)(3 * t.np + lead_pt)), b_rt = 96u * (unsigned)t.ncam;
+            mbar_expect_tx(bar, b_pt + b_rt);
+            bulk_g2s(s_pt, gp, b_pt, bar);
+            bulk_g2s(s_rt, grt, b_rt, bar);
         }
-        const double* __restrict__ grt = P.cam_rt[cur] + 12 * (size_t)t.cam0;
-        for (int i = tid; i < 12 * t.ncam; i += kWinThreads) cp_async8(s_rt + i, grt + i);
 #pragma unroll
         for (int i = 0; i < kObsPerThread; ++i) {
             const int o = tid + i * kWinThreads;
@@ -180,6 +225,7 @@ __global__ void __launch_bounds__(kWinThreads, kWinLsCtas) k_win_linearize_schur
     }
     cp_async_wait_all();
     __syncthreads();
+    mbar_wait(bar, 0);
 
     // ---- A1 ----
     double cost = 0.0;
@@ -189,7 +235,7 @@ __global__ void __launch_bounds__(kWinThreads, kWinLsCtas) k_win_linearize_schur
         if (o < t.no) {
             const int c = meta[i] & 0xff, p = (meta[i] >> 8) & 0xff, sl = o;
             ObsGeom g;
-            obs_geometry(P, s_rt + 12 * c, s_pt[p], s_pt[kPtStride + p], s_pt[2 * kPtStride + p], uv[i], g);
+            obs_geometry(P, s_rt + 12 * c, pt_s[3 * p], pt_s[3 * p + 1], pt_s[3 * p + 2], uv[i], g);
             cost += g.rho;
             REC(0, sl) = make_double2(g.xn, g.yn);
             REC(1, sl) = make_double2(g.iz, g.w);
@@ -251,7 +297,7 @@ __global__ void __launch_bounds__(kWinThreads, kWinLsCtas) k_win_linearize_schur
         double* gi = P.ptinfo + kPtInfoDoubles * (size_t)(t.p0 + p);
 #pragma unroll
         for (int k = 0; k < 9; ++k) {
-            s_info[k * kPtStride + p] = v[k];
+            s_info[9 * p + k] = v[k];
             gi[k] = v[k];
         }
     }
@@ -268,9 +314,9 @@ __global__ void __launch_bounds__(kWinThreads, kWinLsCtas) k_win_linearize_schur
         const int o = tid + i * kWinThreads;
         if (o < t.no) {
             const int p = (meta[i] >> 8) & 0xff, sl = o;
-            const double i00 = s_info[p], i10 = s_info[kPtStride + p], i11 = s_info[2 * kPtStride + p];
-            const double i20 = s_info[3 * kPtStride + p], i21 = s_info[4 * kPtStride + p], i22 = s_info[5 * kPtStride + p];
-            const double z0 = s_info[6 * kPtStride + p], z1 = s_info[7 * kPtStride + p], z2 = s_info[8 * kPtStride + p];
+            const double* in = s_info + 9 * p;
+            const double i00 = in[0], i10 = in[1], i11 = in[2], i20 = in[3], i21 = in[4], i22 = in[5];
+            const double z0 = in[6], z1 = in[7], z2 = in[8];
             const double w = REC(1, sl).y;
             const double2 j01 = REC(2, sl), j2a = REC(3, sl), jb = REC(4, sl), r = REC(5, sl);
             const double g00 = w * (j01.x * i00);
@@ -472,32 +518,44 @@ __global__ void __launch_bounds__(kWinThreads, 5) k_win_update(DevProblem P)
             slot_r[i] = __ldg(P.win_slot + t.o0 + o);
         }
     }
-    {
-        const double* __restrict__ gi = P.ptinfo + kPtInfoDoubles * (size_t)t.p0;
-        for (int i = tid; i < 9 * t.np; i += kWinThreads) {
-            const int p = i / 9, k = i - 9 * p;
-            cp_async8(s_info + k * kPtStride + p, gi + i);
-        }
-        const double* __restrict__ gd = P.dp + 6 * (size_t)t.cam0;
-        for (int i = tid; i < 6 * t.ncam; i += kWinThreads) cp_async8(s_dp + i, gd + i);
+    // TMA staging (cp.async.bulk + mbarrier).  Barrier 0: what does not depend on the LM state (per-point records, pose
+    // steps), issued before the state is read; barrier 1: points and both R|t tables of the problem's current / candidate
+    // buffers.  A tile that starts at an odd point starts its copies one point-record early (16-byte alignment).
+    void* const bar0 = sm + kUsBar;
+    void* const bar1 = sm + kUsBar + 8;
+    const int lead = t.p0 & 1; // in points: 72 and 24 bytes per point are 8 bytes off the alignment for an odd point
+    double* const pt_s = s_pt + lead;           // point p, coordinate k: pt_s[3 p + k]   (lead: one double)
+    const double* const info_s = s_info + lead; // point p, entry k:      info_s[9 p + k]
+    if (tid == 0) {
+        mbar_init(bar0, 1);
+        mbar_init(bar1, 1);
+        const double* gi = P.ptinfo + kPtInfoDoubles * (size_t)t.p0 - lead;
+        const double* gd = P.dp + 6 * (size_t)t.cam0; // 48 bytes per pose: always aligned
+        const unsigned b_i = round16(8u * (unsigned)(9 * t.np + lead)), b_d = 48u * (unsigned)t.ncam;
+        mbar_expect_tx(bar0, b_i + b_d);
+        bulk_g2s(s_info, gi, b_i, bar0);
+        bulk_g2s(s_dp, gd, b_d, bar0);
     }
     const int obs0_r = tid <= t.np ? __ldg(P.pt_ptr + t.p0 + tid) - t.o0 : 0; // kWinPtCap < kWinThreads
     const LmState& st = P.lm[t.prob];
-    if (!st.active) {
-        cp_async_wait_all();
+    if (!st.active) { // no CTA may exit with a copy into its shared memory in flight
+        __syncthreads();
+        mbar_wait(bar0, 0);
         return;
     }
     const int cur = st.cur, cand = cur ^ 1;
     const double lambda = st.lambda;
     {
-        const double* __restrict__ gp = P.pts[cur] + 3 * (size_t)t.p0;
-        for (int i = tid; i < 3 * t.np; i += kWinThreads) {
-            const int p = i / 3, k = i - 3 * p;
-            cp_async8(s_pt + k * kPtStride + p, gp + i);
+        if (tid == 0) {
+            const double* gp = P.pts[cur] + 3 * (size_t)t.p0 - lead;
+            const double* g1 = P.cam_rt[cur] + 12 * (size_t)t.cam0;
+            const double* g2 = P.cam_rt[cand] + 12 * (size_t)t.cam0;
+            const unsigned b_p = round16(8u * (unsigned)(3 * t.np + lead)), b_r = 96u * (unsigned)t.ncam;
+            mbar_expect_tx(bar1, b_p + 2 * b_r);
+            bulk_g2s(s_pt, gp, b_p, bar1);
+            bulk_g2s(s_rt, g1, b_r, bar1);
+            bulk_g2s(s_rt2, g2, b_r, bar1);
         }
-        const double* __restrict__ g1 = P.cam_rt[cur] + 12 * (size_t)t.cam0;
-        const double* __restrict__ g2 = P.cam_rt[cand] + 12 * (size_t)t.cam0;
-        for (int i = tid; i < 12 * t.ncam; i += kWinThreads) cp_async8(s_rt + i, g1 + i), cp_async8(s_rt2 + i, g2 + i);
 #pragma unroll
         for (int i = 0; i < kObsPerThread; ++i) {
             const int o = tid + i * kWinThreads;
@@ -505,8 +563,9 @@ __global__ void __launch_bounds__(kWinThreads, 5) k_win_update(DevProblem P)
         }
         if (tid <= t.np) s_obs0[tid] = (unsigned short)obs0_r;
     }
-    cp_async_wait_all();
     __syncthreads();
+    mbar_wait(bar0, 0);
+    mbar_wait(bar1, 0);
 
     // ---- U1 ----
 #pragma unroll
@@ -515,9 +574,9 @@ __global__ void __launch_bounds__(kWinThreads, 5) k_win_update(DevProblem P)
         if (o < t.no) {
             const int c = meta[i] & 0xff, p = (meta[i] >> 8) & 0xff;
             ObsGeom g;
-            obs_geometry(P, s_rt + 12 * c, s_pt[p], s_pt[kPtStride + p], s_pt[2 * kPtStride + p], uv[i], g);
-            const double i00 = s_info[p], i10 = s_info[kPtStride + p], i11 = s_info[2 * kPtStride + p];
-            const double i20 = s_info[3 * kPtStride + p], i21 = s_info[4 * kPtStride + p], i22 = s_info[5 * kPtStride + p];
+            obs_geometry(P, s_rt + 12 * c, pt_s[3 * p], pt_s[3 * p + 1], pt_s[3 * p + 2], uv[i], g);
+            const double* in = info_s + 9 * p;
+            const double i00 = in[0], i10 = in[1], i11 = in[2], i20 = in[3], i21 = in[4], i22 = in[5];
             const double g00 = P.fx * (g.w * (g.jl0[0] * i00));
             const double g01 = P.fx * (g.w * (g.jl0[0] * i10 + g.jl0[1] * i11));
             const double g02 = P.fx * (g.w * (g.jl0[0] * i20 + g.jl0[1] * i21 + g.jl0[2] * i22));
@@ -544,9 +603,9 @@ __global__ void __launch_bounds__(kWinThreads, 5) k_win_update(DevProblem P)
     // ---- U2 ----
     double scale = 0.0;
     for (int p = tid; p < t.np; p += kWinThreads) {
-        const double i00 = s_info[p], i10 = s_info[kPtStride + p], i11 = s_info[2 * kPtStride + p];
-        const double i20 = s_info[3 * kPtStride + p], i21 = s_info[4 * kPtStride + p], i22 = s_info[5 * kPtStride + p];
-        const double z0 = s_info[6 * kPtStride + p], z1 = s_info[7 * kPtStride + p], z2 = s_info[8 * kPtStride + p];
+        const double* in = info_s + 9 * p;
+        const double i00 = in[0], i10 = in[1], i11 = in[2], i20 = in[3], i21 = in[4], i22 = in[5];
+        const double z0 = in[6], z1 = in[7], z2 = in[8];
         double y0 = z0, y1 = z1, y2 = z2, sc = 0.0;
         for (int o = s_obs0[p]; o < s_obs0[p + 1]; ++o) {
             const int sl = s_slot[o];
@@ -561,15 +620,12 @@ __global__ void __launch_bounds__(kWinThreads, 5) k_win_update(DevProblem P)
         const double d2 = i22 * y2;
         sc += y0 * z0 + y1 * z1 + y2 * z2 + lambda * (d0 * d0 + d1 * d1 + d2 * d2);
         scale += sc;
-        s_pt[p] += d0, s_pt[kPtStride + p] += d1, s_pt[2 * kPtStride + p] += d2;
+        pt_s[3 * p] += d0, pt_s[3 * p + 1] += d1, pt_s[3 * p + 2] += d2;
     }
     __syncthreads();
     { // candidate points out, coalesced
         double* __restrict__ gp = P.pts[cand] + 3 * (size_t)t.p0;
-        for (int i = tid; i < 3 * t.np; i += kWinThreads) {
-            const int p = i / 3, k = i - 3 * p;
-            gp[i] = s_pt[k * kPtStride + p];
-        }
+        for (int i = tid; i < 3 * t.np; i += kWinThreads) gp[i] = pt_s[i];
     }
 
     // ---- U3 ----
@@ -580,7 +636,7 @@ __global__ void __launch_bounds__(kWinThreads, 5) k_win_update(DevProblem P)
         if (o < t.no) {
             const int c = meta[i] & 0xff, p = (meta[i] >> 8) & 0xff;
             const double* rt = s_rt2 + 12 * c;
-            const double X = s_pt[p], Y = s_pt[kPtStride + p], Z = s_pt[2 * kPtStride + p];
+            const double X = pt_s[3 * p], Y = pt_s[3 * p + 1], Z = pt_s[3 * p + 2];
             const double x = rt[0] * X + rt[1] * Y + rt[2] * Z + rt[9];
             const double y = rt[3] * X + rt[4] * Y + rt[5] * Z + rt[10];
             const double z = rt[6] * X + rt[7] * Y + rt[8] * Z + rt[11];
