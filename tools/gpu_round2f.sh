@@ -1,4 +1,4 @@
-# GPU box, round 2f (state after the solver / photometric-edge / lone-window work): all GPU tests, smoke, reference arm,
+# GPU box, final state of round 2: all GPU tests, smoke, reference arm,
 # default bench, launch list of the bench command, full ncu capture of the window kernels at the benched size
 set -x
 mkdir -p gpurun_out
@@ -11,5 +11,5 @@ timeout 900 python bench.py > gpurun_out/bench.json 2> gpurun_out/bench.err; ech
 tail -3 gpurun_out/bench.err
 B="python bench.py --steps 2 --warmup 1 --no-others --no-e2e --no-cpu"
 $B > gpurun_out/plain.log 2>&1 && timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/launches_c5.csv $B > gpurun_out/ncu1.log 2>&1
-$B > gpurun_out/plain2.log 2>&1 && timeout 900 ncu --set full --metrics sm__inst_executed_pipe_fp64.sum,sm__sass_thread_inst_executed_op_dfma_pred_on.sum,sm__sass_thread_inst_executed_op_dmul_pred_on.sum,sm__sass_thread_inst_executed_op_dadd_pred_on.sum --clock-control none --import-source on -k regex:"k_win_|k_solve_small" -s 4 -c 4 -o gpurun_out/prof_win_c5 $B > gpurun_out/ncu2.log 2>&1
+$B > gpurun_out/plain2.log 2>&1 && timeout 900 ncu --set full --metrics sm__inst_executed_pipe_fp64.sum,sm__sass_thread_inst_executed_op_dfma_pred_on.sum,sm__sass_thread_inst_executed_op_dmul_pred_on.sum,sm__sass_thread_inst_executed_op_dadd_pred_on.sum --clock-control none --import-source on -k regex:"k_win_linearize_schur|k_win_finalize|k_win_update|k_solve_small" -s 4 -c 4 -f -o gpurun_out/prof_win_c5 $B > gpurun_out/ncu2.log 2>&1
 ls -la gpurun_out | head -40
