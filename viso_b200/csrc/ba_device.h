@@ -71,6 +71,9 @@ constexpr int kWinObsCap = VISO_WIN_OBS_CAP; // observations per tile (their rec
 constexpr int kWinPtCap = VISO_WIN_PT_CAP;   // points per tile
 constexpr int kWinLsCtas = VISO_WIN_LS_CTAS; // CTAs of k_win_linearize_schur resident per SM (registers and shared memory)
 constexpr int kWinMaxCams = 32; // keyframes per problem (visibility mask is 32 bits)
+// per tile in win_blkptr: nblk + 1 offsets of the S blocks' pair lists, then nblk block indices in the ORDER the tile kernel
+// takes them (longest list first: the four sub-warps of a warp then work on lists of similar length)
+__host__ __device__ constexpr long long win_blkptr_entries(long long nblk) { return 2 * nblk + 1; }
 
 struct WinTile { // one CTA's share of a problem: consecutive points and all their observations
     int32_t prob, p0, np, o0, no, cam0, ncam, nf;

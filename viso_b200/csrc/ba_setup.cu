@@ -165,7 +165,7 @@ __global__ void k_setup_prob_offsets(SetupIn in, const int32_t* __restrict__ pro
         const int64_t nblk = (int64_t)prob_nfree[b] * (prob_nfree[b] + 1) / 2;
         t += prob_ntiles[b];
         part += prob_ntiles[b] * nblk * kItemPart;
-        bp += prob_ntiles[b] * (nblk + 1);
+        bp += prob_ntiles[b] * win_blkptr_entries(nblk);
     }
     prob_tile_ptr[in.n_problems] = t, prob_part_off[in.n_problems] = part, prob_blkptr_off[in.n_problems] = bp;
     totals[0] = t, totals[1] = part, totals[2] = bp;
@@ -184,7 +184,7 @@ __global__ void __launch_bounds__(kCutThreads) k_setup_tiles_fill(SetupIn in, co
     WinTile proto = {};
     proto.prob = b, proto.cam0 = in.prob_cam0[b], proto.ncam = in.prob_cam0[b + 1] - in.prob_cam0[b], proto.nf = prob_nfree[b];
     proto.part_off = prob_part_off[b], proto.blkptr_off = prob_blkptr_off[b];
-    cut_tiles<true>(src, q0, hi, proto, tiles + prob_tile_ptr[b], nblk * kItemPart, nblk + 1);
+    cut_tiles<true>(src, q0, hi, proto, tiles + prob_tile_ptr[b], nblk * kItemPart, win_blkptr_entries(nblk));
 }
 
 // ---- 5a. per tile: keyframe-major slots and pair counts ----
@@ -282,6 +282,19 @@ __global__ void __launch_bounds__(kSetupThreads) k_setup_tile_pairs(WinTile* __r
         if (f >= 0) s_fcam[f] = (unsigned char)c;
     }
     for (int k = tid; k <= nblk; k += kSetupThreads) s_bp[k] = win_blkptr[t.blkptr_off + k];
+    __syncthreads();
+    // the order the tile kernel takes the blocks in: by pair count, longest first (ties: lower index first).  Rank sort: the
+    // rank of block k is the number of blocks that come before it.  Sixteen sub-warps take sixteen consecutive entries per pass
+    // and the four of one warp wait for their longest list, so neighbours in this order should be of similar length.
+    for (int k = tid; k < nblk; k += kSetupThreads) {
+        const unsigned int ck = s_bp[k + 1];
+        int rank = 0;
+        for (int j = 0; j < nblk; ++j) {
+            const unsigned int cj = s_bp[j + 1];
+            rank += (cj > ck || (cj == ck && j < k)) ? 1 : 0;
+        }
+        win_blkptr[t.blkptr_off + nblk + 1 + rank] = (unsigned int)k;
+    }
     __syncthreads();
     if (tid == 0) { // exclusive scan of the counts (nblk <= 378)
         unsigned int run = 0;

@@ -344,20 +344,22 @@ __global__ void __launch_bounds__(kWinThreads, kWinLsCtas) k_win_linearize_schur
     double* part = P.tile_part + t.part_off;
     const unsigned int* __restrict__ pairs = P.win_pairs + t.list_off;
     const int npass = (nblk + kSubsPerCta - 1) / kSubsPerCta;
+    // slot -> block.  Init pass: the nf diagonal blocks.  Otherwise the order ba_setup.cu left behind the tile's offsets
+    // (longest pair list first), fetched one pass ahead of its use.
+    const unsigned int* __restrict__ order = P.win_blkptr + t.blkptr_off + nblk_all + 1;
+    int blk_next = (!init_pass && g < nblk) ? (int)__ldg(order + g) : 0;
     for (int pass = 0; pass < npass; ++pass) {
-        // slot -> block: the nf diagonal blocks first, then the strictly lower ones row by row
         const int slot = pass * kSubsPerCta + g;
         const bool have = slot < nblk;
         int I = 0, J = 0;
-        if (have) {
-            if (slot < nf) I = J = slot;
-            else {
-                const int q = slot - nf;
-                I = (int)((sqrtf(8.0f * (float)q + 1.0f) + 1.0f) * 0.5f);
-                while (I * (I - 1) / 2 > q) --I;
-                while ((I + 1) * I / 2 <= q) ++I;
-                J = q - I * (I - 1) / 2;
-            }
+        if (init_pass) I = J = have ? slot : 0;
+        else {
+            const int b = have ? blk_next : 0; // triangular index I (I + 1) / 2 + J
+            I = (int)((sqrtf(8.0f * (float)b + 1.0f) - 1.0f) * 0.5f);
+            while ((I + 1) * (I + 2) / 2 <= b) ++I;
+            while (I * (I + 1) / 2 > b) --I;
+            J = b - I * (I + 1) / 2;
+            blk_next = slot + kSubsPerCta < nblk ? (int)__ldg(order + slot + kSubsPerCta) : 0;
         }
         const bool diag = I == J;
         const int blk = I * (I + 1) / 2 + J;

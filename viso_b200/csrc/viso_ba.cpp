@@ -1032,7 +1032,7 @@ int32_t build_tables(viso_ba* h, Built& b)
             const int64_t tp = (pt0[(size_t)p + 1] - pt0[(size_t)p]) / kWinPtCap +
                 (h->edge_off_all[(size_t)p + 1] - h->edge_off_all[(size_t)p]) / (kWinObsCap - kWinMaxCams + 1) + 2;
             b.part_max += tp * nblk * kItemPart;
-            b.blkptr_max += tp * (nblk + 1);
+            b.blkptr_max += tp * win_blkptr_entries(nblk);
         }
     }
     return VISO_BA_OK;
