@@ -413,4 +413,139 @@ int setup_stage3(const SetupIn& in, const SetupWork& w, const SetupOut& o, int32
     return 1;
 }
 
+// ------------------------------------------------------------------------------------------
+// general path (one large problem, B == 1): structure build on the device.  Same tables as the host build in viso_ba.cpp
+// (build_general) leaves: observations in (point, pose) order, the pair list sorted by S block with the pairs of a block
+// in point order (the radix sort is stable and the pairs are generated point by point), blk_ptr.
+// ------------------------------------------------------------------------------------------
+namespace {
+
+__global__ void k_gen_present(int32_t n_points, const int32_t* __restrict__ pt_ptr, const int32_t* __restrict__ obs_cam,
+    const int32_t* __restrict__ cam_free, uint8_t* __restrict__ present)
+{
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n_points) return;
+    const int s0 = pt_ptr[p], s1 = pt_ptr[p + 1];
+    for (int a = s0; a < s1; ++a) {
+        const int fa = cam_free[obs_cam[a]];
+        if (fa < 0) continue;
+        const size_t row = (size_t)fa * (fa + 1) / 2;
+        for (int c = s0; c < a; ++c) {
+            const int fc = cam_free[obs_cam[c]];
+            if (fc >= 0 && !present[row + (size_t)fc]) present[row + (size_t)fc] = 1; // every writer writes 1
+        }
+    }
+}
+
+__global__ void k_gen_pair_counts(int32_t pt_begin, int32_t pt_end, const int32_t* __restrict__ pt_ptr, const int32_t* __restrict__ obs_cam,
+    const int32_t* __restrict__ cam_free, int64_t* __restrict__ counts)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int n = pt_end - pt_begin;
+    if (i > n) return;
+    int64_t f = 0;
+    if (i < n)
+        for (int s = pt_ptr[pt_begin + i]; s < pt_ptr[pt_begin + i + 1]; ++s) f += cam_free[obs_cam[s]] >= 0 ? 1 : 0;
+    counts[i] = f * (f + 1) / 2; // entry n: 0, becomes the total after the scan
+}
+
+__global__ void k_gen_pairs(int32_t pt_begin, int32_t pt_end, const int32_t* __restrict__ pt_ptr, const int32_t* __restrict__ obs_cam,
+    const int32_t* __restrict__ cam_free, const int32_t* __restrict__ remap, const int64_t* __restrict__ offsets,
+    unsigned int* __restrict__ keys, unsigned long long* __restrict__ vals)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= pt_end - pt_begin) return;
+    const int p = pt_begin + i;
+    const int s0 = pt_ptr[p], s1 = pt_ptr[p + 1];
+    int64_t q = offsets[i];
+    for (int a = s0; a < s1; ++a) { // the order of build_general: a ascending, c ascending up to a
+        const int fa = cam_free[obs_cam[a]];
+        if (fa < 0) continue;
+        for (int c = s0; c <= a; ++c) { // sorted by pose: fc <= fa
+            const int fc = cam_free[obs_cam[c]];
+            if (fc < 0) continue;
+            const int tri = fa * (fa + 1) / 2 + fc;
+            keys[q] = (unsigned int)(remap ? remap[tri] : tri);
+            vals[q] = (unsigned long long)(unsigned int)a | ((unsigned long long)(unsigned int)c << 32);
+            ++q;
+        }
+    }
+}
+
+__global__ void k_gen_blkptr(const unsigned int* __restrict__ keys, int64_t n_pairs, int32_t n_blocks, int64_t* __restrict__ blk_ptr)
+{
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k > n_blocks) return;
+    int64_t lo = 0, hi = n_pairs; // first pair with key >= k
+    while (lo < hi) {
+        const int64_t mid = (lo + hi) >> 1;
+        if (keys[mid] < (unsigned int)k) lo = mid + 1;
+        else hi = mid;
+    }
+    blk_ptr[k] = lo;
+}
+
+} // namespace
+
+int setup_sort_only(const SetupIn& in, const SetupWork& w, const SetupOut& o, cudaStream_t st)
+{
+    int launches = 0;
+    const int cam_bits = key_cam_bits(in);
+    if (in.n_edges > 0) {
+        int end_bit = cam_bits + 1;
+        while (end_bit < 64 && ((int64_t)1 << (end_bit - cam_bits)) < (int64_t)in.n_points) ++end_bit;
+        size_t bytes = w.temp_bytes;
+        cub::DeviceRadixSort::SortPairs(w.temp, bytes, w.keys, w.keys_sorted, w.vals, w.vals_sorted, in.n_edges, 0, end_bit, st);
+        k_setup_gather<<<cdiv(in.n_edges, 256), 256, 0, st>>>(in, cam_bits, w.keys_sorted, w.vals_sorted, o.obs_cam, o.obs_uv, w.err);
+        launches += 2;
+    }
+    k_setup_ptptr<<<cdiv((int64_t)in.n_points + 1, 256), 256, 0, st>>>(in.n_edges, in.n_points, cam_bits, w.keys_sorted, o.pt_ptr);
+    k_setup_fill_pt_prob<<<cdiv(in.n_points, 256), 256, 0, st>>>(in.n_points, in.n_problems, in.prob_pt0, o.pt_prob);
+    return launches + 2;
+}
+
+int gen_present(int32_t n_points, const int32_t* pt_ptr, const int32_t* obs_cam, const int32_t* cam_free, uint8_t* present, cudaStream_t st)
+{
+    if (n_points <= 0) return 0;
+    k_gen_present<<<cdiv(n_points, 128), 128, 0, st>>>(n_points, pt_ptr, obs_cam, cam_free, present);
+    return 1;
+}
+
+size_t gen_temp_bytes(int64_t n_points, int64_t n_pairs)
+{
+    size_t scan = 0, sort = 0;
+    cub::DeviceScan::ExclusiveSum(nullptr, scan, (const int64_t*)nullptr, (int64_t*)nullptr, (int)std::min<int64_t>(n_points + 1, 0x7fffffff));
+    cub::DeviceRadixSort::SortPairs(nullptr, sort, (const unsigned int*)nullptr, (unsigned int*)nullptr, (const unsigned long long*)nullptr,
+        (unsigned long long*)nullptr, std::max<int64_t>(n_pairs, 1));
+    return std::max(scan, sort) + 256;
+}
+
+int gen_pair_offsets(int32_t pt_begin, int32_t pt_end, const int32_t* pt_ptr, const int32_t* obs_cam, const int32_t* cam_free,
+                     int64_t* counts, void* temp, size_t temp_bytes, cudaStream_t st)
+{
+    const int n = pt_end - pt_begin;
+    k_gen_pair_counts<<<cdiv((int64_t)n + 1, 256), 256, 0, st>>>(pt_begin, pt_end, pt_ptr, obs_cam, cam_free, counts);
+    size_t bytes = temp_bytes;
+    cub::DeviceScan::ExclusiveSum(temp, bytes, counts, counts, n + 1, st);
+    return 2;
+}
+
+int gen_pairs(int32_t pt_begin, int32_t pt_end, const int32_t* pt_ptr, const int32_t* obs_cam, const int32_t* cam_free,
+              const int32_t* remap, const int64_t* offsets, int64_t n_pairs, int32_t n_blocks, unsigned int* keys, unsigned int* keys_sorted,
+              unsigned long long* vals, unsigned long long* vals_sorted, int64_t* blk_ptr, void* temp, size_t temp_bytes, cudaStream_t st)
+{
+    int launches = 0;
+    const int n = pt_end - pt_begin;
+    if (n > 0 && n_pairs > 0) {
+        k_gen_pairs<<<cdiv(n, 128), 128, 0, st>>>(pt_begin, pt_end, pt_ptr, obs_cam, cam_free, remap, offsets, keys, vals);
+        int end_bit = 1;
+        while (end_bit < 32 && ((int64_t)1 << end_bit) < (int64_t)n_blocks) ++end_bit;
+        size_t bytes = temp_bytes;
+        cub::DeviceRadixSort::SortPairs(temp, bytes, keys, keys_sorted, vals, vals_sorted, n_pairs, 0, end_bit, st);
+        launches += 2;
+    }
+    k_gen_blkptr<<<cdiv((int64_t)n_blocks + 1, 256), 256, 0, st>>>(keys_sorted, n_pairs, n_blocks, blk_ptr);
+    return launches + 1;
+}
+
 } // namespace visoba

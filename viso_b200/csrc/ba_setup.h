@@ -61,5 +61,20 @@ int setup_stage2(const SetupIn& in, const SetupWork& w, const SetupOut& o, int32
 // stage 3: pair lists
 int setup_stage3(const SetupIn& in, const SetupWork& w, const SetupOut& o, int32_t n_tiles, cudaStream_t st);
 
+// ---- general path (one large problem): the same sort, then the pair lists by S block, on the device ----
+// sort + CSR only (stage 1 without the tiles): obs_cam / obs_uv in (point, pose) order, pt_ptr, pt_prob
+int setup_sort_only(const SetupIn& in, const SetupWork& w, const SetupOut& o, cudaStream_t st);
+// present[I (I + 1) / 2 + J] = 1 for every pair of FREE poses I >= J some point sees (the structure of S; all points)
+int gen_present(int32_t n_points, const int32_t* pt_ptr, const int32_t* obs_cam, const int32_t* cam_free, uint8_t* present, cudaStream_t st);
+size_t gen_temp_bytes(int64_t n_points, int64_t n_pairs);
+// counts[i] = pairs of point pt_begin + i (free observations f: f (f + 1) / 2), then the exclusive scan in place: counts[n] = total
+int gen_pair_offsets(int32_t pt_begin, int32_t pt_end, const int32_t* pt_ptr, const int32_t* obs_cam, const int32_t* cam_free,
+                     int64_t* counts, void* temp, size_t temp_bytes, cudaStream_t st);
+// the pairs of the points [pt_begin, pt_end) in point order: key = S block (through remap when the storage is compact), value =
+// observation a | observation c << 32; stable radix sort by block; blk_ptr[k] = first pair of block k
+int gen_pairs(int32_t pt_begin, int32_t pt_end, const int32_t* pt_ptr, const int32_t* obs_cam, const int32_t* cam_free,
+              const int32_t* remap, const int64_t* offsets, int64_t n_pairs, int32_t n_blocks, unsigned int* keys, unsigned int* keys_sorted,
+              unsigned long long* vals, unsigned long long* vals_sorted, int64_t* blk_ptr, void* temp, size_t temp_bytes, cudaStream_t st);
+
 } // namespace visoba
 #endif

@@ -234,6 +234,7 @@ struct viso_ba {
     int64_t n_edges_dev = 0;
     std::vector<int64_t> edge_off_all; // B+1 (also for B == 1)
     DevBuf raw, scratch, pairbuf, pts_stage;
+    DevBuf gen_obs, gen_tabs, gen_work; // device-side build of the general path (one large problem)
     bool pts_staged = false;            // pts_stage holds the points exactly as `points` does (bulk set_problem)
     std::vector<int32_t> stage_c0, stage_p0; // source of an H2D copy that may still be in flight
     // ---- photometric edges (ba_photo.cu): the handle holds either reprojection or photometric edges ----
@@ -470,7 +471,7 @@ extern "C" void viso_ba_destroy(viso_ba* h)
         resolve_timing(h);
         if (h->comm && nccl_api()) nccl_api()->CommDestroy(h->comm);
         if (h->arena.base) cudaFree(h->arena.base);
-        for (DevBuf* b : { &h->raw, &h->scratch, &h->pairbuf, &h->pts_stage, &h->ph_img_dev, &h->ph_frames_dev, &h->ph_srcrt_dev, &h->ph_sum_dev, &h->ph_mid_dev })
+        for (DevBuf* b : { &h->raw, &h->scratch, &h->pairbuf, &h->pts_stage, &h->gen_obs, &h->gen_tabs, &h->gen_work, &h->ph_img_dev, &h->ph_frames_dev, &h->ph_srcrt_dev, &h->ph_sum_dev, &h->ph_mid_dev })
             if (b->p) cudaFree(b->p);
         if (h->pin) cudaFreeHost(h->pin);
         if (h->ev0) cudaEventDestroy(h->ev0);
@@ -946,6 +947,7 @@ struct Built {
     std::vector<int32_t> blk_ij;     // 2 per S block: (I, J) free indices (compact storage, large solver only)
     SolvePlan plan;                  // segments / separators / elimination steps of the large solver (large solver only)
     bool compact = false;            // S blocks stored for co-visible pose pairs only
+    bool dev_general = false;        // general path built on the device: obs arrays and pairs live in the handle's DevBufs
     std::vector<int32_t> chunks;     // 4 per chunk
     std::vector<int32_t> prob_chunk_ptr;
     // window fast path: the structure is built on the device; the host only bounds its size
@@ -1039,6 +1041,78 @@ int32_t build_tables(viso_ba* h, Built& b)
 }
 
 // general path: sort the edges, shard the points, list the observation pairs of every S block (host)
+// compact storage of S (one large problem): blocks of co-visible pose pairs only.  `present` is indexed by the dense
+// triangular index I (I + 1) / 2 + J of FREE poses (the diagonal is added here); fills remap (dense -> stored block or -1),
+// blk_ij, the solve plan, block_cam and diag_blk, and shrinks n_blocks.
+void compact_structure(viso_ba* h, Built& b, int32_t nf, std::vector<uint8_t>& present, std::vector<int32_t>& remap)
+{
+    const int64_t Nc = (int64_t)h->poses.size() / 7;
+    for (int32_t f = 0; f < nf; ++f) present[(size_t)f * (f + 1) / 2 + f] = 1;
+    remap.assign((size_t)b.n_blocks, -1);
+    int32_t k = 0;
+    for (int32_t I = 0; I < nf; ++I)
+        for (int32_t J = 0; J <= I; ++J)
+            if (present[(size_t)I * (I + 1) / 2 + J]) {
+                remap[(size_t)I * (I + 1) / 2 + J] = k++;
+                b.blk_ij.push_back(I);
+                b.blk_ij.push_back(J);
+            }
+    // how the solver cuts the pose chain (ba_solve_plan.h): config.solver_segments 0 = auto (up to 8 interior segments
+    // when the co-visibility span is small against the chain), 1 = never, k >= 2 = up to k whenever the structure allows
+    {
+        const int seg = h->cfg.solver_segments;
+        b.plan = make_solve_plan(nf, b.blk_ij, large_solve_cta_count(), seg == 0 ? 8 : seg, seg >= 2);
+    }
+    b.n_blocks = k;
+    b.prob_tri0[1] = k;
+    b.block_cam.assign((size_t)k, -1);
+    for (int64_t c = 0; c < Nc; ++c) {
+        const int32_t f = b.cam_free[(size_t)c];
+        if (f >= 0) {
+            b.diag_blk[(size_t)c] = remap[(size_t)f * (f + 1) / 2 + f];
+            b.block_cam[(size_t)b.diag_blk[(size_t)c]] = (int32_t)c;
+        }
+    }
+}
+
+// work items (slices of one block's pairs, one warp each) from the block offsets of the pair list, and the chunks of points
+// of the deterministic per-problem sums
+void general_items_and_chunks(viso_ba* h, Built& b, const std::vector<int64_t>& blk_ptr, int32_t pt_begin, int32_t pt_end)
+{
+    const int64_t B = h->n_problems;
+    const std::vector<int64_t>& pt0 = b.pt0;
+    int64_t item_pairs = (b.n_pairs / 16384 + 31) / 32 * 32;
+    item_pairs = std::max<int64_t>(64, std::min<int64_t>(512, item_pairs));
+    b.block_item_ptr.assign((size_t)b.n_blocks + 1, 0);
+    {
+        int32_t prob = 0;
+        for (int32_t k = 0; k < b.n_blocks; ++k) {
+            while (k >= b.prob_tri0[(size_t)prob + 1]) ++prob;
+            const int32_t is_diag = b.block_cam[(size_t)k] >= 0 ? 1 : 0;
+            for (int64_t q = blk_ptr[(size_t)k]; q < blk_ptr[(size_t)k + 1]; q += item_pairs) {
+                const int64_t q1 = std::min(q + item_pairs, blk_ptr[(size_t)k + 1]);
+                if (is_diag) b.diag_items.push_back((int32_t)(b.items.size() / 4));
+                b.items.push_back((int32_t)q);
+                b.items.push_back((int32_t)q1);
+                b.items.push_back(k);
+                b.items.push_back((prob << 1) | is_diag);
+            }
+            b.block_item_ptr[(size_t)k + 1] = (int32_t)(b.items.size() / 4);
+        }
+    }
+    b.prob_chunk_ptr.assign((size_t)B + 1, 0);
+    for (int64_t p = 0; p < B; ++p) {
+        const int32_t lo = std::max<int64_t>(pt0[(size_t)p], pt_begin), hi = (int32_t)std::min<int64_t>(pt0[(size_t)p + 1], pt_end);
+        for (int32_t q = lo; q < hi; q += kChunkPoints) {
+            b.chunks.push_back((int32_t)p);
+            b.chunks.push_back(q);
+            b.chunks.push_back(std::min(q + kChunkPoints, hi));
+            b.chunks.push_back(0);
+        }
+        b.prob_chunk_ptr[(size_t)p + 1] = (int32_t)(b.chunks.size() / 4);
+    }
+}
+
 int32_t build_general(viso_ba* h, Built& b)
 {
     const int64_t Nc = (int64_t)h->poses.size() / 7, Np = (int64_t)h->points.size() / 3;
@@ -1111,7 +1185,6 @@ int32_t build_general(viso_ba* h, Built& b)
     if (b.compact) {
         const int32_t nf = b.prob_nfree[0];
         std::vector<uint8_t> present((size_t)b.n_blocks, 0);
-        for (int32_t f = 0; f < nf; ++f) present[(size_t)f * (f + 1) / 2 + f] = 1;
         // every thread writes the same value (1) and nothing reads until the threads have joined
         uint8_t* const pres = present.data();
         parallel_ranges(nt, 0, Np, [&](int, int64_t lo, int64_t hi) {
@@ -1128,31 +1201,7 @@ int32_t build_general(viso_ba* h, Built& b)
                 }
             }
         });
-        remap.assign((size_t)b.n_blocks, -1);
-        int32_t k = 0;
-        for (int32_t I = 0; I < nf; ++I)
-            for (int32_t J = 0; J <= I; ++J)
-                if (present[(size_t)I * (I + 1) / 2 + J]) {
-                    remap[(size_t)I * (I + 1) / 2 + J] = k++;
-                    b.blk_ij.push_back(I);
-                    b.blk_ij.push_back(J);
-                }
-        // how the solver cuts the pose chain (ba_solve_plan.h): config.solver_segments 0 = auto (up to 8 interior segments
-        // when the co-visibility span is small against the chain), 1 = never, k >= 2 = up to k whenever the structure allows
-        {
-            const int seg = h->cfg.solver_segments;
-            b.plan = make_solve_plan(nf, b.blk_ij, large_solve_cta_count(), seg == 0 ? 8 : seg, seg >= 2);
-        }
-        b.n_blocks = k;
-        b.prob_tri0[1] = k;
-        b.block_cam.assign((size_t)k, -1);
-        for (int64_t c = 0; c < Nc; ++c) {
-            const int32_t f = b.cam_free[(size_t)c];
-            if (f >= 0) {
-                b.diag_blk[(size_t)c] = remap[(size_t)f * (f + 1) / 2 + f];
-                b.block_cam[(size_t)b.diag_blk[(size_t)c]] = (int32_t)c;
-            }
-        }
+        compact_structure(h, b, nf, present, remap);
     }
 
     const double t_struct = now_ms();
@@ -1204,39 +1253,7 @@ int32_t build_general(viso_ba* h, Built& b)
     });
 
     const double t_pairs = now_ms();
-    // ---- work items: slices of one block's pairs, one warp each ----
-    int64_t item_pairs = (b.n_pairs / 16384 + 31) / 32 * 32;
-    item_pairs = std::max<int64_t>(64, std::min<int64_t>(512, item_pairs));
-    b.block_item_ptr.assign((size_t)b.n_blocks + 1, 0);
-    {
-        int32_t prob = 0;
-        for (int32_t k = 0; k < b.n_blocks; ++k) {
-            while (k >= b.prob_tri0[(size_t)prob + 1]) ++prob;
-            const int32_t is_diag = b.block_cam[(size_t)k] >= 0 ? 1 : 0;
-            for (int64_t q = blk_ptr[(size_t)k]; q < blk_ptr[(size_t)k + 1]; q += item_pairs) {
-                const int64_t q1 = std::min(q + item_pairs, blk_ptr[(size_t)k + 1]);
-                if (is_diag) b.diag_items.push_back((int32_t)(b.items.size() / 4));
-                b.items.push_back((int32_t)q);
-                b.items.push_back((int32_t)q1);
-                b.items.push_back(k);
-                b.items.push_back((prob << 1) | is_diag);
-            }
-            b.block_item_ptr[(size_t)k + 1] = (int32_t)(b.items.size() / 4);
-        }
-    }
-
-    // ---- chunks of points for the deterministic per-problem sums ----
-    b.prob_chunk_ptr.assign((size_t)B + 1, 0);
-    for (int64_t p = 0; p < B; ++p) {
-        const int32_t lo = std::max<int64_t>(pt0[(size_t)p], pt_begin), hi = (int32_t)std::min<int64_t>(pt0[(size_t)p + 1], pt_end);
-        for (int32_t q = lo; q < hi; q += kChunkPoints) {
-            b.chunks.push_back((int32_t)p);
-            b.chunks.push_back(q);
-            b.chunks.push_back(std::min(q + kChunkPoints, hi));
-            b.chunks.push_back(0);
-        }
-        b.prob_chunk_ptr[(size_t)p + 1] = (int32_t)(b.chunks.size() / 4);
-    }
+    general_items_and_chunks(h, b, blk_ptr, pt_begin, pt_end);
     if (h->cfg.verbose)
         fprintf(stderr, "[viso_ba] host structure build, %d threads: sort %.1f ms, block structure + solve plan %.1f ms, pair lists %.1f ms (%lld pairs), items %.1f ms\n",
             nt, t_sort - t_begin, t_struct - t_sort, t_pairs - t_struct, (long long)b.n_pairs, now_ms() - t_pairs);
