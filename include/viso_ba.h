@@ -72,6 +72,9 @@ typedef struct {
                               solve.  0 = auto (up to 8 interior segments when the co-visibility span is small against
                               the chain, as on a long trajectory), 1 = never (one envelope Cholesky), k >= 2 = up to k
                               segments whenever the structure allows it.  The result does not depend on the GPU count. */
+    int32_t host_structure_build; /* general path, one large problem: 0 (default) = the structure (sort by point and pose, pair
+                              lists by S block) is built on the device from 200 k edges on, 1 = always on the host threads.
+                              Both build the same tables. */
 } viso_ba_config;
 
 /* per outer LM iteration (single-problem handles) */

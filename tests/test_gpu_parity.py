@@ -506,3 +506,21 @@ def test_small_solver_sizes_and_padding(vb, oracle, n_poses):
         assert s.final_cost == pytest.approx(fc, rel=1e-10)
         _quat_close(ba.poses(), poses, 1e-9)
         assert np.abs(ba.points() - points).max() < 1e-8
+
+
+@pytest.mark.parametrize("kw", [dict(cid=3, n_poses=60, n_points=30000, target_edges=300000),
+                                dict(cid=4, n_poses=400, n_points=40000, target_edges=320000),
+                                dict(cid=2, n_poses=20, n_points=30000, target_edges=250000)], ids=["dense_S", "banded_S", "small_S"])
+def test_device_and_host_structure_builds_agree_bitwise(vb, kw):
+    """one large problem on the general path: the structure (sort by point and pose, pair lists by S block, work items) is
+    built on the device from 200 k edges on and on host threads otherwise; both give the same tables, hence the same bits"""
+    kw = dict(kw)
+    p = vb.synth_config(kw.pop("cid"), **kw)
+    out = []
+    for host in (1, 0):
+        ba = _adjuster(vb, p, path=2, host_structure_build=host)
+        s = ba.Optimize(3)
+        out.append((s.final_cost, s.trials, ba.poses().copy(), ba.points().copy()))
+        ba.close()
+    assert out[0][0] == out[1][0] and out[0][1] == out[1][1]
+    assert np.array_equal(out[0][2], out[1][2]) and np.array_equal(out[0][3], out[1][3])

@@ -38,7 +38,7 @@ class Config(C.Structure):
         ("huber_delta", C.c_double), ("lm_tau", C.c_double), ("lm_lambda_init", C.c_double),
         ("lm_max_trials", C.c_int32), ("verbose", C.c_int32),
         ("fix_first_pose", C.c_int32), ("use_cuda_graph", C.c_int32),
-        ("path", C.c_int32), ("solver_segments", C.c_int32),
+        ("path", C.c_int32), ("solver_segments", C.c_int32), ("host_structure_build", C.c_int32),
     ]
 
 

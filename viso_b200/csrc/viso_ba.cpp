@@ -195,6 +195,8 @@ double now_ms()
 
 } // namespace
 
+constexpr int64_t kDevGeneralMinEdges = 200000; // general path, one problem: from here on the structure is built on the device (below, the host build is cheaper than a dozen launches and four syncs)
+
 struct viso_ba {
     viso_ba_config cfg;
     std::string err;
@@ -436,6 +438,7 @@ extern "C" void viso_ba_default_config(viso_ba_config* c)
     c->use_cuda_graph = 1;
     c->path = 0;
     c->solver_segments = 0;
+    c->host_structure_build = 0;
 }
 
 extern "C" int32_t viso_ba_create(const viso_ba_config* cfg, viso_ba** out)
@@ -731,7 +734,9 @@ extern "C" int32_t viso_ba_set_problem_batched(viso_ba* h, int64_t B, const int6
     // window fast path for sure (<= 27 keyframes per problem: eligible whatever gets fixed later) and a
     // usable device: the edges never touch host memory of this library
     h->no_window = false; // a duplicate edge of the PREVIOUS problem says nothing about this one
-    const bool direct = Nc > 0 && Np > 0 && window_shape_ok(h, B, pose_off, Ne, kSmallMaxN / 6) && ensure_cuda(h) == VISO_BA_OK;
+    // ... and one LARGE problem whose structure the device builds (build_general_device) is staged the same way
+    const bool big_general = B == 1 && Ne >= kDevGeneralMinEdges && h->cfg.host_structure_build == 0 && !h->photo_next;
+    const bool direct = Nc > 0 && Np > 0 && (window_shape_ok(h, B, pose_off, Ne, kSmallMaxN / 6) || big_general) && ensure_cuda(h) == VISO_BA_OK;
     const int nt_host = host_threads(h);
     if (!direct) { // validation of the edges on a few host threads: the first offending edge (lowest index) is reported
         for (int64_t b = 0; b < B; ++b) {
@@ -1025,7 +1030,8 @@ int32_t build_tables(viso_ba* h, Built& b)
     std::vector<int64_t> cam_off((size_t)B + 1);
     for (int64_t p = 0; p <= B; ++p) cam_off[(size_t)p] = b.prob_cam0[(size_t)p];
     b.window = Np > 0 && b.max_n <= kSmallMaxN && window_shape_ok(h, B, cam_off.data(), Ne, kWinMaxCams);
-    if (h->edges_on_device && !b.window) return fail(h, VISO_BA_ERR_STATE, "internal: device-resident edges without the window path");
+    // device-resident edges off the window path: one large problem whose structure build_general_device makes (upload
+    // brings them back to the host if it has to fall back to the host build)
     if (b.window) {
         if (B == 1) h->edge_off_all.assign({ 0, Ne }); // AddEdge may have grown a single problem since
         b.tiles_max = tiles_upper_bound(B, pt0.data(), h->edge_off_all.data());
@@ -1260,6 +1266,138 @@ int32_t build_general(viso_ba* h, Built& b)
     return VISO_BA_OK;
 }
 
+// The general path's structure build ON THE DEVICE (one large problem, B == 1): the edges are staged and validated like the
+// window path's, sorted by (point, pose) with the same radix sort, the structure of S is marked by a kernel, the pairs are
+// generated point by point and ordered by S block with a stable radix sort.  The host keeps what is small: shard bounds
+// (from pt_ptr), the compact block numbering and the solve plan (from the presence bytes), the work items (from the block
+// offsets).  The tables are the ones build_general makes (same order of observations, same order of pairs inside a block).
+// Observations and pairs stay in the handle's own buffers; the arena holds everything else.
+
+int32_t build_general_device(viso_ba* h, Built& b)
+{
+    const int64_t Nc = (int64_t)h->poses.size() / 7, Np = (int64_t)h->points.size() / 3;
+    const int64_t Ne = h->edges_on_device ? h->n_edges_dev : (int64_t)h->e_pose.size();
+    const double t_begin = now_ms();
+    cudaStream_t st = h->stream;
+    int32_t rc;
+    SetupIn in;
+    SetupWork w;
+    const int64_t cam_off[2] = { 0, Nc }, edge_off[2] = { 0, Ne };
+    if (h->edges_on_device) { // staged (and validated) by set_problem straight from the caller's arrays; only the views are rebuilt
+        RawEdges r;
+        carve_raw(h->raw.p, r, Ne, 1);
+        carve_scratch(h->scratch.p, w, Ne, 1, tiles_upper_bound(1, b.pt0.data(), edge_off));
+        std::memset(&in, 0, sizeof(in));
+        in.n_edges = Ne, in.n_points = (int32_t)Np, in.n_cams = (int32_t)Nc, in.n_problems = 1;
+        in.local_indices = h->edges_local ? 1 : 0;
+        in.e_pose = r.e_pose, in.e_point = r.e_point, in.e_uv = r.e_uv, in.edge_off = r.edge_off;
+        in.prob_cam0 = r.prob_cam0, in.prob_pt0 = r.prob_pt0;
+    } else if ((rc = stage_edges_on_device(h, 1, cam_off, b.pt0.data(), edge_off, h->e_pose.data(), h->e_point.data(), h->e_uv.data(), false, &in, &w))) {
+        return rc;
+    }
+    // small tables the kernels read: cam_free, prob_nfree; later the compact block numbering
+    const size_t dense_blocks = (size_t)b.n_blocks;
+    Carver ct(nullptr);
+    ct.take<int32_t>((size_t)Nc), ct.take<int32_t>(1), ct.take<int32_t>(dense_blocks), ct.take<uint8_t>(dense_blocks);
+    if ((rc = devbuf_reserve(h, h->gen_tabs, ct.used))) return rc;
+    Carver c2(h->gen_tabs.p);
+    int32_t* d_cam_free = c2.take<int32_t>((size_t)Nc);
+    int32_t* d_nfree = c2.take<int32_t>(1);
+    int32_t* d_remap = c2.take<int32_t>(dense_blocks);
+    uint8_t* d_present = c2.take<uint8_t>(dense_blocks);
+    CU(cudaMemcpyAsync(d_cam_free, b.cam_free.data(), sizeof(int32_t) * (size_t)Nc, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(d_nfree, b.prob_nfree.data(), sizeof(int32_t), cudaMemcpyHostToDevice, st));
+    in.cam_free = d_cam_free, in.prob_nfree = d_nfree;
+    // observations in (point, pose) order
+    Carver co(nullptr);
+    co.take<int32_t>((size_t)Np + 1), co.take<int32_t>((size_t)Np), co.take<int32_t>((size_t)Ne), co.take<float2>((size_t)Ne);
+    if ((rc = devbuf_reserve(h, h->gen_obs, co.used))) return rc;
+    Carver c3(h->gen_obs.p);
+    SetupOut o;
+    std::memset(&o, 0, sizeof(o));
+    o.pt_ptr = c3.take<int32_t>((size_t)Np + 1), o.pt_prob = c3.take<int32_t>((size_t)Np);
+    o.obs_cam = c3.take<int32_t>((size_t)Ne), o.obs_uv = c3.take<float2>((size_t)Ne);
+    run_k(h, "setup", [&] { return setup_sort_only(in, w, o, st); });
+    const bool compact = b.max_n > kSmallMaxN;
+    if (compact) {
+        CU(cudaMemsetAsync(d_present, 0, dense_blocks, st));
+        run_k(h, "setup", [&] { return gen_present((int32_t)Np, o.pt_ptr, o.obs_cam, d_cam_free, d_present, st); });
+    }
+    b.pt_ptr.resize((size_t)Np + 1);
+    CU(cudaMemcpyAsync(b.pt_ptr.data(), o.pt_ptr, sizeof(int32_t) * ((size_t)Np + 1), cudaMemcpyDeviceToHost, st));
+    std::vector<uint8_t> present;
+    if (compact) {
+        present.resize(dense_blocks);
+        CU(cudaMemcpyAsync(present.data(), d_present, dense_blocks, cudaMemcpyDeviceToHost, st));
+    }
+    CU(cudaStreamSynchronize(st));
+    CU(cudaGetLastError());
+    const double t_sort = now_ms();
+    { // this rank's point range (sharding: contiguous points, balanced on edge count)
+        std::vector<int64_t> bounds((size_t)h->n_ranks + 1);
+        shard_bounds(b.pt_ptr.data(), Np, Ne, h->n_ranks, bounds.data());
+        h->shard_pt.assign(bounds.begin(), bounds.end());
+    }
+    const int32_t pt_begin = h->shard_pt[(size_t)h->rank], pt_end = h->shard_pt[(size_t)h->rank + 1];
+    std::vector<int32_t> remap;
+    b.compact = compact;
+    if (compact) {
+        compact_structure(h, b, b.prob_nfree[0], present, remap);
+        CU(cudaMemcpyAsync(d_remap, remap.data(), sizeof(int32_t) * dense_blocks, cudaMemcpyHostToDevice, st));
+    }
+    const double t_struct = now_ms();
+    // pairs of this rank's points: count, scan, generate, sort by block, block offsets
+    const int64_t npl = (int64_t)pt_end - pt_begin;
+    size_t temp_bytes = gen_temp_bytes(npl, 0);
+    Carver cw0(nullptr);
+    cw0.take<int64_t>((size_t)npl + 1), cw0.take<char>(temp_bytes);
+    if ((rc = devbuf_reserve(h, h->gen_work, cw0.used))) return rc;
+    {
+        Carver cw(h->gen_work.p);
+        int64_t* d_counts = cw.take<int64_t>((size_t)npl + 1);
+        void* d_temp = cw.take<char>(temp_bytes);
+        run_k(h, "setup", [&] { return gen_pair_offsets(pt_begin, pt_end, o.pt_ptr, o.obs_cam, d_cam_free, d_counts, d_temp, temp_bytes, st); });
+        if ((rc = pin_reserve(h, 64))) return rc;
+        CU(cudaMemcpyAsync(h->pin, d_counts + npl, sizeof(int64_t), cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+    }
+    b.n_pairs = *static_cast<const int64_t*>(h->pin);
+    if (b.n_pairs > 0x7fffffff) return fail(h, VISO_BA_ERR_UNSUPPORTED, "pair list too long (%lld)", (long long)b.n_pairs);
+    const size_t npairs = (size_t)std::max<int64_t>(b.n_pairs, 1);
+    temp_bytes = gen_temp_bytes(npl, b.n_pairs);
+    Carver cw1(nullptr); // the offsets stay at the front: the buffer may move when it grows, so they are recomputed below
+    cw1.take<int64_t>((size_t)npl + 1), cw1.take<char>(temp_bytes), cw1.take<unsigned int>(npairs), cw1.take<unsigned int>(npairs);
+    cw1.take<unsigned long long>(npairs), cw1.take<int64_t>((size_t)b.n_blocks + 1);
+    const bool moved = cw1.used > h->gen_work.cap;
+    if ((rc = devbuf_reserve(h, h->gen_work, cw1.used))) return rc;
+    if ((rc = devbuf_reserve(h, h->pairbuf, sizeof(unsigned long long) * npairs))) return rc;
+    std::vector<int64_t> blk_ptr((size_t)b.n_blocks + 1, 0);
+    {
+        Carver cw(h->gen_work.p);
+        int64_t* d_counts = cw.take<int64_t>((size_t)npl + 1);
+        void* d_temp = cw.take<char>(temp_bytes);
+        unsigned int* d_keys = cw.take<unsigned int>(npairs);
+        unsigned int* d_keys_sorted = cw.take<unsigned int>(npairs);
+        unsigned long long* d_vals = cw.take<unsigned long long>(npairs);
+        int64_t* d_blk_ptr = cw.take<int64_t>((size_t)b.n_blocks + 1);
+        if (moved) run_k(h, "setup", [&] { return gen_pair_offsets(pt_begin, pt_end, o.pt_ptr, o.obs_cam, d_cam_free, d_counts, d_temp, temp_bytes, st); });
+        run_k(h, "setup", [&] {
+            return gen_pairs(pt_begin, pt_end, o.pt_ptr, o.obs_cam, d_cam_free, compact ? d_remap : nullptr, d_counts, b.n_pairs, b.n_blocks, d_keys,
+                d_keys_sorted, d_vals, static_cast<unsigned long long*>(h->pairbuf.p), d_blk_ptr, d_temp, temp_bytes, st);
+        });
+        CU(cudaMemcpyAsync(blk_ptr.data(), d_blk_ptr, sizeof(int64_t) * ((size_t)b.n_blocks + 1), cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+        CU(cudaGetLastError());
+    }
+    const double t_pairs = now_ms();
+    general_items_and_chunks(h, b, blk_ptr, pt_begin, pt_end);
+    b.dev_general = true;
+    if (h->cfg.verbose)
+        fprintf(stderr, "[viso_ba] device structure build: stage + sort %.1f ms, block structure + solve plan %.1f ms, pair lists %.1f ms (%lld pairs), items %.1f ms\n",
+            t_sort - t_begin, t_struct - t_sort, t_pairs - t_struct, (long long)b.n_pairs, now_ms() - t_pairs);
+    return VISO_BA_OK;
+}
+
 template <typename T> int32_t h2d(viso_ba* h, T* dst, const std::vector<T>& src)
 {
     if (src.empty()) return VISO_BA_OK;
@@ -1310,16 +1448,17 @@ constexpr int kMaxIterStats = 4096;
 void carve(Arena& A, DevPtrs& d, int64_t Nc, int64_t Np, int64_t Ne, int64_t B, const Built& b, bool large, int ldL)
 {
     A.used = 0;
-    d.pt_ptr = A.take<int32_t>((size_t)Np + 1);
-    d.pt_prob = A.take<int32_t>((size_t)Np);
-    d.obs_cam = A.take<int32_t>((size_t)Ne);
-    d.obs_uv = A.take<float2>((size_t)Ne);
+    const bool own = !b.dev_general; // the device-side general build keeps observations and pairs in the handle's own buffers
+    d.pt_ptr = A.take<int32_t>(own ? (size_t)Np + 1 : 0);
+    d.pt_prob = A.take<int32_t>(own ? (size_t)Np : 0);
+    d.obs_cam = A.take<int32_t>(own ? (size_t)Ne : 0);
+    d.obs_uv = A.take<float2>(own ? (size_t)Ne : 0);
     d.cam_free = A.take<int32_t>((size_t)Nc);
     d.cam_prob = A.take<int32_t>((size_t)Nc);
     d.prob_cam0 = A.take<int32_t>((size_t)B + 1);
     d.prob_tri0 = A.take<int32_t>((size_t)B + 1);
     d.prob_nfree = A.take<int32_t>((size_t)B);
-    d.pairs = A.take<int2>((size_t)b.n_pairs);
+    d.pairs = A.take<int2>(own ? (size_t)b.n_pairs : 0);
     const size_t NeW = b.window ? (size_t)Ne : 0, NpW = b.window ? (size_t)Np : 0, BW = b.window ? (size_t)B + 1 : 0;
     d.items = A.take<int4>(b.items.size() / 4);
     d.diag_items = A.take<int32_t>(b.diag_items.size());
@@ -1587,7 +1726,11 @@ extern "C" int32_t viso_ba_upload(viso_ba* h)
         const int64_t Ne = h->edges_on_device ? h->n_edges_dev : (int64_t)h->e_pose.size();
         Built b;
         if ((rc = build_tables(h, b))) break;
-        if (!b.window && (rc = build_general(h, b))) break;
+        if (!b.window) {
+            const bool on_device = B == 1 && !h->photo && Ne >= kDevGeneralMinEdges && h->cfg.host_structure_build == 0;
+            if (!on_device && (rc = edges_back_to_host(h))) break; // the host build reads the host vectors
+            if ((rc = on_device ? build_general_device(h, b) : build_general(h, b))) break;
+        }
         h->max_n = b.max_n;
         h->use_large = b.max_n > kSmallMaxN;
         if (h->use_large && B > 1) {
@@ -1643,11 +1786,18 @@ extern "C" int32_t viso_ba_upload(viso_ba* h)
                 continue;
             }
         } else {
-            if ((rc = h2d(h, d.pt_ptr, b.pt_ptr))) break;
-            if ((rc = h2d(h, d.pt_prob, b.pt_prob))) break;
-            if ((rc = h2d(h, d.obs_cam, b.obs_cam))) break;
-            if ((rc = h2d(h, reinterpret_cast<float*>(d.obs_uv), b.obs_uv))) break;
-            if ((rc = h2d(h, reinterpret_cast<int32_t*>(d.pairs), b.pairs))) break;
+            if (b.dev_general) { // observations and pairs were built on the device and live in the handle's own buffers
+                Carver c3(h->gen_obs.p);
+                d.pt_ptr = c3.take<int32_t>((size_t)Np + 1), d.pt_prob = c3.take<int32_t>((size_t)Np);
+                d.obs_cam = c3.take<int32_t>((size_t)Ne), d.obs_uv = c3.take<float2>((size_t)Ne);
+                d.pairs = static_cast<int2*>(h->pairbuf.p);
+            } else {
+                if ((rc = h2d(h, d.pt_ptr, b.pt_ptr))) break;
+                if ((rc = h2d(h, d.pt_prob, b.pt_prob))) break;
+                if ((rc = h2d(h, d.obs_cam, b.obs_cam))) break;
+                if ((rc = h2d(h, reinterpret_cast<float*>(d.obs_uv), b.obs_uv))) break;
+                if ((rc = h2d(h, reinterpret_cast<int32_t*>(d.pairs), b.pairs))) break;
+            }
             if ((rc = h2d(h, reinterpret_cast<int32_t*>(d.items), b.items))) break;
             if ((rc = h2d(h, d.diag_items, b.diag_items))) break;
             if ((rc = h2d(h, d.block_item_ptr, b.block_item_ptr))) break;
