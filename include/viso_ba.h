@@ -213,6 +213,36 @@ int32_t viso_ba_get_problem_summaries(viso_ba* h, viso_ba_summary* out);
 int32_t viso_ba_eval_cost(viso_ba* h, double* cost);
 
 /*
+ * No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ *
+ * The same robustified reprojection cost as viso_ba_eval_cost, of a raw edge list that is ALREADY on the device, computed
+ * with no handle and no allocation: no cudaMalloc / cudaFree / allocating library call, here or inside.  The scratch the
+ * pass needs (the R|t table of the poses, the partial sums of the CTAs) lives in one file-scope `static __device__`
+ * array of 402,688 bytes (viso_b200/csrc/ba_static_cost.cu) that every GPU loading the library holds until exit.
+ *   - runs on the calling thread's CURRENT device, on cuda_stream (a cudaStream_t of that device; NULL: the default
+ *     stream); three kernels are enqueued and the call returns without synchronising: *cost_out_dev is valid once the
+ *     stream has reached that point
+ *   - every *_dev pointer is device memory of that device: poses7 [n_poses][7] (q xyzw, t), points3 [n_points][3],
+ *     edge_pose / edge_point [n_edges], edge_uv [n_edges][2] float32 (the layout of viso_ba_set_problem), one double out
+ *   - limits: n_poses <= VISO_BA_STATIC_MAX_POSES, n_edges <= VISO_BA_STATIC_MAX_EDGES; beyond them the call returns
+ *     VISO_BA_ERR_CAPACITY, enqueues nothing and says so in err (err_cap bytes, may be NULL)
+ *   - edge indices are checked on the device: one out of range makes the cost NaN (nothing is read out of bounds)
+ *   - the sum has a fixed shape: repeated calls on the same input return the same bits; viso_ba_eval_cost sums in another
+ *     order, so the two agree to rounding (~1e-15 relative)
+ *   - the first call on a device looks the array's address up (cudaGetSymbolAddress): make that call outside a capture
+ *   - every call on a GPU shares the array, which keeps the last call's contents (nothing in it needs clearing: a call
+ *     writes each word before reading it).  Calls that OVERLAP on one GPU (two streams, two threads) race: serialise them.
+ */
+#define VISO_BA_STATIC_MAX_POSES 4096
+#define VISO_BA_STATIC_MAX_EDGES 2147483647LL
+int32_t viso_ba_eval_cost_static(void* cuda_stream, int64_t n_poses, const double* poses7_dev, int64_t n_points,
+                                 const double* points3_dev, int64_t n_edges, const int32_t* edge_pose_dev,
+                                 const int32_t* edge_point_dev, const float* edge_uv_dev, double fx, double fy,
+                                 double cx, double cy, double huber_delta, double* cost_out_dev, char* err,
+                                 int32_t err_cap);
+
+/*
  * debug / parity hooks: one linearisation of the current state with damping lambda.
  * S is the dense reduced camera system (row-major n x n, n = 6 * #free poses of problem 0),
  * bs its right-hand side (b = -gradient convention of g2o).  Single-problem handles.

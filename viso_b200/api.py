@@ -115,6 +115,9 @@ SYMBOLS = {
     "viso_ba_get_points": (C.c_int32, [_P, C.c_int64, C.c_int64, _D]),
     "viso_ba_get_problem_summaries": (C.c_int32, [_P, C.POINTER(Summary)]),
     "viso_ba_eval_cost": (C.c_int32, [_P, _D]),
+    # device pointers as plain addresses (the caller owns the device memory; nothing is allocated by the call)
+    "viso_ba_eval_cost_static": (C.c_int32, [_P, C.c_int64, _P, C.c_int64, _P, C.c_int64, _P, _P, _P, C.c_double, C.c_double,
+                                             C.c_double, C.c_double, C.c_double, _P, C.c_char_p, C.c_int32]),
     "viso_ba_debug_reduced_system": (C.c_int32, [_P, C.c_double, C.c_int32, _D, _D, _I32]),
     "viso_ba_debug_host_build": (C.c_int32, [_P, C.c_int32, _D, C.POINTER(C.c_uint64)]),
     "viso_ba_kernel_launches": (C.c_int64, [_P]),

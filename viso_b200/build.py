@@ -17,7 +17,7 @@ CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libviso_ba.so")
 STAMP = os.path.join(HERE, ".libviso_ba.stamp")
 SYNTH_LIB = os.path.join(HERE, "libviso_synth.so")
-SOURCES = ["ba_kernels.cu", "ba_window.cu", "ba_dense.cu", "ba_setup.cu", "ba_photo.cu", "direct_pose.cu", "lk_align.cu", "pyramid.cu", "viso_ba.cpp"]
+SOURCES = ["ba_kernels.cu", "ba_window.cu", "ba_dense.cu", "ba_setup.cu", "ba_photo.cu", "ba_static_cost.cu", "direct_pose.cu", "lk_align.cu", "pyramid.cu", "viso_ba.cpp"]
 SYNTH_SOURCES = ["synth.cpp"]
 HEADERS = sorted(glob.glob(os.path.join(CSRC, "*.h")) + glob.glob(os.path.join(CSRC, "*.cuh"))) + [os.path.join(ROOT, "include", h) for h in ("viso_ba.h", "viso_ba_synth.h", "viso_direct.h", "viso_lk.h")]
 NVCC_FLAGS = [
