@@ -54,6 +54,7 @@ constexpr int kRecDoubles = 12;   // per-observation record
 constexpr int kPtInfoDoubles = 9; // per-point record
 constexpr int kItemPart = 42;     // 36 block entries + 6 rhs entries per work item
 constexpr int kChunkPoints = 1024;
+constexpr int kItemMaxPairs = 512; // general path: most pairs in one work item of k_schur_blocks (one warp: 16 per lane)
 constexpr int kSmallMaxN = 162; // dense per-problem solve in shared memory up to 27 free poses
 // window fast path (ba_window.cu): one CTA per tile of consecutive points of one problem
 constexpr int kWinThreads = 128;

@@ -213,12 +213,65 @@ __device__ __forceinline__ void butterfly_reduce(double (&v)[N], int lane)
     }
 }
 
+// Round 2: the records of the next kSbStages pairs of a lane are on their way to shared memory (cp.async, no registers
+// held) while the lane computes: the kernel was bound by the latency of its gathers (two dependent L2 round trips per
+// pair at 8 warps per SM), not by their bandwidth.  The pair product is the tile kernel's (ba_window.cu): M = -G~_a G~_b^T,
+// T = M J~_b, S += J~_a^T T with the structural zeros of J~ left out, fused into the 42 accumulators (104 FP64 instructions
+// per pair; the version it replaces formed the 6 x 6 product first and added it: 160).
+constexpr int kSbThreads = 128;
+constexpr int kSbStages = 4;    // pairs of a lane in flight
+constexpr int kSbChunks = 11;   // 16-byte chunks staged per pair: a0..a5, b0..b4
+constexpr int kSbMaxIter = kItemMaxPairs / 32; // pairs of an item per lane (general_items_and_chunks cuts the items)
+constexpr size_t kSbIdxBytes = sizeof(int2) * kSbMaxIter * kSbThreads;
+constexpr size_t kSbBytes = kSbIdxBytes + sizeof(double2) * kSbStages * kSbChunks * kSbThreads;
+
+__device__ __forceinline__ void sb_cp16(void* smem, const void* gmem)
+{
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void sb_cp8(void* smem, const void* gmem)
+{
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((unsigned)__cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void sb_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void sb_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+// v += J~_a^T (M J~_b) for one pair; a*, b*: chunks 0..4 of the two records
+__device__ __forceinline__ void sb_pair_product(double (&v)[48], const double2& a0, const double2& a1, const double2& b0, const double2& b1,
+    double m00, double m01, double m10, double m11)
+{
+    const double xb = b0.x, yb = b0.y, zb = b1.x;
+    const double bxz = xb * zb, byz = yb * zb, bxy = xb * yb, bxx = fma(xb, xb, 1.0), byy = fma(yb, yb, 1.0);
+    double t0[6], t1[6];
+    t0[0] = m00 * zb, t1[0] = m10 * zb;
+    t0[1] = m01 * zb, t1[1] = m11 * zb;
+    t0[2] = -fma(m00, bxz, m01 * byz), t1[2] = -fma(m10, bxz, m11 * byz);
+    t0[3] = -fma(m00, bxy, m01 * byy), t1[3] = -fma(m10, bxy, m11 * byy);
+    t0[4] = fma(m00, bxx, m01 * bxy), t1[4] = fma(m10, bxx, m11 * bxy);
+    t0[5] = fma(m01, xb, -(m00 * yb)), t1[5] = fma(m11, xb, -(m10 * yb));
+    const double xa = a0.x, ya = a0.y, za = a1.x;
+    const double axz = -(xa * za), ayz = -(ya * za), axy = xa * ya, axx = fma(xa, xa, 1.0), ayy = -fma(ya, ya, 1.0);
+    const double naxy = -axy, nya = -ya;
+#pragma unroll
+    for (int c = 0; c < 6; ++c) {
+        v[c] = fma(za, t0[c], v[c]);
+        v[6 + c] = fma(za, t1[c], v[6 + c]);
+        v[12 + c] = fma(axz, t0[c], fma(ayz, t1[c], v[12 + c]));
+        v[18 + c] = fma(naxy, t0[c], fma(ayy, t1[c], v[18 + c]));
+        v[24 + c] = fma(axx, t0[c], fma(axy, t1[c], v[24 + c]));
+        v[30 + c] = fma(nya, t0[c], fma(xa, t1[c], v[30 + c]));
+    }
+}
+
 // PHOTO: photometric edges (ba_photo.cu): the 2 x 2 middle of a diagonal pair is the symmetric matrix w F C_tt F in ph_mid
 // instead of diag(w fx^2, w fy^2)
 template <bool PHOTO>
-__global__ void __launch_bounds__(128) k_schur_blocks(DevProblem P, int diag_only)
+__global__ void __launch_bounds__(kSbThreads, 2) k_schur_blocks(DevProblem P, int diag_only)
 {
-    const int lane = threadIdx.x & 31;
+    extern __shared__ __align__(16) unsigned char sb_sm[];
+    int2* const s_idx = reinterpret_cast<int2*>(sb_sm);                  // [kSbMaxIter][kSbThreads]
+    double2* const s_rec = reinterpret_cast<double2*>(sb_sm + kSbIdxBytes); // [kSbStages][kSbChunks][kSbThreads]
+    const int tid = threadIdx.x, lane = tid & 31;
     const int widx = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     int item;
     if (diag_only) {
@@ -233,69 +286,75 @@ __global__ void __launch_bounds__(128) k_schur_blocks(DevProblem P, int diag_onl
     const bool is_diag = (it.w & 1) != 0;
     if (!P.lm[prob].active) return;
     const double fx2 = P.fx * P.fx, fy2 = P.fy * P.fy;
-
-    double acc[32];
-    double acc2[16]; // entries 32..35 of the block, then 6 rhs entries, padded to 16
+    // this lane's pairs: it.x + lane, + 32, ...  Their indices first (one group), then the records of kSbStages pairs ahead
+    const int n_it = it.y - it.x > lane ? (it.y - it.x - lane + 31) >> 5 : 0; // <= kSbMaxIter
+    for (int j = 0; j < n_it; ++j) sb_cp8(s_idx + j * kSbThreads + tid, P.pairs + it.x + lane + 32 * j);
+    sb_commit();
+    sb_wait<0>();
+    auto issue = [&](int j) { // records of pair j of this lane -> stage j % kSbStages
+        if (j < n_it) {
+            const int2 pr = s_idx[j * kSbThreads + tid];
+            const double2* ra = reinterpret_cast<const double2*>(P.rec + kRecDoubles * (size_t)pr.x);
+            double2* dst = s_rec + (size_t)(j % kSbStages) * kSbChunks * kSbThreads + tid;
 #pragma unroll
-    for (int i = 0; i < 32; ++i) acc[i] = 0.0;
+            for (int c = 0; c < 6; ++c) sb_cp16(dst + c * kSbThreads, ra + c);
+            if (pr.y != pr.x) {
+                const double2* rb = reinterpret_cast<const double2*>(P.rec + kRecDoubles * (size_t)pr.y);
 #pragma unroll
-    for (int i = 0; i < 16; ++i) acc2[i] = 0.0;
+                for (int c = 0; c < 5; ++c) sb_cp16(dst + (6 + c) * kSbThreads, rb + c);
+            }
+        }
+        sb_commit(); // one group per pair, empty or not: the wait below counts groups
+    };
+#pragma unroll
+    for (int j = 0; j < kSbStages; ++j) issue(j);
 
-    for (int q = it.x + lane; q < it.y; q += 32) {
-        const int2 pr = __ldg(P.pairs + q);
-        const double2* __restrict__ ra = reinterpret_cast<const double2*>(P.rec + kRecDoubles * (size_t)pr.x);
-        const double2* __restrict__ rb = reinterpret_cast<const double2*>(P.rec + kRecDoubles * (size_t)pr.y);
-        const double2 a0 = ra[0], a1 = ra[1], a2 = ra[2], a3 = ra[3], a4 = ra[4];
-        const double2 b0 = rb[0], b1 = rb[1], b2 = rb[2], b3 = rb[3], b4 = rb[4];
-        double ja0[6], ja1[6], jb0[6], jb1[6];
-        jtilde(a0.x, a0.y, a1.x, ja0, ja1);
-        jtilde(b0.x, b0.y, b1.x, jb0, jb1);
-        // M = -G~_a G~_b^T
-        double m00 = -(a2.x * b2.x + a2.y * b2.y + a3.x * b3.x);
-        double m01 = -(a2.x * b3.y + a2.y * b4.x + a3.x * b4.y);
-        double m10 = -(a3.y * b2.x + a4.x * b2.y + a4.y * b3.x);
-        double m11 = -(a3.y * b3.y + a4.x * b4.x + a4.y * b4.y);
+    double v[48]; // 36 block entries, 6 rhs entries, padding
+#pragma unroll
+    for (int i = 0; i < 48; ++i) v[i] = 0.0;
+    for (int j = 0; j < n_it; ++j) {
+        sb_wait<kSbStages - 1>(); // the group of pair j has landed
+        const int2 pr = s_idx[j * kSbThreads + tid];
         const bool same = pr.x == pr.y;
+        const double2* src = s_rec + (size_t)(j % kSbStages) * kSbChunks * kSbThreads + tid;
+        const double2 a0 = src[0], a1 = src[kSbThreads], a2 = src[2 * kSbThreads], a3 = src[3 * kSbThreads], a4 = src[4 * kSbThreads];
+        const double2 a5 = src[5 * kSbThreads];
+        const double2* sb = same ? src : src + 6 * kSbThreads;
+        const double2 b0 = sb[0], b1 = sb[kSbThreads], b2 = sb[2 * kSbThreads], b3 = sb[3 * kSbThreads], b4 = sb[4 * kSbThreads];
+        issue(j + kSbStages); // the stage is free: its values are in registers
+        // M = -G~_a G~_b^T;  G~ = (c2.x c2.y c3.x ; c3.y c4.x c4.y)
+        double m00 = -fma(a2.x, b2.x, fma(a2.y, b2.y, a3.x * b3.x));
+        double m01 = -fma(a2.x, b3.y, fma(a2.y, b4.x, a3.x * b4.y));
+        double m10 = -fma(a3.y, b2.x, fma(a4.x, b2.y, a4.y * b3.x));
+        double m11 = -fma(a3.y, b3.y, fma(a4.x, b4.x, a4.y * b4.y));
         if (same) {
             if (PHOTO) {
                 const double* __restrict__ md = P.ph_mid + 4 * (size_t)pr.x;
                 m00 += md[0], m01 += md[1], m10 += md[1], m11 += md[2];
             } else {
-                m00 += a1.y * fx2;
-                m11 += a1.y * fy2;
+                m00 = fma(a1.y, fx2, m00);
+                m11 = fma(a1.y, fy2, m11);
             }
         }
-        double t0[6], t1[6];
-#pragma unroll
-        for (int c = 0; c < 6; ++c) {
-            t0[c] = m00 * jb0[c] + m01 * jb1[c];
-            t1[c] = m10 * jb0[c] + m11 * jb1[c];
-        }
-        double x[36];
-#pragma unroll
-        for (int r = 0; r < 6; ++r)
-#pragma unroll
-            for (int c = 0; c < 6; ++c) x[6 * r + c] = ja0[r] * t0[c] + ja1[r] * t1[c];
-        if (is_diag && !same) { // duplicate (point, pose) edges: both (a,b) and (b,a) land here
-#pragma unroll
-            for (int r = 0; r < 6; ++r)
-#pragma unroll
-                for (int c = r; c < 6; ++c) {
-                    const double sdiag = x[6 * r + c] + x[6 * c + r];
-                    x[6 * r + c] = sdiag;
-                    x[6 * c + r] = sdiag;
-                }
-        }
-#pragma unroll
-        for (int i = 0; i < 32; ++i) acc[i] += x[i];
-#pragma unroll
-        for (int i = 0; i < 4; ++i) acc2[i] += x[32 + i];
-        if (same) {
-            const double2 a5 = ra[5];
-#pragma unroll
-            for (int r = 0; r < 6; ++r) acc2[4 + r] += ja0[r] * a5.x + ja1[r] * a5.y;
+        sb_pair_product(v, a0, a1, b0, b1, m00, m01, m10, m11);
+        if (is_diag && !same) // duplicate (point, pose) edges: (a, b) and (b, a) both land in this diagonal block
+            sb_pair_product(v, b0, b1, a0, a1, m00, m10, m01, m11);
+        if (same) { // rhs: Jp^T v~
+            const double xa = a0.x, ya = a0.y, za = a1.x;
+            v[36] = fma(za, a5.x, v[36]);
+            v[37] = fma(za, a5.y, v[37]);
+            v[38] = fma(-(xa * za), a5.x, fma(-(ya * za), a5.y, v[38]));
+            v[39] = fma(-(xa * ya), a5.x, fma(-fma(ya, ya, 1.0), a5.y, v[39]));
+            v[40] = fma(fma(xa, xa, 1.0), a5.x, fma(xa * ya, a5.y, v[40]));
+            v[41] = fma(-ya, a5.x, fma(xa, a5.y, v[41]));
         }
     }
+    sb_wait<0>();
+    double acc[32], acc2[16]; // the fold below takes 32 + 16 values
+#pragma unroll
+    for (int i = 0; i < 32; ++i) acc[i] = v[i];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) acc2[i] = v[32 + i];
     butterfly_reduce<32>(acc, lane);
     // second group: 16 padded values; fold the two half-warps first, then butterfly over 16 lanes
 #pragma unroll
@@ -620,8 +679,14 @@ int launch_schur_blocks(const DevProblem& P, int diag_only, cudaStream_t st)
 {
     const long long warps = diag_only ? P.n_diag_items : P.n_items;
     if (warps <= 0) return 0;
-    if (P.ph_sum) k_schur_blocks<true><<<cdiv(warps * 32, 128), 128, 0, st>>>(P, diag_only);
-    else k_schur_blocks<false><<<cdiv(warps * 32, 128), 128, 0, st>>>(P, diag_only);
+    static PerDeviceOnce once;
+    if (!once.run([] {
+            return cudaFuncSetAttribute(k_schur_blocks<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSbBytes) == cudaSuccess
+                && cudaFuncSetAttribute(k_schur_blocks<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSbBytes) == cudaSuccess;
+        }))
+        return 0;
+    if (P.ph_sum) k_schur_blocks<true><<<cdiv(warps * 32, kSbThreads), kSbThreads, kSbBytes, st>>>(P, diag_only);
+    else k_schur_blocks<false><<<cdiv(warps * 32, kSbThreads), kSbThreads, kSbBytes, st>>>(P, diag_only);
     return 1;
 }
 

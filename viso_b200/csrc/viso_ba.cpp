@@ -1088,7 +1088,7 @@ void general_items_and_chunks(viso_ba* h, Built& b, const std::vector<int64_t>& 
     const int64_t B = h->n_problems;
     const std::vector<int64_t>& pt0 = b.pt0;
     int64_t item_pairs = (b.n_pairs / 16384 + 31) / 32 * 32;
-    item_pairs = std::max<int64_t>(64, std::min<int64_t>(512, item_pairs));
+    item_pairs = std::max<int64_t>(64, std::min<int64_t>(kItemMaxPairs, item_pairs));
     b.block_item_ptr.assign((size_t)b.n_blocks + 1, 0);
     {
         int32_t prob = 0;
