@@ -80,6 +80,18 @@ __global__ void k_gather_current(DevProblem P, double* __restrict__ poses_out, d
 //   S_IJ  -= Jp_a^T G_a G_b^T Jp_b,  S_II += w Jp_a^T Jp_a,  bs_I -= Jp_a^T v_a
 // with Jp = F J~(x/z, y/z, 1/z) rebuilt from three doubles (viso.cpp:653-655).
 // ------------------------------------------------------------------------------------------
+// R|t of one pose (96 bytes, 16-byte aligned) by six 16-byte loads instead of twelve 8-byte ones: the per-point kernels
+// below are bound by the number of their outstanding global loads (ncu on C4: 56 % long scoreboard, 29 % LG throttle)
+__device__ __forceinline__ void load_rt(const double* __restrict__ cam_rt, int cam, double (&rt)[12])
+{
+    const double2* __restrict__ p = reinterpret_cast<const double2*>(cam_rt + 12 * (size_t)cam);
+#pragma unroll
+    for (int k = 0; k < 6; ++k) {
+        const double2 v = __ldg(p + k);
+        rt[2 * k] = v.x, rt[2 * k + 1] = v.y;
+    }
+}
+
 __global__ void __launch_bounds__(128) k_linearize(DevProblem P, int init_pass, double lambda_override)
 {
     const int p = P.pt_begin + blockIdx.x * blockDim.x + threadIdx.x;
@@ -95,11 +107,17 @@ __global__ void __launch_bounds__(128) k_linearize(DevProblem P, int init_pass, 
     const int s0 = P.pt_ptr[p], s1 = P.pt_ptr[p + 1];
 
     double h00 = 0, h10 = 0, h11 = 0, h20 = 0, h21 = 0, h22 = 0, b0 = 0, b1 = 0, b2 = 0, cost = 0;
+    // the pose index and the pixel of the NEXT observation are requested before this one's R|t: one dependent round trip less
+    int cam_n = s0 < s1 ? __ldg(P.obs_cam + s0) : 0;
+    float2 uv_n = s0 < s1 ? __ldg(P.obs_uv + s0) : make_float2(0.f, 0.f);
     for (int s = s0; s < s1; ++s) {
-        const int cam = __ldg(P.obs_cam + s);
-        const float2 uv = __ldg(P.obs_uv + s);
+        const int cam = cam_n;
+        const float2 uv = uv_n;
+        if (s + 1 < s1) cam_n = __ldg(P.obs_cam + s + 1), uv_n = __ldg(P.obs_uv + s + 1);
+        double rt[12];
+        load_rt(cam_rt, cam, rt);
         ObsGeom g;
-        obs_geometry(P, cam_rt + 12 * (size_t)cam, X, Y, Z, uv, g);
+        obs_geometry(P, rt, X, Y, Z, uv, g);
         cost += g.rho;
         h00 += g.w * (g.jl0[0] * g.jl0[0] + g.jl1[0] * g.jl1[0]);
         h10 += g.w * (g.jl0[1] * g.jl0[0] + g.jl1[1] * g.jl1[0]);
@@ -149,11 +167,16 @@ __global__ void __launch_bounds__(128) k_linearize(DevProblem P, int init_pass, 
     info[0] = i00, info[1] = i10, info[2] = i11, info[3] = i20, info[4] = i21, info[5] = i22;
     info[6] = z0, info[7] = z1, info[8] = z2;
 
+    cam_n = s0 < s1 ? __ldg(P.obs_cam + s0) : 0;
+    uv_n = s0 < s1 ? __ldg(P.obs_uv + s0) : make_float2(0.f, 0.f);
     for (int s = s0; s < s1; ++s) {
-        const int cam = __ldg(P.obs_cam + s);
-        const float2 uv = __ldg(P.obs_uv + s);
+        const int cam = cam_n;
+        const float2 uv = uv_n;
+        if (s + 1 < s1) cam_n = __ldg(P.obs_cam + s + 1), uv_n = __ldg(P.obs_uv + s + 1);
+        double rt[12];
+        load_rt(cam_rt, cam, rt);
         ObsGeom g;
-        obs_geometry(P, cam_rt + 12 * (size_t)cam, X, Y, Z, uv, g);
+        obs_geometry(P, rt, X, Y, Z, uv, g);
         // G = w Jl L^-T   (L^-T)[m][k] = Linv[k][m], k >= m
         const double g00 = g.w * (g.jl0[0] * i00);
         const double g01 = g.w * (g.jl0[0] * i10 + g.jl0[1] * i11);
@@ -573,11 +596,15 @@ __global__ void __launch_bounds__(128) k_update(DevProblem P)
     const double z0 = info[6], z1 = info[7], z2 = info[8];
     double y0 = z0, y1 = z1, y2 = z2, sc = 0.0;
     const int s0 = P.pt_ptr[p], s1 = P.pt_ptr[p + 1];
+    int cam_n = s0 < s1 ? __ldg(P.obs_cam + s0) : 0;
     for (int s = s0; s < s1; ++s) {
-        const int cam = __ldg(P.obs_cam + s);
+        const int cam = cam_n;
+        if (s + 1 < s1) cam_n = __ldg(P.obs_cam + s + 1);
         const double2* __restrict__ r = reinterpret_cast<const double2*>(P.rec + kRecDoubles * (size_t)s);
         const double2 r0 = r[0], r1 = r[1], r2 = r[2], r3 = r[3], r4 = r[4], r5 = r[5];
-        const double* __restrict__ d = P.dp + 6 * (size_t)cam;
+        const double2* __restrict__ d2 = reinterpret_cast<const double2*>(P.dp + 6 * (size_t)cam); // 48 bytes per pose
+        const double2 da = d2[0], db = d2[1], dc = d2[2];
+        const double d[6] = { da.x, da.y, db.x, db.y, dc.x, dc.y };
         double ja0[6], ja1[6];
         jtilde(r0.x, r0.y, r1.x, ja0, ja1);
         double t0 = 0.0, t1 = 0.0;
@@ -608,9 +635,14 @@ __global__ void __launch_bounds__(128) k_update(DevProblem P)
     if (PHOTO) return;
     const double* __restrict__ cam_rt = P.cam_rt[cand];
     double cost = 0.0;
+    cam_n = s0 < s1 ? __ldg(P.obs_cam + s0) : 0;
+    float2 uv_n = s0 < s1 ? __ldg(P.obs_uv + s0) : make_float2(0.f, 0.f);
     for (int s = s0; s < s1; ++s) {
-        const double* __restrict__ rt = cam_rt + 12 * (size_t)__ldg(P.obs_cam + s);
-        const float2 uv = __ldg(P.obs_uv + s);
+        const int cam = cam_n;
+        const float2 uv = uv_n;
+        if (s + 1 < s1) cam_n = __ldg(P.obs_cam + s + 1), uv_n = __ldg(P.obs_uv + s + 1);
+        double rt[12];
+        load_rt(cam_rt, cam, rt);
         const double x = rt[0] * X + rt[1] * Y + rt[2] * Z + rt[9];
         const double y = rt[3] * X + rt[4] * Y + rt[5] * Z + rt[10];
         const double z = rt[6] * X + rt[7] * Y + rt[8] * Z + rt[11];
