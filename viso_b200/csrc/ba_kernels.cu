@@ -746,6 +746,12 @@ int launch_lm_init(const DevProblem& P, double tau, double lambda_init, cudaStre
     return 1;
 }
 
+static int win_sm_count_hint()
+{
+    static PerDeviceOnce once;
+    return once.sm_count();
+}
+
 int launch_solve_small(const DevProblem& P, int max_n, cudaStream_t st)
 {
     const int n8 = (max_n + 7) & ~7;
@@ -754,7 +760,9 @@ int launch_solve_small(const DevProblem& P, int max_n, cudaStream_t st)
     constexpr size_t kMaxSmem = small_smem_bytes(kSmallN8);
     if (smem > kMaxSmem) return 0;
     if (!once.run([] { return cudaFuncSetAttribute(k_solve_small, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxSmem) == cudaSuccess; })) return 0;
-    const int threads = max_n <= 64 ? 128 : 256;
+    // a batch of small systems: 64 threads per CTA, so that all of 1024 problems are resident at once (8 CTAs per SM instead of
+    // 4 at 104 registers: one wave instead of two); a few systems: more threads per system.  Same arithmetic either way.
+    const int threads = max_n <= 64 ? (P.n_problems >= 4 * win_sm_count_hint() ? 64 : 128) : 256;
     k_solve_small<<<P.n_problems, threads, smem, st>>>(P);
     return 1;
 }
