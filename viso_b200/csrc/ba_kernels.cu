@@ -92,6 +92,18 @@ __device__ __forceinline__ void load_rt(const double* __restrict__ cam_rt, int c
     }
 }
 
+// 32-byte global accesses (sm_100: LDG / STG.256).  A per-observation record is three 32-byte sectors; written as six 16-byte
+// pieces by lanes whose records lie 1 KB apart, every store instruction became 32 half-sector requests to L2, and the
+// request rate, not the bytes, bounded k_linearize.  p must be 32-byte aligned.
+__device__ __forceinline__ void st_global_256(double* p, double a, double b, double c, double d)
+{
+    asm volatile("st.global.v4.f64 [%0], {%1, %2, %3, %4};" ::"l"(p), "d"(a), "d"(b), "d"(c), "d"(d) : "memory");
+}
+__device__ __forceinline__ void ld_global_256(const double* p, double& a, double& b, double& c, double& d)
+{
+    asm volatile("ld.global.v4.f64 {%0, %1, %2, %3}, [%4];" : "=d"(a), "=d"(b), "=d"(c), "=d"(d) : "l"(p));
+}
+
 __global__ void __launch_bounds__(128) k_linearize(DevProblem P, int init_pass, double lambda_override)
 {
     const int p = P.pt_begin + blockIdx.x * blockDim.x + threadIdx.x;
@@ -186,13 +198,10 @@ __global__ void __launch_bounds__(128) k_linearize(DevProblem P, int init_pass, 
         const double g12 = g.w * (g.jl1[0] * i20 + g.jl1[1] * i21 + g.jl1[2] * i22);
         const double v0 = g.w * g.ru + g00 * z0 + g01 * z1 + g02 * z2;
         const double v1 = g.w * g.rv + g10 * z0 + g11 * z1 + g12 * z2;
-        double2* r = reinterpret_cast<double2*>(P.rec + kRecDoubles * (size_t)s);
-        r[0] = make_double2(g.xn, g.yn);
-        r[1] = make_double2(g.iz, g.w);
-        r[2] = make_double2(P.fx * g00, P.fx * g01);
-        r[3] = make_double2(P.fx * g02, P.fy * g10);
-        r[4] = make_double2(P.fy * g11, P.fy * g12);
-        r[5] = make_double2(P.fx * v0, P.fy * v1);
+        double* r = P.rec + kRecDoubles * (size_t)s; // 96 bytes per record, the array 256-byte aligned
+        st_global_256(r, g.xn, g.yn, g.iz, g.w);
+        st_global_256(r + 4, P.fx * g00, P.fx * g01, P.fx * g02, P.fy * g10);
+        st_global_256(r + 8, P.fy * g11, P.fy * g12, P.fx * v0, P.fy * v1);
     }
 }
 
@@ -600,8 +609,13 @@ __global__ void __launch_bounds__(128) k_update(DevProblem P)
     for (int s = s0; s < s1; ++s) {
         const int cam = cam_n;
         if (s + 1 < s1) cam_n = __ldg(P.obs_cam + s + 1);
-        const double2* __restrict__ r = reinterpret_cast<const double2*>(P.rec + kRecDoubles * (size_t)s);
-        const double2 r0 = r[0], r1 = r[1], r2 = r[2], r3 = r[3], r4 = r[4], r5 = r[5];
+        double2 r0, r1, r2, r3, r4, r5;
+        {
+            const double* r = P.rec + kRecDoubles * (size_t)s;
+            ld_global_256(r, r0.x, r0.y, r1.x, r1.y);
+            ld_global_256(r + 4, r2.x, r2.y, r3.x, r3.y);
+            ld_global_256(r + 8, r4.x, r4.y, r5.x, r5.y);
+        }
         const double2* __restrict__ d2 = reinterpret_cast<const double2*>(P.dp + 6 * (size_t)cam); // 48 bytes per pose
         const double2 da = d2[0], db = d2[1], dc = d2[2];
         const double d[6] = { da.x, da.y, db.x, db.y, dc.x, dc.y };
