@@ -469,16 +469,24 @@ __global__ void __launch_bounds__(256) k_chunk_reduce(DevProblem P, int which)
     }
 }
 
-__global__ void k_prob_sums(DevProblem P, int which)
+// one WARP per problem: the lanes fetch 32 chunk partials at once (one large problem has ~1000 of them: a single thread took one
+// round trip after the other), lane 0's additions stay sequential in chunk order
+__global__ void __launch_bounds__(128) k_prob_sums(DevProblem P, int which)
 {
-    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    const int b = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (b >= P.n_problems) return;
     if (!P.lm[b].active && which != 2) return;
     double s0 = 0.0, s1 = 0.0;
-    for (int c = P.prob_chunk_ptr[b]; c < P.prob_chunk_ptr[b + 1]; ++c) {
-        s0 += P.chunk_part[2 * (size_t)c];
-        s1 += P.chunk_part[2 * (size_t)c + 1];
+    const int c1 = P.prob_chunk_ptr[b + 1];
+    for (int c = P.prob_chunk_ptr[b]; c < c1; c += 32) {
+        const double2 v = c + lane < c1 ? *reinterpret_cast<const double2*>(P.chunk_part + 2 * (size_t)(c + lane)) : make_double2(0.0, 0.0);
+        const int n = min(32, c1 - c);
+        for (int k = 0; k < n; ++k) {
+            s0 += __shfl_sync(0xffffffffu, v.x, k);
+            s1 += __shfl_sync(0xffffffffu, v.y, k);
+        }
     }
+    if (lane) return;
     P.prob_sums[2 * (size_t)b] = s0;
     P.prob_sums[2 * (size_t)b + 1] = s1;
 }
@@ -750,7 +758,7 @@ int launch_reduce(const DevProblem& P, int which, cudaStream_t st)
         k_chunk_reduce<<<P.n_chunks, 256, 0, st>>>(P, which);
         ++n;
     }
-    k_prob_sums<<<cdiv(P.n_problems, 128), 128, 0, st>>>(P, which);
+    k_prob_sums<<<cdiv(P.n_problems, 4), 128, 0, st>>>(P, which);
     return n + 1;
 }
 
